@@ -1,0 +1,112 @@
+"""ctypes binding of libgaussmart_b200.so (the C ABI declared in include/gaussmart_b200.h).
+
+There is NO fallback: if the shared library is missing or does not export the ABI, importing the
+product path raises.  Nothing here imports oracle/.
+"""
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_size_t, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libgaussmart_b200.so")
+
+GSM_OK = 0
+GSM_ERR_INVALID_ARGUMENT = 10001
+GSM_ERR_BINNING_OVERFLOW = 10002
+GSM_ERR_WORKSPACE_TOO_SMALL = 10003
+GSM_SURFEL_RECORD_BYTES = 80
+GSM_GRAD_RECORD_FLOATS = 20
+ABI_VERSION = 1
+
+EXPORTS = [
+    "gsm_last_error", "gsm_abi_version", "gsm_geometry_bytes", "gsm_image_bytes", "gsm_binning_bytes",
+    "gsm_binning_sorted_keys_offset", "gsm_image_ranges_offset", "gsm_image_ncontrib_offset",
+    "gsm_forward", "gsm_grad_workspace_bytes", "gsm_backward", "gsm_mark_visible",
+    "gsm_knn_workspace_bytes", "gsm_knn_dist2",
+]
+
+
+class ForwardArgs(Structure):
+    _fields_ = [
+        ("P", c_int), ("D", c_int), ("M", c_int), ("width", c_int), ("height", c_int),
+        ("tan_fovx", c_float), ("tan_fovy", c_float), ("scale_modifier", c_float),
+        ("prefiltered", c_int), ("debug", c_int),
+        ("background", c_void_p), ("means3D", c_void_p), ("shs", c_void_p), ("colors_precomp", c_void_p),
+        ("opacities", c_void_p), ("scales", c_void_p), ("rotations", c_void_p),
+        ("transMat_precomp", c_void_p), ("viewmatrix", c_void_p), ("projmatrix", c_void_p),
+        ("campos", c_void_p), ("out_color", c_void_p), ("out_others", c_void_p), ("radii", c_void_p),
+        ("geometry", c_void_p), ("geometry_bytes", c_size_t),
+        ("image", c_void_p), ("image_bytes", c_size_t),
+        ("binning", c_void_p), ("binning_bytes", c_size_t), ("binning_capacity", c_size_t),
+        ("num_rendered_host", POINTER(c_int)),
+    ]
+
+
+class BackwardArgs(Structure):
+    _fields_ = [
+        ("P", c_int), ("D", c_int), ("M", c_int), ("width", c_int), ("height", c_int),
+        ("tan_fovx", c_float), ("tan_fovy", c_float), ("scale_modifier", c_float), ("debug", c_int),
+        ("background", c_void_p), ("means3D", c_void_p), ("shs", c_void_p), ("colors_precomp", c_void_p),
+        ("scales", c_void_p), ("rotations", c_void_p), ("transMat_precomp", c_void_p),
+        ("viewmatrix", c_void_p), ("projmatrix", c_void_p), ("campos", c_void_p), ("radii", c_void_p),
+        ("geometry", c_void_p), ("image", c_void_p), ("binning", c_void_p),
+        ("dL_dout_color", c_void_p), ("dL_dout_others", c_void_p),
+        ("grad_workspace", c_void_p), ("grad_workspace_bytes", c_size_t),
+        ("dL_dmeans2D", c_void_p), ("dL_dcolors", c_void_p), ("dL_dopacity", c_void_p),
+        ("dL_dmeans3D", c_void_p), ("dL_dtransMat", c_void_p), ("dL_dsh", c_void_p),
+        ("dL_dscales", c_void_p), ("dL_drotations", c_void_p),
+    ]
+
+
+_lib = None
+
+
+def load():
+    """Load the shared library once; raise loudly if it is absent or the ABI does not match."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"gaussmart_b200: native library not built ({LIB_PATH}). Run `python -m gaussmart_b200.build` "
+            "(or __graft_entry__.build()). There is no CPU or PyTorch fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name in EXPORTS:
+        if not hasattr(lib, name):
+            raise ImportError(f"gaussmart_b200: {LIB_PATH} does not export {name}")
+    lib.gsm_last_error.restype = c_char_p
+    lib.gsm_abi_version.restype = c_int
+    for f in ("gsm_geometry_bytes", "gsm_grad_workspace_bytes", "gsm_knn_workspace_bytes"):
+        getattr(lib, f).restype = c_size_t
+        getattr(lib, f).argtypes = [c_int]
+    lib.gsm_image_bytes.restype = c_size_t
+    lib.gsm_image_bytes.argtypes = [c_int, c_int]
+    lib.gsm_image_ranges_offset.restype = c_size_t
+    lib.gsm_image_ranges_offset.argtypes = [c_int, c_int]
+    lib.gsm_image_ncontrib_offset.restype = c_size_t
+    lib.gsm_image_ncontrib_offset.argtypes = [c_int, c_int]
+    lib.gsm_binning_bytes.restype = c_size_t
+    lib.gsm_binning_bytes.argtypes = [c_size_t, c_int, c_int]
+    lib.gsm_binning_sorted_keys_offset.restype = c_size_t
+    lib.gsm_binning_sorted_keys_offset.argtypes = [c_size_t]
+    lib.gsm_forward.restype = c_int
+    lib.gsm_forward.argtypes = [POINTER(ForwardArgs), c_void_p]
+    lib.gsm_backward.restype = c_int
+    lib.gsm_backward.argtypes = [POINTER(BackwardArgs), c_void_p]
+    lib.gsm_mark_visible.restype = c_int
+    lib.gsm_mark_visible.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
+    lib.gsm_knn_dist2.restype = c_int
+    lib.gsm_knn_dist2.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
+    if lib.gsm_abi_version() != ABI_VERSION:
+        raise ImportError(f"gaussmart_b200: ABI version mismatch ({lib.gsm_abi_version()} != {ABI_VERSION})")
+    _lib = lib
+    return lib
+
+
+def last_error():
+    return load().gsm_last_error().decode("utf-8", "replace")
+
+
+def check(code, what):
+    if code != GSM_OK:
+        raise RuntimeError(f"gaussmart_b200 {what} failed (code {code}): {last_error()}")

@@ -1,0 +1,261 @@
+// C ABI entry points (include/gaussmart_b200.h): workspace layouts, forward, backward,
+// markVisible.  Host-side orchestration that replaces CudaRasterizer::Rasterizer::{forward,
+// backward,markVisible} (rasterizer_impl.cu:141-153,198-458).
+#include "common.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace gsm {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  return (int)e;
+}
+
+GeometryLayout geometry_layout(int P) {
+  GeometryLayout L{};
+  const size_t n = (size_t)(P > 0 ? P : 0);
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 128); return o; };
+  L.records = take(n * GSM_SURFEL_RECORD_BYTES);
+  L.tiles_touched = take(n * 4);
+  L.offsets = take(n * 4);
+  L.scan_temp_bytes = scan_temp_bytes(P);
+  L.scan_temp = take(L.scan_temp_bytes);
+  L.flags = take(16);
+  L.total = off + 128;
+  return L;
+}
+
+ImageLayout image_layout(int width, int height) {
+  ImageLayout L{};
+  const size_t N = (size_t)width * height;
+  const size_t Nt = (size_t)((width + TILE_X - 1) / TILE_X) * ((height + TILE_Y - 1) / TILE_Y);
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 128); return o; };
+  L.final_T = take(N * 3 * 4);
+  L.n_contrib = take(N * 2 * 4);
+  L.ranges = take(Nt * 8);
+  L.total = off + 128;
+  return L;
+}
+
+BinningLayout binning_layout(size_t capacity, int width, int height) {
+  (void)width; (void)height;
+  BinningLayout L{};
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 128); return o; };
+  L.point_list = take(capacity * 4);
+  L.keys_sorted = take(capacity * 8);
+  L.keys_unsorted = take(capacity * 8);
+  L.values_unsorted = take(capacity * 4);
+  L.sort_temp_bytes = sort_temp_bytes(capacity);
+  L.sort_temp = take(L.sort_temp_bytes);
+  L.total = off + 128;
+  return L;
+}
+
+// same function as getHigherMsb (rasterizer_impl.cu:35-50): number of bits needed for n
+static int higher_msb(uint32_t n) {
+  int bits = 0;
+  while (bits < 32 && (n >> bits)) bits++;
+  return bits;
+}
+
+}  // namespace gsm
+
+using namespace gsm;
+
+extern "C" const char* gsm_last_error(void) { return g_error; }
+extern "C" int gsm_abi_version(void) { return GSM_ABI_VERSION; }
+extern "C" size_t gsm_geometry_bytes(int P) { return geometry_layout(P).total; }
+extern "C" size_t gsm_image_bytes(int width, int height) { return image_layout(width, height).total; }
+extern "C" size_t gsm_binning_bytes(size_t capacity, int width, int height) {
+  return binning_layout(capacity, width, height).total;
+}
+extern "C" size_t gsm_binning_sorted_keys_offset(size_t capacity) { return binning_layout(capacity, 0, 0).keys_sorted; }
+extern "C" size_t gsm_image_ranges_offset(int width, int height) { return image_layout(width, height).ranges; }
+extern "C" size_t gsm_image_ncontrib_offset(int width, int height) { return image_layout(width, height).n_contrib; }
+extern "C" size_t gsm_grad_workspace_bytes(int P) {
+  return align_up((size_t)(P > 0 ? P : 0) * GSM_GRAD_RECORD_FLOATS * 4, 128) + 128;
+}
+
+static char* aligned_base(const void* p) {
+  return reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), 128));
+}
+
+extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (a == nullptr) { set_error("gsm_forward: null args"); return GSM_ERR_INVALID_ARGUMENT; }
+  const int P = a->P, W = a->width, H = a->height;
+  const bool debug = a->debug != 0;
+  if (P < 0 || W <= 0 || H <= 0) { set_error("gsm_forward: bad sizes P=%d W=%d H=%d", P, W, H); return GSM_ERR_INVALID_ARGUMENT; }
+  if (a->num_rendered_host == nullptr) { set_error("gsm_forward: num_rendered_host is null"); return GSM_ERR_INVALID_ARGUMENT; }
+  if ((a->shs == nullptr) == (a->colors_precomp == nullptr) && P > 0) {
+    set_error("gsm_forward: exactly one of shs / colors_precomp must be given"); return GSM_ERR_INVALID_ARGUMENT;
+  }
+  if (P > 0 && a->transMat_precomp == nullptr && (a->scales == nullptr || a->rotations == nullptr)) {
+    set_error("gsm_forward: scales+rotations or transMat_precomp must be given"); return GSM_ERR_INVALID_ARGUMENT;
+  }
+  if (a->shs != nullptr && (a->D < 0 || a->D > 3 || (a->D + 1) * (a->D + 1) > a->M)) {
+    set_error("gsm_forward: SH degree %d needs %d coefficients, M=%d", a->D, (a->D + 1) * (a->D + 1), a->M);
+    return GSM_ERR_INVALID_ARGUMENT;
+  }
+  const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
+  const int num_tiles = grid_x * grid_y;
+  *a->num_rendered_host = 0;
+
+  const GeometryLayout G = geometry_layout(P);
+  const ImageLayout I = image_layout(W, H);
+  if (a->geometry_bytes < G.total || a->image_bytes < I.total) {
+    set_error("gsm_forward: geometry/image workspace too small"); return GSM_ERR_WORKSPACE_TOO_SMALL;
+  }
+  char* geom = aligned_base(a->geometry);
+  char* img = aligned_base(a->image);
+  float4* records = (float4*)(geom + G.records);
+  uint32_t* tiles_touched = (uint32_t*)(geom + G.tiles_touched);
+  uint32_t* offsets = (uint32_t*)(geom + G.offsets);
+  uint32_t* flags = (uint32_t*)(geom + G.flags);
+  uint2* ranges = (uint2*)(img + I.ranges);
+
+  int R = 0;
+  if (P > 0) {
+    GSM_CUDA(cudaMemsetAsync(flags, 0, 16, stream));
+    FwdPreprocessParams pp{};
+    pp.P = P; pp.D = a->D; pp.M = a->M; pp.W = W; pp.H = H; pp.grid_x = grid_x; pp.grid_y = grid_y;
+    pp.scale_modifier = a->scale_modifier; pp.prefiltered = a->prefiltered;
+    pp.means3D = a->means3D; pp.scales = a->scales; pp.rotations = a->rotations; pp.opacities = a->opacities;
+    pp.shs = a->shs; pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;
+    pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
+    pp.radii = a->radii; pp.records = records; pp.tiles_touched = tiles_touched; pp.flags = flags;
+    launch_preprocess_fwd(pp, stream);
+    GSM_STAGE("forward preprocess");
+    GSM_CUDA(launch_inclusive_scan(tiles_touched, offsets, P, geom + G.scan_temp, G.scan_temp_bytes, stream));
+    GSM_STAGE("tile-count scan");
+    // S1: the one host<-device dependency of the forward (rasterizer_impl.cu:282)
+    uint32_t host_vals[2] = {0, 0};
+    GSM_CUDA(cudaMemcpyAsync(&host_vals[0], offsets + P - 1, 4, cudaMemcpyDeviceToHost, stream));
+    GSM_CUDA(cudaMemcpyAsync(&host_vals[1], flags, 4, cudaMemcpyDeviceToHost, stream));
+    GSM_CUDA(cudaStreamSynchronize(stream));
+    if (host_vals[1] != 0) {
+      set_error("Point is filtered although prefiltered is set. This shouldn't happen!");
+      return GSM_ERR_INVALID_ARGUMENT;
+    }
+    if (host_vals[0] > 0x7fffffffu) { set_error("gsm_forward: too many instances"); return GSM_ERR_INVALID_ARGUMENT; }
+    R = (int)host_vals[0];
+  }
+  *a->num_rendered_host = R;
+  if ((size_t)R > a->binning_capacity) {
+    set_error("gsm_forward: binning capacity %zu < num_rendered %d", a->binning_capacity, R);
+    return GSM_ERR_BINNING_OVERFLOW;
+  }
+  const BinningLayout B = binning_layout(a->binning_capacity, W, H);
+  char* bin = nullptr;
+  if (R > 0) {
+    if (a->binning == nullptr || a->binning_bytes < B.total) {
+      set_error("gsm_forward: binning workspace too small"); return GSM_ERR_WORKSPACE_TOO_SMALL;
+    }
+    bin = aligned_base(a->binning);
+    uint64_t* keys_unsorted = (uint64_t*)(bin + B.keys_unsorted);
+    uint64_t* keys_sorted = (uint64_t*)(bin + B.keys_sorted);
+    uint32_t* values_unsorted = (uint32_t*)(bin + B.values_unsorted);
+    uint32_t* point_list = (uint32_t*)(bin + B.point_list);
+    launch_duplicate_with_keys(P, records, offsets, a->radii, keys_unsorted, values_unsorted, grid_x, grid_y, stream);
+    GSM_STAGE("duplicate with keys");
+    const int end_bit = 32 + higher_msb((uint32_t)num_tiles);
+    GSM_CUDA(launch_sort_pairs(keys_unsorted, keys_sorted, values_unsorted, point_list, (size_t)R, end_bit,
+                               bin + B.sort_temp, B.sort_temp_bytes, stream));
+    GSM_STAGE("sort");
+    launch_tile_ranges((size_t)R, keys_sorted, ranges, num_tiles, stream);
+    GSM_STAGE("tile ranges");
+  } else {
+    GSM_CUDA(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream));
+  }
+  if (P > 0) {  // the reference returns zero images without launching when P == 0 (rasterize_points.cu:99)
+    FwdRenderParams rp{};
+    rp.W = W; rp.H = H; rp.grid_x = grid_x; rp.grid_y = grid_y;
+    rp.ranges = ranges;
+    rp.point_list = bin ? (const uint32_t*)(bin + B.point_list) : nullptr;
+    rp.records = records; rp.background = a->background;
+    rp.final_T = (float*)(img + I.final_T); rp.n_contrib = (uint32_t*)(img + I.n_contrib);
+    rp.out_color = a->out_color; rp.out_others = a->out_others;
+    launch_render_fwd(rp, stream);
+    GSM_STAGE("forward render");
+  } else {
+    GSM_CUDA(cudaMemsetAsync(a->out_color, 0, sizeof(float) * 3 * (size_t)W * H, stream));
+    GSM_CUDA(cudaMemsetAsync(a->out_others, 0, sizeof(float) * 7 * (size_t)W * H, stream));
+  }
+  return GSM_OK;
+}
+
+extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (a == nullptr) { set_error("gsm_backward: null args"); return GSM_ERR_INVALID_ARGUMENT; }
+  const int P = a->P, W = a->width, H = a->height;
+  const bool debug = a->debug != 0;
+  if (P < 0 || W <= 0 || H <= 0) { set_error("gsm_backward: bad sizes"); return GSM_ERR_INVALID_ARGUMENT; }
+  if (P == 0) return GSM_OK;
+  if (a->grad_workspace == nullptr || a->grad_workspace_bytes < gsm_grad_workspace_bytes(P)) {
+    set_error("gsm_backward: grad workspace too small"); return GSM_ERR_WORKSPACE_TOO_SMALL;
+  }
+  const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
+  const GeometryLayout G = geometry_layout(P);
+  const ImageLayout I = image_layout(W, H);
+  const char* geom = aligned_base(a->geometry);
+  const char* img = aligned_base(a->image);
+  const char* bin = a->binning ? aligned_base(a->binning) : nullptr;
+  float* grad_records = (float*)aligned_base(a->grad_workspace);
+  GSM_CUDA(cudaMemsetAsync(grad_records, 0, (size_t)P * GSM_GRAD_RECORD_FLOATS * 4, stream));
+
+  BwdRenderParams rp{};
+  rp.W = W; rp.H = H; rp.grid_x = grid_x; rp.grid_y = grid_y;
+  rp.ranges = (const uint2*)(img + I.ranges);
+  rp.point_list = (const uint32_t*)bin;  // point_list sits at offset 0 of the binning workspace
+  rp.records = (const float4*)(geom + G.records);
+  rp.background = a->background;
+  rp.final_T = (const float*)(img + I.final_T);
+  rp.n_contrib = (const uint32_t*)(img + I.n_contrib);
+  rp.dL_dpix = a->dL_dout_color; rp.dL_dothers = a->dL_dout_others;
+  rp.grad_records = grad_records;
+  launch_render_bwd(rp, stream);
+  GSM_STAGE("backward render");
+
+  // W,H re-derived in fp32 exactly as backward.cu:613-614 with focal from rasterizer_impl.cu:387-388
+  const float focal_y = H / (2.0f * a->tan_fovy);
+  const float focal_x = W / (2.0f * a->tan_fovx);
+  volatile float wx = focal_x * a->tan_fovx;
+  volatile float wy = focal_y * a->tan_fovy;
+  BwdPreprocessParams pp{};
+  pp.P = P; pp.D = a->D; pp.M = a->M;
+  pp.W = (int)(wx * 2); pp.H = (int)(wy * 2);
+  pp.means3D = a->means3D; pp.scales = a->scales; pp.rotations = a->rotations; pp.shs = a->shs;
+  pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;
+  pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
+  pp.radii = a->radii; pp.records = rp.records; pp.grad_records = grad_records;
+  pp.dL_dmeans2D = a->dL_dmeans2D; pp.dL_dcolors = a->dL_dcolors; pp.dL_dopacity = a->dL_dopacity;
+  pp.dL_dmeans3D = a->dL_dmeans3D; pp.dL_dtransMat = a->dL_dtransMat; pp.dL_dsh = a->dL_dsh;
+  pp.dL_dscales = a->dL_dscales; pp.dL_drotations = a->dL_drotations;
+  launch_preprocess_bwd(pp, stream);
+  GSM_STAGE("backward preprocess");
+  return GSM_OK;
+}
+
+extern "C" int gsm_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                                const float* projmatrix, uint8_t* present, void* stream_) {
+  (void)projmatrix;  // the reference's NDC test is commented out (auxiliary.h:200)
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0) { set_error("gsm_mark_visible: negative P"); return GSM_ERR_INVALID_ARGUMENT; }
+  launch_mark_visible(P, means3D, viewmatrix, present, stream);
+  GSM_CUDA(cudaGetLastError());
+  return GSM_OK;
+}

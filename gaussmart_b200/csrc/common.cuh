@@ -1,0 +1,183 @@
+// Internal definitions shared by the sm_100a kernels of gaussmart_b200.
+// Not part of the C ABI (see include/gaussmart_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/gaussmart_b200.h"
+
+namespace gsm {
+
+// Tile geometry is fixed by the reference (cuda_rasterizer/config.h:15-17).
+constexpr int TILE_X = 16;
+constexpr int TILE_Y = 16;
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+
+// Compile-time constants of the reference (auxiliary.h:37-40).
+constexpr float NEAR_N = 0.2f;
+constexpr float FAR_N = 100.0f;
+constexpr float FILTER_INV_SQUARE = 2.0f;
+// (float)(3.0f * 0.707106f) as folded by the reference build: 0x4007C3AC
+#define GSM_MIN_RADIUS_BITS 0x4007C3ACu
+// far/(far-near) folded in fp32 by the reference build: 0x3F8041AB
+#define GSM_FAR_RATIO_BITS 0x3F8041ABu
+
+constexpr float ALPHA_MAX = 0.99f;
+constexpr float ALPHA_MIN = 1.0f / 255.0f;
+constexpr float T_EPS = 0.0001f;
+
+// Packed per-surfel record (GSM_SURFEL_RECORD_BYTES = 80): five float4.
+//   q0 = (Tu.x, Tu.y, Tu.z, centre.x)     Tu,Tv,Tw: rows of the splat->pixel homography
+//   q1 = (Tv.x, Tv.y, Tv.z, centre.y)     centre: AABB centre used by the low-pass filter
+//   q2 = (Tw.x, Tw.y, Tw.z, opacity)
+//   q3 = (n.x,  n.y,  n.z,  view depth)   n: view-space normal, flipped to face the camera
+//   q4 = (r,    g,    b,    clamp bits)   clamp bits: int bit c set when channel c was clamped at 0
+constexpr int REC_F4 = 5;
+
+// Gradient accumulation record (GSM_GRAD_RECORD_FLOATS = 20 floats, 80 B):
+//   [0..2] dTu  [3..5] dTv  [6..8] dTw  [9..10] dcentre  [11..13] drgb  [14..16] dnormal
+//   [17] dopacity  [18..19] pad
+constexpr int GREC = GSM_GRAD_RECORD_FLOATS;
+constexpr int GREC_USED = 18;
+
+__host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ---- workspace layouts ------------------------------------------------------------------
+struct GeometryLayout {
+  size_t records;        // float4[P*5]
+  size_t tiles_touched;  // u32[P]
+  size_t offsets;        // u32[P]   inclusive scan of tiles_touched
+  size_t scan_temp;      // bytes for the scan
+  size_t scan_temp_bytes;
+  size_t flags;          // u32[4]: [0] prefiltered-violation flag
+  size_t total;
+};
+GeometryLayout geometry_layout(int P);
+
+struct ImageLayout {
+  size_t final_T;    // f32[3*N]  (T, M1, M2)
+  size_t n_contrib;  // u32[2*N]  (last contributor, median contributor)
+  size_t ranges;     // uint2[Nt]
+  size_t total;
+};
+ImageLayout image_layout(int width, int height);
+
+struct BinningLayout {
+  size_t point_list;       // u32[cap]   sorted values     (kept for backward)
+  size_t keys_sorted;      // u64[cap]
+  size_t keys_unsorted;    // u64[cap]
+  size_t values_unsorted;  // u32[cap]
+  size_t sort_temp;
+  size_t sort_temp_bytes;
+  size_t total;
+};
+BinningLayout binning_layout(size_t capacity, int width, int height);
+
+// ---- error plumbing -----------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+
+#define GSM_CUDA(expr)                                   \
+  do {                                                   \
+    cudaError_t _e = (expr);                             \
+    if (_e != cudaSuccess) return gsm::cuda_fail(_e, #expr); \
+  } while (0)
+
+#define GSM_STAGE(stage_name)                                                   \
+  do {                                                                          \
+    cudaError_t _e = cudaGetLastError();                                        \
+    if (_e == cudaSuccess && debug) _e = cudaStreamSynchronize(stream);         \
+    if (_e != cudaSuccess) return gsm::cuda_fail(_e, stage_name);               \
+  } while (0)
+
+// ---- stage launchers (one translation unit each) ----------------------------------------
+struct FwdPreprocessParams {
+  int P, D, M, W, H;
+  int grid_x, grid_y;
+  float scale_modifier;
+  int prefiltered;
+  const float* means3D;
+  const float* scales;
+  const float* rotations;
+  const float* opacities;
+  const float* shs;
+  const float* transMat_precomp;
+  const float* colors_precomp;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  int* radii;
+  float4* records;
+  uint32_t* tiles_touched;
+  uint32_t* flags;
+};
+void launch_preprocess_fwd(const FwdPreprocessParams& p, cudaStream_t stream);
+void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present,
+                         cudaStream_t stream);
+
+size_t scan_temp_bytes(int P);
+cudaError_t launch_inclusive_scan(const uint32_t* in, uint32_t* out, int P, void* temp,
+                                  size_t temp_bytes, cudaStream_t stream);
+void launch_duplicate_with_keys(int P, const float4* records, const uint32_t* offsets,
+                                const int* radii, uint64_t* keys, uint32_t* values, int grid_x,
+                                int grid_y, cudaStream_t stream);
+size_t sort_temp_bytes(size_t n);
+cudaError_t launch_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in,
+                              uint32_t* vals_out, size_t n, int end_bit, void* temp,
+                              size_t temp_bytes, cudaStream_t stream);
+void launch_tile_ranges(size_t R, const uint64_t* keys_sorted, uint2* ranges, int num_tiles,
+                        cudaStream_t stream);
+
+struct FwdRenderParams {
+  int W, H, grid_x, grid_y;
+  const uint2* ranges;
+  const uint32_t* point_list;
+  const float4* records;
+  const float* background;
+  float* final_T;
+  uint32_t* n_contrib;
+  float* out_color;
+  float* out_others;
+};
+void launch_render_fwd(const FwdRenderParams& p, cudaStream_t stream);
+
+struct BwdRenderParams {
+  int W, H, grid_x, grid_y;
+  const uint2* ranges;
+  const uint32_t* point_list;
+  const float4* records;
+  const float* background;
+  const float* final_T;
+  const uint32_t* n_contrib;
+  const float* dL_dpix;
+  const float* dL_dothers;
+  float* grad_records;  // [P*GREC], zero-initialised
+};
+void launch_render_bwd(const BwdRenderParams& p, cudaStream_t stream);
+
+struct BwdPreprocessParams {
+  int P, D, M, W, H;  // W,H: the sizes re-derived in fp32 as backward.cu:613-614 does
+  const float* means3D;
+  const float* scales;
+  const float* rotations;
+  const float* shs;
+  const float* transMat_precomp;
+  const float* colors_precomp;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  const int* radii;
+  const float4* records;
+  const float* grad_records;
+  float* dL_dmeans2D;
+  float* dL_dcolors;
+  float* dL_dopacity;
+  float* dL_dmeans3D;
+  float* dL_dtransMat;
+  float* dL_dsh;
+  float* dL_dscales;
+  float* dL_drotations;
+};
+void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream);
+
+}  // namespace gsm

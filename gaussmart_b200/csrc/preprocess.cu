@@ -1,0 +1,250 @@
+// Forward per-surfel preprocess (K1) and markVisible (K7) for sm_100a.
+//
+// Restates, with its own data layout, what the reference does in
+//   cuda_rasterizer/forward.cu:20-71   (SH -> RGB, clamp flags)
+//   cuda_rasterizer/forward.cu:75-115  (splat->pixel homography T, view-space normal)
+//   cuda_rasterizer/forward.cu:119-145 (AABB centre / extent)
+//   cuda_rasterizer/forward.cu:175-251 (cull, radius, tile rect)
+//   cuda_rasterizer/auxiliary.h:67-77,185-235 (rect, frustum test, quaternion)
+//
+// radii, the tile rect and the depth key must be BIT-EXACT against the reference build, so every
+// expression feeding them is written with explicit round-to-nearest intrinsics in the operation
+// order the reference's sm_100a build performs (documented in DESIGN.md, "FP association").
+// Output is one packed 80-byte record per visible surfel instead of the reference's six SoA arrays.
+#include "common.cuh"
+
+namespace gsm {
+
+#define MUL(a, b) __fmul_rn((a), (b))
+#define ADD(a, b) __fadd_rn((a), (b))
+#define SUB(a, b) __fsub_rn((a), (b))
+#define FMA(a, b, c) __fmaf_rn((a), (b), (c))
+
+// SH basis constants as fp32 (auxiliary.h:43-60)
+__device__ __forceinline__ float3 sh_to_rgb(int D, const float4* __restrict__ sh4, float3 dir) {
+  // sh4 points at this surfel's M*3 floats (16-byte aligned when M*3*4 % 16 == 0, else scalar path)
+  const float* sh = reinterpret_cast<const float*>(sh4);
+  const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
+  float3 r;
+  r.x = MUL(C0, __ldg(sh + 0)); r.y = MUL(C0, __ldg(sh + 1)); r.z = MUL(C0, __ldg(sh + 2));
+  if (D > 0) {
+    const float x = dir.x, y = dir.y, z = dir.z;
+    float t = MUL(y, C1);
+    r.x = SUB(r.x, MUL(t, __ldg(sh + 3))); r.y = SUB(r.y, MUL(t, __ldg(sh + 4))); r.z = SUB(r.z, MUL(t, __ldg(sh + 5)));
+    t = MUL(z, C1);
+    r.x = FMA(t, __ldg(sh + 6), r.x); r.y = FMA(t, __ldg(sh + 7), r.y); r.z = FMA(t, __ldg(sh + 8), r.z);
+    t = MUL(x, C1);
+    r.x = SUB(r.x, MUL(t, __ldg(sh + 9))); r.y = SUB(r.y, MUL(t, __ldg(sh + 10))); r.z = SUB(r.z, MUL(t, __ldg(sh + 11)));
+    if (D > 1) {
+      const float xx = MUL(x, x), yy = MUL(y, y), zz = MUL(z, z);
+      const float xy = MUL(x, y), yz = MUL(y, z), xz = MUL(x, z);
+      const float C20 = 1.0925484305920792f, C21 = -1.0925484305920792f, C22 = 0.31539156525252005f,
+                  C23 = -1.0925484305920792f, C24 = 0.5462742152960396f;
+      t = MUL(xy, C20);
+      r.x = FMA(t, __ldg(sh + 12), r.x); r.y = FMA(t, __ldg(sh + 13), r.y); r.z = FMA(t, __ldg(sh + 14), r.z);
+      t = MUL(yz, C21);
+      r.x = FMA(t, __ldg(sh + 15), r.x); r.y = FMA(t, __ldg(sh + 16), r.y); r.z = FMA(t, __ldg(sh + 17), r.z);
+      const float zz2 = ADD(zz, zz);
+      t = MUL(SUB(SUB(zz2, xx), yy), C22);
+      r.x = FMA(t, __ldg(sh + 18), r.x); r.y = FMA(t, __ldg(sh + 19), r.y); r.z = FMA(t, __ldg(sh + 20), r.z);
+      t = MUL(xz, C23);
+      r.x = FMA(t, __ldg(sh + 21), r.x); r.y = FMA(t, __ldg(sh + 22), r.y); r.z = FMA(t, __ldg(sh + 23), r.z);
+      const float xx_yy = SUB(xx, yy);
+      t = MUL(xx_yy, C24);
+      r.x = FMA(t, __ldg(sh + 24), r.x); r.y = FMA(t, __ldg(sh + 25), r.y); r.z = FMA(t, __ldg(sh + 26), r.z);
+      if (D > 2) {
+        const float C30 = -0.5900435899266435f, C31 = 2.890611442640554f, C32 = -0.4570457994644658f,
+                    C33 = 0.3731763325901154f, C34 = -0.4570457994644658f, C35 = 1.445305721320277f,
+                    C36 = -0.5900435899266435f;
+        const float xx3 = MUL(xx, 3.0f), yy3 = MUL(yy, 3.0f);
+        const float zz4_xx_yy = SUB(SUB(MUL(zz, 4.0f), xx), yy);
+        t = MUL(MUL(y, C30), SUB(xx3, yy));
+        r.x = FMA(t, __ldg(sh + 27), r.x); r.y = FMA(t, __ldg(sh + 28), r.y); r.z = FMA(t, __ldg(sh + 29), r.z);
+        t = MUL(z, MUL(xy, C31));
+        r.x = FMA(t, __ldg(sh + 30), r.x); r.y = FMA(t, __ldg(sh + 31), r.y); r.z = FMA(t, __ldg(sh + 32), r.z);
+        t = MUL(MUL(y, C32), zz4_xx_yy);
+        r.x = FMA(t, __ldg(sh + 33), r.x); r.y = FMA(t, __ldg(sh + 34), r.y); r.z = FMA(t, __ldg(sh + 35), r.z);
+        t = MUL(MUL(z, C33), SUB(SUB(zz2, xx3), yy3));
+        r.x = FMA(t, __ldg(sh + 36), r.x); r.y = FMA(t, __ldg(sh + 37), r.y); r.z = FMA(t, __ldg(sh + 38), r.z);
+        t = MUL(MUL(x, C34), zz4_xx_yy);
+        r.x = FMA(t, __ldg(sh + 39), r.x); r.y = FMA(t, __ldg(sh + 40), r.y); r.z = FMA(t, __ldg(sh + 41), r.z);
+        t = MUL(MUL(z, C35), xx_yy);
+        r.x = FMA(t, __ldg(sh + 42), r.x); r.y = FMA(t, __ldg(sh + 43), r.y); r.z = FMA(t, __ldg(sh + 44), r.z);
+        t = MUL(MUL(x, C36), SUB(xx, yy3));
+        r.x = FMA(t, __ldg(sh + 45), r.x); r.y = FMA(t, __ldg(sh + 46), r.y); r.z = FMA(t, __ldg(sh + 47), r.z);
+      }
+    }
+  }
+  r.x = ADD(r.x, 0.5f); r.y = ADD(r.y, 0.5f); r.z = ADD(r.z, 0.5f);
+  return r;
+}
+
+// Quaternion (w,x,y,z) -> rotation columns, scaled: L0 = sx*R[:,0], L1 = sy*R[:,1], L2 = R[:,2]
+// (auxiliary.h:213-235, forward.cu:88-90).  rsqrtf is the approximate PTX rsqrt, as the reference.
+__device__ __forceinline__ void build_L(float4 q, float sx, float sy, float3& L0, float3& L1, float3& L2) {
+  float n2 = MUL(q.w, q.w);
+  n2 = FMA(q.x, q.x, n2);
+  n2 = FMA(q.y, q.y, n2);
+  n2 = FMA(q.z, q.z, n2);
+  const float s = rsqrtf(n2);
+  const float w = MUL(q.x, s), x = MUL(q.y, s), y = MUL(q.z, s), z = MUL(q.w, s);
+  const float yy = MUL(y, y), zz = MUL(z, z);
+  const float xy = MUL(x, y), wz = MUL(w, z), xz = MUL(x, z), wy = MUL(w, y), yz = MUL(y, z), wx = MUL(w, x);
+  const float xx_zz = FMA(x, x, zz), xx_yy = FMA(x, x, yy), yy_zz = ADD(yy, zz);
+  const float a = ADD(xy, wz), b = SUB(xy, wz), c = SUB(xz, wy), d = ADD(xz, wy), e = ADD(yz, wx), f = SUB(yz, wx);
+  const float R00 = SUB(1.0f, ADD(yy_zz, yy_zz)), R01 = ADD(a, a), R02 = ADD(c, c);
+  const float R10 = ADD(b, b), R11 = SUB(1.0f, ADD(xx_zz, xx_zz)), R12 = ADD(e, e);
+  const float R20 = ADD(d, d), R21 = ADD(f, f), R22 = SUB(1.0f, ADD(xx_yy, xx_yy));
+  L0 = make_float3(MUL(sx, R00), MUL(sx, R01), MUL(sx, R02));
+  L1 = make_float3(MUL(sy, R10), MUL(sy, R11), MUL(sy, R12));
+  L2 = make_float3(R20, R21, R22);
+}
+
+__device__ __forceinline__ float dot3_ref(float a0, float a1, float a2, float b0, float b1, float b2) {
+  // reference association of a0*b0 + a1*b1 + a2*b2:  fma(a2,b2, fma(a0,b0, a1*b1))
+  return FMA(a2, b2, FMA(a0, b0, MUL(a1, b1)));
+}
+
+__global__ void __launch_bounds__(256) preprocess_fwd_kernel(const FwdPreprocessParams p) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= p.P) return;
+
+  int radius_out = 0;
+  uint32_t tiles_out = 0;
+
+  // camera matrices are 16 floats each: uniform, served by the constant/L1 path
+  const float* __restrict__ vm = p.viewmatrix;
+  const float* __restrict__ pm = p.projmatrix;
+
+  const float px = __ldg(p.means3D + 3 * (size_t)idx + 0);
+  const float py = __ldg(p.means3D + 3 * (size_t)idx + 1);
+  const float pz = __ldg(p.means3D + 3 * (size_t)idx + 2);
+
+  // p_view = [p 1] * V   (auxiliary.h:79-87), association: m12 + fma(z,m8, fma(x,m0, y*m4))
+  const float vx = ADD(vm[12], FMA(pz, vm[8], FMA(px, vm[0], MUL(py, vm[4]))));
+  const float vy = ADD(vm[13], FMA(pz, vm[9], FMA(px, vm[1], MUL(py, vm[5]))));
+  const float vz = ADD(vm[14], FMA(pz, vm[10], FMA(px, vm[2], MUL(py, vm[6]))));
+
+  do {
+    if (vz <= NEAR_N) {  // auxiliary.h:200
+      if (p.prefiltered) atomicOr(p.flags, 1u);
+      break;
+    }
+
+    float Tu0, Tu1, Tu2, Tv0, Tv1, Tv2, Tw0, Tw1, Tw2;
+    float nx, ny, nz;
+    if (p.transMat_precomp == nullptr) {
+      const float2 sc = __ldg(reinterpret_cast<const float2*>(p.scales) + idx);
+      const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+      float3 L0, L1, L2;
+      build_L(q, MUL(p.scale_modifier, sc.x), MUL(p.scale_modifier, sc.y), L0, L1, L2);
+      // A = M^T * world2ndc, rows (L0,0), (L1,0), (p,1); columns c = 0..3 of projmatrix
+      float A0[4], A1[4], A2[4];
+#pragma unroll
+      for (int c = 0; c < 4; c++) {
+        A0[c] = FMA(L0.z, pm[8 + c], FMA(L0.x, pm[c], MUL(L0.y, pm[4 + c])));
+        A1[c] = FMA(L1.z, pm[8 + c], FMA(L1.x, pm[c], MUL(L1.y, pm[4 + c])));
+        A2[c] = ADD(pm[12 + c], FMA(pz, pm[8 + c], FMA(px, pm[c], MUL(py, pm[4 + c]))));
+      }
+      const float hW = MUL((float)p.W, 0.5f), hWm1 = MUL((float)(p.W - 1), 0.5f);
+      const float hH = MUL((float)p.H, 0.5f), hHm1 = MUL((float)(p.H - 1), 0.5f);
+      Tu0 = FMA(hWm1, A0[3], MUL(hW, A0[0])); Tu1 = FMA(hWm1, A1[3], MUL(hW, A1[0])); Tu2 = FMA(hWm1, A2[3], MUL(hW, A2[0]));
+      Tv0 = FMA(hHm1, A0[3], MUL(hH, A0[1])); Tv1 = FMA(hHm1, A1[3], MUL(hH, A1[1])); Tv2 = FMA(hHm1, A2[3], MUL(hH, A2[1]));
+      Tw0 = A0[3]; Tw1 = A1[3]; Tw2 = A2[3];
+      // normal = L2 * V[:3,:3]  (auxiliary.h:100-108)
+      nx = FMA(L2.z, vm[8], FMA(L2.x, vm[0], MUL(L2.y, vm[4])));
+      ny = FMA(L2.z, vm[9], FMA(L2.x, vm[1], MUL(L2.y, vm[5])));
+      nz = FMA(L2.z, vm[10], FMA(L2.x, vm[2], MUL(L2.y, vm[6])));
+    } else {
+      const float* T = p.transMat_precomp + 9 * (size_t)idx;
+      Tu0 = __ldg(T + 0); Tu1 = __ldg(T + 1); Tu2 = __ldg(T + 2);
+      Tv0 = __ldg(T + 3); Tv1 = __ldg(T + 4); Tv2 = __ldg(T + 5);
+      Tw0 = __ldg(T + 6); Tw1 = __ldg(T + 7); Tw2 = __ldg(T + 8);
+      nx = 0.0f; ny = 0.0f; nz = 1.0f;
+    }
+
+    // dual-visible flip (forward.cu:209-214): cos = -<p_view, n>
+    const float pn = FMA(vz, nz, FMA(vx, nx, MUL(vy, ny)));
+    if (pn == 0.0f) break;
+    const float mult = (pn < 0.0f) ? 1.0f : -1.0f;
+    nx = MUL(nx, mult); ny = MUL(ny, mult); nz = MUL(nz, mult);
+
+    // AABB (forward.cu:119-145), cutoff 3 -> t = (9, 9, -1)
+    const float d = SUB(FMA(MUL(Tw0, Tw0), 9.0f, MUL(MUL(Tw1, Tw1), 9.0f)), MUL(Tw2, Tw2));
+    if (d == 0.0f) break;
+    const float inv = __frcp_rn(d);
+    const float f9 = MUL(inv, 9.0f);
+    const float cx = SUB(FMA(f9, MUL(Tu0, Tw0), MUL(f9, MUL(Tu1, Tw1))), MUL(inv, MUL(Tu2, Tw2)));
+    const float cy = SUB(FMA(f9, MUL(Tv0, Tw0), MUL(f9, MUL(Tv1, Tw1))), MUL(inv, MUL(Tv2, Tw2)));
+    const float su = SUB(MUL(inv, MUL(Tu2, Tu2)), FMA(f9, MUL(Tu0, Tu0), MUL(f9, MUL(Tu1, Tu1))));
+    const float sv = SUB(MUL(inv, MUL(Tv2, Tv2)), FMA(f9, MUL(Tv0, Tv0), MUL(f9, MUL(Tv1, Tv1))));
+    const float hx = __fsqrt_rn(fmaxf(FMA(cx, cx, su), 1e-4f));
+    const float hy = __fsqrt_rn(fmaxf(FMA(cy, cy, sv), 1e-4f));
+    const float radius = ceilf(fmaxf(fmaxf(hx, hy), __uint_as_float(GSM_MIN_RADIUS_BITS)));
+    const int ri = (int)radius;
+    const float rf = (float)ri;
+
+    // tile rect (auxiliary.h:67-77); /16 is exact as *0.0625
+    const int minx = min(p.grid_x, max(0, (int)MUL(SUB(cx, rf), 0.0625f)));
+    const int miny = min(p.grid_y, max(0, (int)MUL(SUB(cy, rf), 0.0625f)));
+    const int maxx = min(p.grid_x, max(0, (int)MUL(ADD(ADD(ADD(cx, rf), 16.0f), -1.0f), 0.0625f)));
+    const int maxy = min(p.grid_y, max(0, (int)MUL(ADD(ADD(ADD(cy, rf), 16.0f), -1.0f), 0.0625f)));
+    const uint32_t area = (uint32_t)((maxx - minx) * (maxy - miny));
+    if (area == 0) break;
+
+    float3 rgb;
+    int clamp_bits = 0;
+    if (p.colors_precomp == nullptr) {
+      const float* cp = p.campos;
+      const float dx = SUB(px, cp[0]), dy = SUB(py, cp[1]), dz = SUB(pz, cp[2]);
+      const float len = __fsqrt_rn(FMA(dz, dz, FMA(dx, dx, MUL(dy, dy))));
+      const float3 dir = make_float3(__fdiv_rn(dx, len), __fdiv_rn(dy, len), __fdiv_rn(dz, len));
+      rgb = sh_to_rgb(p.D, reinterpret_cast<const float4*>(p.shs + (size_t)idx * p.M * 3), dir);
+      if (rgb.x < 0.0f) { clamp_bits |= 1; rgb.x = 0.0f; }
+      if (rgb.y < 0.0f) { clamp_bits |= 2; rgb.y = 0.0f; }
+      if (rgb.z < 0.0f) { clamp_bits |= 4; rgb.z = 0.0f; }
+    } else {
+      rgb.x = __ldg(p.colors_precomp + 3 * (size_t)idx + 0);
+      rgb.y = __ldg(p.colors_precomp + 3 * (size_t)idx + 1);
+      rgb.z = __ldg(p.colors_precomp + 3 * (size_t)idx + 2);
+    }
+
+    float4* rec = p.records + (size_t)idx * REC_F4;
+    rec[0] = make_float4(Tu0, Tu1, Tu2, cx);
+    rec[1] = make_float4(Tv0, Tv1, Tv2, cy);
+    rec[2] = make_float4(Tw0, Tw1, Tw2, __ldg(p.opacities + idx));
+    rec[3] = make_float4(nx, ny, nz, vz);
+    rec[4] = make_float4(rgb.x, rgb.y, rgb.z, __int_as_float(clamp_bits));
+    radius_out = ri;
+    tiles_out = area;
+  } while (false);
+
+  p.radii[idx] = radius_out;
+  p.tiles_touched[idx] = tiles_out;
+}
+
+void launch_preprocess_fwd(const FwdPreprocessParams& p, cudaStream_t stream) {
+  if (p.P <= 0) return;
+  preprocess_fwd_kernel<<<(p.P + 255) / 256, 256, 0, stream>>>(p);
+}
+
+// markVisible (rasterizer_impl.cu:54-66): present = view_z > 0.2
+__global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* __restrict__ means3D,
+                                                           const float* __restrict__ vm,
+                                                           uint8_t* __restrict__ present) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  const float px = __ldg(means3D + 3 * (size_t)idx + 0);
+  const float py = __ldg(means3D + 3 * (size_t)idx + 1);
+  const float pz = __ldg(means3D + 3 * (size_t)idx + 2);
+  const float vz = ADD(vm[14], FMA(pz, vm[10], FMA(px, vm[2], MUL(py, vm[6]))));
+  present[idx] = (vz <= NEAR_N) ? 0 : 1;
+}
+
+void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present,
+                         cudaStream_t stream) {
+  if (P <= 0) return;
+  mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, viewmatrix, present);
+}
+
+}  // namespace gsm

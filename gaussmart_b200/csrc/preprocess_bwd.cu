@@ -1,0 +1,270 @@
+// Backward per-surfel preprocess (K6) for sm_100a.
+//
+// Restates cuda_rasterizer/backward.cu:20-139 (SH backward), :449-579 (compute_transmat_aabb) and
+// :581-636 (preprocessCUDA), plus auxiliary.h:128-138 (dnormvdv) and :238-282 (quaternion VJP),
+// including the reference's deliberate deviations from autograd: scale modifier
+// forced to 1, rsqrt normaliser treated as constant, W/H re-derived from focal*tan in fp32, and
+// dL_dmean2D overwritten by the densification heuristic.
+// It reads the compact gradient record written by the backward compositing kernel and writes
+// EVERY public gradient row (zeros for culled surfels), so no output needs a prior memset.
+#include "common.cuh"
+
+namespace gsm {
+
+struct f3 { float x, y, z; };
+__device__ __forceinline__ f3 mk(float x, float y, float z) { return f3{x, y, z}; }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ f3 operator*(f3 a, f3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ f3 operator*(float s, f3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ float dot(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+__device__ __forceinline__ void store3(float* dst, f3 v) { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; }
+
+// SH backward (backward.cu:20-139). dL_dsh row is fully written (zeros beyond the active degree).
+__device__ void sh_backward(int D, int M, const float* __restrict__ sh, f3 dir_orig, f3 dL_dRGB,
+                            float* __restrict__ dL_dsh, f3& dL_dmean_add) {
+  const float inv_len = 1.0f / sqrtf(dot(dir_orig, dir_orig));
+  const float x = dir_orig.x * inv_len, y = dir_orig.y * inv_len, z = dir_orig.z * inv_len;
+  const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
+  f3 dx = mk(0, 0, 0), dy = mk(0, 0, 0), dz = mk(0, 0, 0);
+#define SH(k) mk(__ldg(sh + 3 * (k)), __ldg(sh + 3 * (k) + 1), __ldg(sh + 3 * (k) + 2))
+  store3(dL_dsh + 0, C0 * dL_dRGB);
+  int written = 1;
+  if (D > 0) {
+    store3(dL_dsh + 3, (-C1 * y) * dL_dRGB);
+    store3(dL_dsh + 6, (C1 * z) * dL_dRGB);
+    store3(dL_dsh + 9, (-C1 * x) * dL_dRGB);
+    dx = (-C1) * SH(3);
+    dy = (-C1) * SH(1);
+    dz = C1 * SH(2);
+    written = 4;
+    if (D > 1) {
+      const float C20 = 1.0925484305920792f, C21 = -1.0925484305920792f, C22 = 0.31539156525252005f,
+                  C23 = -1.0925484305920792f, C24 = 0.5462742152960396f;
+      const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+      store3(dL_dsh + 12, (C20 * xy) * dL_dRGB);
+      store3(dL_dsh + 15, (C21 * yz) * dL_dRGB);
+      store3(dL_dsh + 18, (C22 * (2.f * zz - xx - yy)) * dL_dRGB);
+      store3(dL_dsh + 21, (C23 * xz) * dL_dRGB);
+      store3(dL_dsh + 24, (C24 * (xx - yy)) * dL_dRGB);
+      const f3 s4 = SH(4), s5 = SH(5), s6 = SH(6), s7 = SH(7), s8 = SH(8);
+      dx = dx + (C20 * y) * s4 + (C22 * 2.f * -x) * s6 + (C23 * z) * s7 + (C24 * 2.f * x) * s8;
+      dy = dy + (C20 * x) * s4 + (C21 * z) * s5 + (C22 * 2.f * -y) * s6 + (C24 * 2.f * -y) * s8;
+      dz = dz + (C21 * y) * s5 + (C22 * 2.f * 2.f * z) * s6 + (C23 * x) * s7;
+      written = 9;
+      if (D > 2) {
+        const float C30 = -0.5900435899266435f, C31 = 2.890611442640554f, C32 = -0.4570457994644658f,
+                    C33 = 0.3731763325901154f, C34 = -0.4570457994644658f, C35 = 1.445305721320277f,
+                    C36 = -0.5900435899266435f;
+        store3(dL_dsh + 27, (C30 * y * (3.f * xx - yy)) * dL_dRGB);
+        store3(dL_dsh + 30, (C31 * xy * z) * dL_dRGB);
+        store3(dL_dsh + 33, (C32 * y * (4.f * zz - xx - yy)) * dL_dRGB);
+        store3(dL_dsh + 36, (C33 * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB);
+        store3(dL_dsh + 39, (C34 * x * (4.f * zz - xx - yy)) * dL_dRGB);
+        store3(dL_dsh + 42, (C35 * z * (xx - yy)) * dL_dRGB);
+        store3(dL_dsh + 45, (C36 * x * (xx - 3.f * yy)) * dL_dRGB);
+        const f3 s9 = SH(9), s10 = SH(10), s11 = SH(11), s12 = SH(12), s13 = SH(13), s14 = SH(14), s15 = SH(15);
+        dx = dx + ((C30 * 3.f * 2.f * xy) * s9 + (C31 * yz) * s10 + (C32 * -2.f * xy) * s11 +
+                   (C33 * -3.f * 2.f * xz) * s12 + (C34 * (-3.f * xx + 4.f * zz - yy)) * s13 +
+                   (C35 * 2.f * xz) * s14 + (C36 * 3.f * (xx - yy)) * s15);
+        dy = dy + ((C30 * 3.f * (xx - yy)) * s9 + (C31 * xz) * s10 + (C32 * (-3.f * yy + 4.f * zz - xx)) * s11 +
+                   (C33 * -3.f * 2.f * yz) * s12 + (C34 * -2.f * xy) * s13 + (C35 * -2.f * yz) * s14 +
+                   (C36 * -3.f * 2.f * xy) * s15);
+        dz = dz + ((C31 * xy) * s10 + (C32 * 4.f * 2.f * yz) * s11 + (C33 * 3.f * (2.f * zz - xx - yy)) * s12 +
+                   (C34 * 4.f * 2.f * xz) * s13 + (C35 * (xx - yy)) * s14);
+        written = 16;
+      }
+    }
+  }
+#undef SH
+  for (int k = written * 3; k < M * 3; k++) dL_dsh[k] = 0.0f;
+
+  const f3 dL_ddir = mk(dot(dx, dL_dRGB), dot(dy, dL_dRGB), dot(dz, dL_dRGB));
+  // dnormvdv (auxiliary.h:128-138)
+  const f3 v = dir_orig, dv = dL_ddir;
+  const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+  const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+  dL_dmean_add.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+  dL_dmean_add.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+  dL_dmean_add.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+}
+
+__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocessParams p) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= p.P) return;
+  const size_t i = (size_t)idx;
+  const bool visible = __ldg(p.radii + idx) > 0;
+
+  f3 dmean3D = mk(0, 0, 0);
+  float dmean2D_x = 0.f, dmean2D_y = 0.f, dopacity = 0.f;
+  f3 dcolor = mk(0, 0, 0);
+  float dscale_x = 0.f, dscale_y = 0.f;
+  float4 drot = make_float4(0, 0, 0, 0);
+  float dT[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  bool sh_written = false;
+
+  if (visible) {
+    const float* g = p.grad_records + i * GREC;
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(g) + 0);
+    const float4 g1 = __ldg(reinterpret_cast<const float4*>(g) + 1);
+    const float4 g2 = __ldg(reinterpret_cast<const float4*>(g) + 2);
+    const float4 g3 = __ldg(reinterpret_cast<const float4*>(g) + 3);
+    const float4 g4 = __ldg(reinterpret_cast<const float4*>(g) + 4);
+    dT[0] = g0.x; dT[1] = g0.y; dT[2] = g0.z; dT[3] = g0.w; dT[4] = g1.x; dT[5] = g1.y;
+    dT[6] = g1.z; dT[7] = g1.w; dT[8] = g2.x;
+    const float gcx = g2.y, gcy = g2.z;
+    dcolor = mk(g2.w, g3.x, g3.y);
+    const f3 dnormal = mk(g3.z, g3.w, g4.x);
+    dopacity = g4.y;
+    const float raw_dTu_z = dT[2], raw_dTv_z = dT[5];
+
+    const float* vm = p.viewmatrix;
+    const float* pm = p.projmatrix;
+    const f3 pos = mk(__ldg(p.means3D + 3 * i), __ldg(p.means3D + 3 * i + 1), __ldg(p.means3D + 3 * i + 2));
+    const float4* rec = p.records + i * REC_F4;
+    const float depth = __ldg(&rec[2].z);  // transMats[idx*9+8] of the forward
+
+    const bool precomp = (p.scales == nullptr);
+    f3 T0, T1, T2;            // rows Tu, Tv, Tw
+    f3 R0, R1, R2;            // rotation columns
+    f3 normal = mk(0, 0, 0);
+    float Pm[3][4];           // P[k][r] = (world2ndc * ndc2pix)[k][r]
+    float2 sc = make_float2(0, 0);
+    float4 q = make_float4(0, 0, 0, 0);
+    if (precomp) {
+      const float* T = p.transMat_precomp + 9 * i;
+      T0 = mk(__ldg(T + 0), __ldg(T + 1), __ldg(T + 2));
+      T1 = mk(__ldg(T + 3), __ldg(T + 4), __ldg(T + 5));
+      T2 = mk(__ldg(T + 6), __ldg(T + 7), __ldg(T + 8));
+    } else {
+      sc = __ldg(reinterpret_cast<const float2*>(p.scales) + idx);
+      q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+      const float s = rsqrtf(q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z);
+      const float w = q.x * s, x = q.y * s, y = q.z * s, z = q.w * s;
+      R0 = mk(1.f - 2.f * (y * y + z * z), 2.f * (x * y + w * z), 2.f * (x * z - w * y));
+      R1 = mk(2.f * (x * y - w * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z + w * x));
+      R2 = mk(2.f * (x * z + w * y), 2.f * (y * z - w * x), 1.f - 2.f * (x * x + y * y));
+      const f3 L0 = sc.x * R0, L1 = sc.y * R1;  // scale modifier forced to 1 (backward.cu:487)
+      const float hW = float(p.W) / 2.0f, hWm1 = float(p.W - 1) / 2.0f;
+      const float hH = float(p.H) / 2.0f, hHm1 = float(p.H - 1) / 2.0f;
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        Pm[0][r] = pm[4 * r + 0] * hW + pm[4 * r + 3] * hWm1;
+        Pm[1][r] = pm[4 * r + 1] * hH + pm[4 * r + 3] * hHm1;
+        Pm[2][r] = pm[4 * r + 3];
+      }
+      // T[k][c] = <M[c], P[k]>, M[0]=(L0,0), M[1]=(L1,0), M[2]=(pos,1)
+      float Tm[3][3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        Tm[k][0] = L0.x * Pm[k][0] + L0.y * Pm[k][1] + L0.z * Pm[k][2];
+        Tm[k][1] = L1.x * Pm[k][0] + L1.y * Pm[k][1] + L1.z * Pm[k][2];
+        Tm[k][2] = pos.x * Pm[k][0] + pos.y * Pm[k][1] + pos.z * Pm[k][2] + Pm[k][3];
+      }
+      T0 = mk(Tm[0][0], Tm[0][1], Tm[0][2]);
+      T1 = mk(Tm[1][0], Tm[1][1], Tm[1][2]);
+      T2 = mk(Tm[2][0], Tm[2][1], Tm[2][2]);
+      normal = mk(vm[0] * R2.x + vm[4] * R2.y + vm[8] * R2.z, vm[1] * R2.x + vm[5] * R2.y + vm[9] * R2.z,
+                  vm[2] * R2.x + vm[6] * R2.y + vm[10] * R2.z);
+    }
+
+    f3 dT0 = mk(dT[0], dT[1], dT[2]), dT1 = mk(dT[3], dT[4], dT[5]), dT2 = mk(dT[6], dT[7], dT[8]);
+    bool chained = false;
+    if (gcx != 0.f || gcy != 0.f) {  // AABB-centre chain (backward.cu:521-535)
+      const f3 tv = mk(9.0f, 9.0f, -1.0f);
+      const float d = dot(tv, T2 * T2);
+      const f3 fv = (1.0f / d) * tv;
+      const f3 a0 = gcx * (fv * T2);
+      const f3 a1 = gcy * (fv * T2);
+      f3 a3 = gcx * (fv * T0) + gcy * (fv * T1);
+      const f3 dL_df = gcx * (T0 * T2) + gcy * (T1 * T2);
+      const float dL_dd = dot(dL_df, fv) * (-1.0f / d);
+      const f3 dd_dT3 = 2.0f * (tv * T2);
+      a3 = a3 + dL_dd * dd_dT3;
+      dT0 = dT0 + a0; dT1 = dT1 + a1; dT2 = dT2 + a3;
+      chained = true;
+    }
+    if (precomp) {
+      if (chained) {
+        dT[0] = dT0.x; dT[1] = dT0.y; dT[2] = dT0.z; dT[3] = dT1.x; dT[4] = dT1.y; dT[5] = dT1.z;
+        dT[6] = dT2.x; dT[7] = dT2.y; dT[8] = dT2.z;
+      }
+    } else {
+      // dL_dM[c] = sum_k P[k] * dL_dT[k][c]   (backward.cu:554)
+      const float dTk[3][3] = {{dT0.x, dT0.y, dT0.z}, {dT1.x, dT1.y, dT1.z}, {dT2.x, dT2.y, dT2.z}};
+      f3 dM[3];
+#pragma unroll
+      for (int c = 0; c < 3; c++) {
+        dM[c].x = Pm[0][0] * dTk[0][c] + Pm[1][0] * dTk[1][c] + Pm[2][0] * dTk[2][c];
+        dM[c].y = Pm[0][1] * dTk[0][c] + Pm[1][1] * dTk[1][c] + Pm[2][1] * dTk[2][c];
+        dM[c].z = Pm[0][2] * dTk[0][c] + Pm[1][2] * dTk[1][c] + Pm[2][2] * dTk[2][c];
+      }
+      // dL_dtn = V[:3,:3] * dL_dnormal (auxiliary.h:110-118), dual-visible sign (backward.cu:556-561)
+      f3 dtn = mk(vm[0] * dnormal.x + vm[1] * dnormal.y + vm[2] * dnormal.z,
+                  vm[4] * dnormal.x + vm[5] * dnormal.y + vm[6] * dnormal.z,
+                  vm[8] * dnormal.x + vm[9] * dnormal.y + vm[10] * dnormal.z);
+      const f3 pv = mk(vm[0] * pos.x + vm[4] * pos.y + vm[8] * pos.z + vm[12],
+                       vm[1] * pos.x + vm[5] * pos.y + vm[9] * pos.z + vm[13],
+                       vm[2] * pos.x + vm[6] * pos.y + vm[10] * pos.z + vm[14]);
+      const float cosv = -(pv.x * normal.x + pv.y * normal.y + pv.z * normal.z);
+      const float mult = cosv > 0 ? 1.f : -1.f;
+      dtn = mult * dtn;
+      const f3 dRS0 = dM[0], dRS1 = dM[1], dRS2 = dtn;
+      // v_R columns
+      const f3 vR0 = sc.x * dRS0, vR1 = sc.y * dRS1, vR2 = dRS2;
+      // quaternion VJP with the normaliser treated as constant (auxiliary.h:238-282)
+      const float s = rsqrtf(q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z);
+      const float w = q.x * s, x = q.y * s, y = q.z * s, z = q.w * s;
+      // v_R[c][r]: column c, row r
+      drot.x = 2.f * (x * (vR1.z - vR2.y) + y * (vR2.x - vR0.z) + z * (vR0.y - vR1.x));
+      drot.y = 2.f * (-2.f * x * (vR1.y + vR2.z) + y * (vR0.y + vR1.x) + z * (vR0.z + vR2.x) + w * (vR1.z - vR2.y));
+      drot.z = 2.f * (x * (vR0.y + vR1.x) - 2.f * y * (vR0.x + vR2.z) + z * (vR1.z + vR2.y) + w * (vR2.x - vR0.z));
+      drot.w = 2.f * (x * (vR0.z + vR2.x) + y * (vR1.z + vR2.y) - 2.f * z * (vR0.x + vR1.y) + w * (vR0.y - vR1.x));
+      dscale_x = dot(dRS0, R0);
+      dscale_y = dot(dRS1, R1);
+      dmean3D = dM[2];
+    }
+
+    if (p.shs != nullptr) {
+      const int clamp_bits = __float_as_int(__ldg(&rec[4].w));
+      f3 dRGB = dcolor;
+      if (clamp_bits & 1) dRGB.x = 0.f;
+      if (clamp_bits & 2) dRGB.y = 0.f;
+      if (clamp_bits & 4) dRGB.z = 0.f;
+      const f3 dir_orig = mk(pos.x - p.campos[0], pos.y - p.campos[1], pos.z - p.campos[2]);
+      f3 add;
+      sh_backward(p.D, p.M, p.shs + i * p.M * 3, dir_orig, dRGB, p.dL_dsh + i * p.M * 3, add);
+      dmean3D = dmean3D + add;
+      sh_written = true;
+    }
+
+    // densification heuristic (backward.cu:632-635); in the precomputed-T case the reference reads
+    // the (possibly rewritten) dL_dtransMat, otherwise the raw accumulation.
+    const float a2 = precomp ? dT[2] : raw_dTu_z;
+    const float a5 = precomp ? dT[5] : raw_dTv_z;
+    dmean2D_x = a2 * depth * 0.5f * float(p.W);
+    dmean2D_y = a5 * depth * 0.5f * float(p.H);
+  }
+
+  if (p.dL_dsh != nullptr && !sh_written) {
+    float* o = p.dL_dsh + i * p.M * 3;
+    for (int k = 0; k < p.M * 3; k++) o[k] = 0.f;
+  }
+  p.dL_dmeans2D[3 * i] = dmean2D_x; p.dL_dmeans2D[3 * i + 1] = dmean2D_y; p.dL_dmeans2D[3 * i + 2] = 0.f;
+  p.dL_dopacity[i] = dopacity;
+  store3(p.dL_dmeans3D + 3 * i, dmean3D);
+  if (p.dL_dcolors) store3(p.dL_dcolors + 3 * i, dcolor);
+  if (p.dL_dtransMat) {
+#pragma unroll
+    for (int k = 0; k < 9; k++) p.dL_dtransMat[9 * i + k] = dT[k];
+  }
+  if (p.dL_dscales) { p.dL_dscales[2 * i] = dscale_x; p.dL_dscales[2 * i + 1] = dscale_y; }
+  if (p.dL_drotations) reinterpret_cast<float4*>(p.dL_drotations)[i] = drot;
+}
+
+void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream) {
+  if (p.P <= 0) return;
+  preprocess_bwd_kernel<<<(p.P + 255) / 256, 256, 0, stream>>>(p);
+}
+
+}  // namespace gsm

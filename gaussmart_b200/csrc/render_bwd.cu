@@ -1,0 +1,276 @@
+// Backward per-tile compositing (K5) for sm_100a.
+//
+// Restates cuda_rasterizer/backward.cu:143-446 (renderCUDA): the tile's depth-sorted list is
+// replayed back to front, T is reconstructed by division (backward.cu:319) and the per-pair
+// gradients w.r.t. the homography rows Tu/Tv/Tw, the AABB centre, colour, normal and opacity are
+// produced.  Differences in HOW:
+//   * the replay starts at the tile's deepest contributor (max n_contrib over the tile, and per
+//     warp over the warp's 32 pixels) instead of the end of the list;
+//   * the 18 per-pair partial gradients are reduced across the warp with a recursive-halving
+//     shuffle network (21 shuffles) and leave the SM as ONE red.global.add per value per
+//     warp-surfel instead of one atomic per value per pixel-surfel (backward.cu:339-443);
+//   * they land in a compact 80-byte per-surfel gradient record that the backward preprocess
+//     expands, so only 80*P bytes are zero-filled per backward instead of 76 floats * P.
+#include "common.cuh"
+#include <cuda_pipeline.h>
+
+namespace gsm {
+
+#define MUL(a, b) __fmul_rn((a), (b))
+#define ADD(a, b) __fadd_rn((a), (b))
+#define SUB(a, b) __fsub_rn((a), (b))
+#define FMA(a, b, c) __fmaf_rn((a), (b), (c))
+
+constexpr int BWD_BATCH = 256;
+
+struct BwdSmem {
+  float4 q[2][REC_F4][BWD_BATCH];
+  uint32_t id[2][BWD_BATCH];
+  int warp_max[TILE_PIX / 32];
+};
+
+__device__ __forceinline__ void stage_batch_rev(BwdSmem& sm, int s, const float4* __restrict__ records,
+                                                const uint32_t* __restrict__ point_list,
+                                                uint32_t list_begin, int pos, int t) {
+  // pos: position (0-based within the tile list) of this thread's entry; negative => none
+  if (pos >= 0) {
+    const uint32_t id = __ldg(point_list + list_begin + pos);
+    sm.id[s][t] = id;
+    const float4* src = records + (size_t)id * REC_F4;
+#pragma unroll
+    for (int f = 0; f < REC_F4; f++) __pipeline_memcpy_async(&sm.q[s][f][t], src + f, sizeof(float4));
+  }
+}
+
+// Recursive-halving reduce-scatter of 16 values over 32 lanes + 2 extra values.
+// On return lane L holds in v[0] the warp sum of slot (L>>1)&15 (both lanes of a pair hold it),
+// e0 holds the warp sum of extra slot (L>>4) (16 or 17).
+__device__ __forceinline__ void warp_reduce_scatter18(float (&v)[16], float& e0, float e1, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  {
+    const bool up = lane & 16;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const float send = up ? v[i] : v[i + 8];
+      const float keep = up ? v[i + 8] : v[i];
+      v[i] = keep + __shfl_xor_sync(FULL, send, 16);
+    }
+    const float send = up ? e0 : e1;
+    const float keep = up ? e1 : e0;
+    e0 = keep + __shfl_xor_sync(FULL, send, 16);
+  }
+  {
+    const bool up = lane & 8;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const float send = up ? v[i] : v[i + 4];
+      const float keep = up ? v[i + 4] : v[i];
+      v[i] = keep + __shfl_xor_sync(FULL, send, 8);
+    }
+    e0 += __shfl_xor_sync(FULL, e0, 8);
+  }
+  {
+    const bool up = lane & 4;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const float send = up ? v[i] : v[i + 2];
+      const float keep = up ? v[i + 2] : v[i];
+      v[i] = keep + __shfl_xor_sync(FULL, send, 4);
+    }
+    e0 += __shfl_xor_sync(FULL, e0, 4);
+  }
+  {
+    const bool up = lane & 2;
+    const float send = up ? v[0] : v[1];
+    const float keep = up ? v[1] : v[0];
+    v[0] = keep + __shfl_xor_sync(FULL, send, 2);
+    e0 += __shfl_xor_sync(FULL, e0, 2);
+  }
+  v[0] += __shfl_xor_sync(FULL, v[0], 1);
+  e0 += __shfl_xor_sync(FULL, e0, 1);
+}
+
+__global__ void __launch_bounds__(TILE_PIX, 2) render_bwd_kernel(const BwdRenderParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
+
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const uint32_t pixx = blockIdx.x * TILE_X + (t & 15);
+  const uint32_t pixy = blockIdx.y * TILE_Y + (t >> 4);
+  const bool inside = pixx < (uint32_t)p.W && pixy < (uint32_t)p.H;
+  const float pxf = (float)pixx, pyf = (float)pixy;
+  const size_t N = (size_t)p.W * p.H;
+  const size_t pix = (size_t)pixy * p.W + pixx;
+  const uint2 range = __ldg(p.ranges + blockIdx.y * p.grid_x + blockIdx.x);
+
+  const float T_final = inside ? __ldg(p.final_T + pix) : 0.0f;
+  const float final_D = inside ? __ldg(p.final_T + pix + N) : 0.0f;
+  const float final_D2 = inside ? __ldg(p.final_T + pix + 2 * N) : 0.0f;
+  const float final_A = 1.0f - T_final;
+  const int last_contributor = inside ? (int)__ldg(p.n_contrib + pix) : 0;
+  const int median_contributor = inside ? (int)__ldg(p.n_contrib + pix + N) : 0;
+
+  float dL_dpixel[3] = {0.f, 0.f, 0.f}, dL_dnormal2D[3] = {0.f, 0.f, 0.f};
+  float dL_ddepth = 0.f, dL_daccum = 0.f, dL_dreg = 0.f, dL_dmedian_depth = 0.f;
+  if (inside) {
+#pragma unroll
+    for (int ch = 0; ch < 3; ch++) dL_dpixel[ch] = __ldg(p.dL_dpix + ch * N + pix);
+    dL_ddepth = __ldg(p.dL_dothers + 0 * N + pix);
+    dL_daccum = __ldg(p.dL_dothers + 1 * N + pix);
+#pragma unroll
+    for (int ch = 0; ch < 3; ch++) dL_dnormal2D[ch] = __ldg(p.dL_dothers + (2 + ch) * N + pix);
+    dL_dmedian_depth = __ldg(p.dL_dothers + 5 * N + pix);
+    dL_dreg = __ldg(p.dL_dothers + 6 * N + pix);
+  }
+  float bg_dot_dpixel = 0.f;
+#pragma unroll
+  for (int ch = 0; ch < 3; ch++) bg_dot_dpixel += __ldg(p.background + ch) * dL_dpixel[ch];
+
+  // deepest contributor of the warp / of the tile
+  const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+  if (lane == 0) sm.warp_max[warp] = warp_last;
+  __syncthreads();
+  int start = 0;
+#pragma unroll
+  for (int w = 0; w < TILE_PIX / 32; w++) start = max(start, sm.warp_max[w]);
+  const int rounds = (start + BWD_BATCH - 1) / BWD_BATCH;
+
+  float T = T_final;
+  float accum_rec[3] = {0.f, 0.f, 0.f}, last_color[3] = {0.f, 0.f, 0.f};
+  float last_alpha = 0.f, last_depth = 0.f, last_normal[3] = {0.f, 0.f, 0.f};
+  float accum_depth_rec = 0.f, accum_alpha_rec = 0.f, accum_normal_rec[3] = {0.f, 0.f, 0.f};
+  float last_dL_dT = 0.f;
+  const float far_ratio = __uint_as_float(GSM_FAR_RATIO_BITS);
+
+  if (rounds > 0) stage_batch_rev(sm, 0, p.records, p.point_list, range.x, start - 1 - t, t);
+  __pipeline_commit();
+
+  for (int i = 0; i < rounds; i++) {
+    const int s = i & 1;
+    __pipeline_wait_prior(0);
+    __syncthreads();
+    if (i + 1 < rounds)
+      stage_batch_rev(sm, s ^ 1, p.records, p.point_list, range.x, start - 1 - ((i + 1) * BWD_BATCH + t), t);
+    __pipeline_commit();
+
+    const int base_pos = start - 1 - i * BWD_BATCH;  // position of entry j = base_pos - j
+    const int n = min(BWD_BATCH, base_pos + 1);
+    const int j0 = max(0, base_pos + 1 - warp_last);  // entries before j0 are behind every pixel of the warp
+    for (int j = j0; j < n; j++) {
+      const int k = base_pos - j;  // == the reference's `contributor` after its decrement
+      bool active = k < last_contributor;
+      const float4 a = sm.q[s][0][j], b = sm.q[s][1][j], c = sm.q[s][2][j];
+      const float kx = SUB(MUL(c.x, pxf), a.x), ky = SUB(MUL(c.y, pxf), a.y), kz = SUB(MUL(c.z, pxf), a.z);
+      const float lx = SUB(MUL(c.x, pyf), b.x), ly = SUB(MUL(c.y, pyf), b.y), lz = SUB(MUL(c.z, pyf), b.z);
+      const float ppx = SUB(MUL(ky, lz), MUL(ly, kz));
+      const float ppy = SUB(MUL(lx, kz), MUL(kx, lz));
+      const float ppz = SUB(MUL(kx, ly), MUL(lx, ky));
+      active = active && (ppz != 0.0f);
+      const float sx = __fdiv_rn(ppx, ppz), sy = __fdiv_rn(ppy, ppz);
+      const float rho3d = FMA(sx, sx, MUL(sy, sy));
+      const float dx = SUB(a.w, pxf), dy = SUB(b.w, pyf);
+      const float r2 = FMA(dy, dy, MUL(dx, dx));
+      const float rho2d = ADD(r2, r2);
+      const float rho = fminf(rho3d, rho2d);
+      const float c_d = ADD(c.z, FMA(c.x, sx, MUL(c.y, sy)));
+      active = active && !(c_d < NEAR_N);
+      const float power = MUL(rho, -0.5f);
+      active = active && !(power > 0.0f);
+      const float G = expf(power);
+      const float alpha = fminf(MUL(c.w, G), ALPHA_MAX);
+      active = active && !(alpha < ALPHA_MIN);
+      if (!__any_sync(0xffffffffu, active)) continue;
+
+      float v[16];
+      float e0 = 0.f, e1 = 0.f;
+#pragma unroll
+      for (int z = 0; z < 16; z++) v[z] = 0.f;
+
+      if (active) {
+        const float4 nrm = sm.q[s][3][j], col = sm.q[s][4][j];
+        const float normal[3] = {nrm.x, nrm.y, nrm.z};
+        const float color[3] = {col.x, col.y, col.z};
+        T = __fdiv_rn(T, SUB(1.0f, alpha));
+        const float w = alpha * T;
+        float dL_dalpha = 0.0f;
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++) {
+          accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+          last_color[ch] = color[ch];
+          dL_dalpha += (color[ch] - accum_rec[ch]) * dL_dpixel[ch];
+          v[11 + ch] = w * dL_dpixel[ch];
+        }
+        float dL_dz = 0.0f;
+        const float m_d = far_ratio * (1.0f - NEAR_N / c_d);
+        const float dmd_dd = (FAR_N * NEAR_N) / ((FAR_N - NEAR_N) * c_d * c_d);
+        if (k == median_contributor - 1) dL_dz += dL_dmedian_depth;
+        const float dL_dweight = (final_D2 + m_d * m_d * final_A - 2.0f * m_d * final_D) * dL_dreg;
+        dL_dalpha += dL_dweight - last_dL_dT;
+        last_dL_dT = dL_dweight * alpha + (1.0f - alpha) * last_dL_dT;
+        const float dL_dmd = 2.0f * (T * alpha) * (m_d * final_A - final_D) * dL_dreg;
+        dL_dz += dL_dmd * dmd_dd;
+
+        accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
+        last_depth = c_d;
+        dL_dalpha += (c_d - accum_depth_rec) * dL_ddepth;
+        accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
+        dL_dalpha += (1.0f - accum_alpha_rec) * dL_daccum;
+        float dn[3];
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++) {
+          accum_normal_rec[ch] = last_alpha * last_normal[ch] + (1.f - last_alpha) * accum_normal_rec[ch];
+          last_normal[ch] = normal[ch];
+          dL_dalpha += (normal[ch] - accum_normal_rec[ch]) * dL_dnormal2D[ch];
+          dn[ch] = alpha * T * dL_dnormal2D[ch];
+        }
+        v[14] = dn[0]; v[15] = dn[1]; e0 = dn[2];
+
+        dL_dalpha *= T;
+        last_alpha = alpha;
+        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+
+        const float dL_dG = c.w * dL_dalpha;
+        dL_dz += alpha * T * dL_ddepth;
+
+        if (rho3d <= rho2d) {
+          const float dL_dsx = dL_dG * -G * sx + dL_dz * c.x;
+          const float dL_dsy = dL_dG * -G * sy + dL_dz * c.y;
+          const float dsx_pz = dL_dsx / ppz, dsy_pz = dL_dsy / ppz;
+          const float dpx = dsx_pz, dpy = dsy_pz, dpz = -(dsx_pz * sx + dsy_pz * sy);
+          // dL_dk = l x dL_dp ; dL_dl = dL_dp x k
+          const float dkx = ly * dpz - lz * dpy, dky = lz * dpx - lx * dpz, dkz = lx * dpy - ly * dpx;
+          const float dlx = dpy * kz - dpz * ky, dly = dpz * kx - dpx * kz, dlz = dpx * ky - dpy * kx;
+          v[0] = -dkx; v[1] = -dky; v[2] = -dkz;
+          v[3] = -dlx; v[4] = -dly; v[5] = -dlz;
+          v[6] = pxf * dkx + pyf * dlx + dL_dz * sx;
+          v[7] = pxf * dky + pyf * dly + dL_dz * sy;
+          v[8] = pxf * dkz + pyf * dlz + dL_dz;
+        } else {
+          const float dG_ddelx = -G * FILTER_INV_SQUARE * dx;
+          const float dG_ddely = -G * FILTER_INV_SQUARE * dy;
+          v[9] = dL_dG * dG_ddelx;
+          v[10] = dL_dG * dG_ddely;
+          v[6] = sx * dL_dz;
+          v[7] = sy * dL_dz;
+          v[8] = dL_dz;
+        }
+        e1 = G * dL_dalpha;
+      }
+
+      warp_reduce_scatter18(v, e0, e1, lane);
+      float* g = p.grad_records + (size_t)sm.id[s][j] * GREC;
+      if ((lane & 1) == 0) atomicAdd(g + (lane >> 1), v[0]);
+      else if (lane == 1) atomicAdd(g + 16, e0);
+      else if (lane == 17) atomicAdd(g + 17, e0);
+    }
+  }
+  __pipeline_wait_prior(0);
+}
+
+void launch_render_bwd(const BwdRenderParams& p, cudaStream_t stream) {
+  cudaFuncSetAttribute(render_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem));
+  dim3 grid(p.grid_x, p.grid_y, 1);
+  render_bwd_kernel<<<grid, TILE_PIX, sizeof(BwdSmem), stream>>>(p);
+}
+
+}  // namespace gsm

@@ -1,0 +1,314 @@
+"""Host-side mirror of the reference's `diff_surfel_rasterization` package
+(submodules/diff-surfel-rasterization/diff_surfel_rasterization/__init__.py:21-222) on top of the
+C ABI of libgaussmart_b200.so.
+
+Same names, argument order, return signature, validation messages and autograd contract as the
+reference, so gaussian_renderer/__init__.py:render() and scene/gaussian_model.py run unchanged:
+
+    GaussianRasterizationSettings(image_height, image_width, tanfovx, tanfovy, bg, scale_modifier,
+                                  viewmatrix, projmatrix, sh_degree, campos, prefiltered, debug)
+    GaussianRasterizer(raster_settings)(means3D, means2D, opacities, shs=None, colors_precomp=None,
+                                        scales=None, rotations=None, cov3D_precomp=None)
+        -> (color[3,H,W], radii[P] int32, allmap[7,H,W])
+
+PyTorch is used for device memory, streams and autograd plumbing only; every kernel is in the
+shared library.  There is no CPU path: CPU tensors raise, as in rasterize_points.cu:27-28.
+"""
+import ctypes
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+def cpu_deep_copy_tuple(input_tuple):
+    copied_tensors = [item.cpu().clone() if isinstance(item, torch.Tensor) else item for item in input_tuple]
+    return tuple(copied_tensors)
+
+
+def _ptr(t):
+    """Device pointer of a tensor, NULL for None / empty (the reference's empty tensors select the
+    in-kernel path through null pointers, dsr.py:198-208)."""
+    if t is None or t.numel() == 0:
+        return None
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def _check_cuda(name, t):
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+
+
+def _f32c(name, t):
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32, got {t.dtype}")
+    return t.contiguous()
+
+
+# grow-only high-water mark of (surfel,tile) instances per device: sizes the binning workspace so
+# that steady-state iterations never take the overflow/retry path.
+_binning_capacity = {}
+
+
+class _Workspaces(NamedTuple):
+    geometry: torch.Tensor
+    image: torch.Tensor
+    binning: torch.Tensor
+    capacity: int
+
+
+def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3Ds_precomp,
+                  viewmatrix, projmatrix, tanfovx, tanfovy, image_height, image_width, sh, sh_degree, campos,
+                  prefiltered, debug):
+    """Equivalent of RasterizeGaussiansCUDA (rasterize_points.cu:39-134)."""
+    lib = _lib.load()
+    if means3D.ndim != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    for name, t in (("background", bg), ("means3D", means3D), ("colors", colors_precomp), ("opacity", opacities),
+                    ("scales", scales), ("rotations", rotations), ("transMat_precomp", cov3Ds_precomp),
+                    ("viewmatrix", viewmatrix), ("projmatrix", projmatrix), ("sh", sh), ("campos", campos)):
+        _check_cuda(name, t)
+    P = means3D.shape[0]
+    H, W = int(image_height), int(image_width)
+    dev = means3D.device
+    bg = _f32c("background", bg)
+    means3D = _f32c("means3D", means3D)
+    colors_precomp = _f32c("colors", colors_precomp)
+    opacities = _f32c("opacity", opacities)
+    scales = _f32c("scales", scales)
+    rotations = _f32c("rotations", rotations)
+    cov3Ds_precomp = _f32c("transMat_precomp", cov3Ds_precomp)
+    viewmatrix = _f32c("viewmatrix", viewmatrix)
+    projmatrix = _f32c("projmatrix", projmatrix)
+    sh = _f32c("sh", sh)
+    campos = _f32c("campos", campos)
+    M = sh.shape[1] if sh.numel() != 0 else 0
+
+    with torch.cuda.device(dev):
+        out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+        out_others = torch.empty((7, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        geometry = torch.empty((lib.gsm_geometry_bytes(P),), dtype=torch.uint8, device=dev)
+        image = torch.empty((lib.gsm_image_bytes(W, H),), dtype=torch.uint8, device=dev)
+        stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        num_rendered = ctypes.c_int(0)
+
+        a = _lib.ForwardArgs()
+        a.P, a.D, a.M, a.width, a.height = P, int(sh_degree), M, W, H
+        a.tan_fovx, a.tan_fovy, a.scale_modifier = float(tanfovx), float(tanfovy), float(scale_modifier)
+        a.prefiltered, a.debug = int(bool(prefiltered)), int(bool(debug))
+        a.background, a.means3D, a.shs, a.colors_precomp = _ptr(bg), _ptr(means3D), _ptr(sh), _ptr(colors_precomp)
+        a.opacities, a.scales, a.rotations = _ptr(opacities), _ptr(scales), _ptr(rotations)
+        a.transMat_precomp = _ptr(cov3Ds_precomp)
+        a.viewmatrix, a.projmatrix, a.campos = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
+        a.out_color, a.out_others, a.radii = _ptr(out_color), _ptr(out_others), _ptr(radii)
+        a.geometry, a.geometry_bytes = _ptr(geometry), geometry.numel()
+        a.image, a.image_bytes = _ptr(image), image.numel()
+        a.num_rendered_host = ctypes.pointer(num_rendered)
+
+        key = (dev.index, )
+        capacity = _binning_capacity.get(key, 0)
+        while True:
+            binning = torch.empty((lib.gsm_binning_bytes(capacity, W, H),), dtype=torch.uint8, device=dev)
+            a.binning, a.binning_bytes, a.binning_capacity = _ptr(binning), binning.numel(), capacity
+            code = lib.gsm_forward(ctypes.byref(a), stream)
+            if code == _lib.GSM_ERR_BINNING_OVERFLOW:
+                capacity = int(num_rendered.value * 1.25) + 1024
+                _binning_capacity[key] = capacity
+                continue
+            _lib.check(code, "forward")
+            break
+    return num_rendered.value, out_color, out_others, radii, geometry, binning, image
+
+
+def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp, viewmatrix,
+                   projmatrix, tanfovx, tanfovy, grad_out_color, grad_depth, sh, sh_degree, campos, geomBuffer,
+                   num_rendered, binningBuffer, imgBuffer, debug):
+    """Equivalent of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:136-233)."""
+    lib = _lib.load()
+    P = means3D.shape[0]
+    H, W = grad_out_color.shape[1], grad_out_color.shape[2]
+    dev = means3D.device
+    M = sh.shape[1] if sh.numel() != 0 else 0
+    grad_out_color = _f32c("dL_dout_color", grad_out_color)
+    grad_depth = _f32c("dL_dout_others", grad_depth)
+    with torch.cuda.device(dev):
+        f32 = dict(dtype=torch.float32, device=dev)
+        dL_dmeans3D = torch.empty((P, 3), **f32)
+        dL_dmeans2D = torch.empty((P, 3), **f32)
+        dL_dcolors = torch.empty((P, 3), **f32)
+        dL_dnormal = None  # folded into the internal gradient record
+        dL_dopacity = torch.empty((P, 1), **f32)
+        dL_dtransMat = torch.empty((P, 9), **f32)
+        dL_dsh = torch.empty((P, M, 3), **f32)
+        dL_dscales = torch.empty((P, 2), **f32)
+        dL_drotations = torch.empty((P, 4), **f32)
+        if P != 0:
+            gws = torch.empty((lib.gsm_grad_workspace_bytes(P),), dtype=torch.uint8, device=dev)
+            a = _lib.BackwardArgs()
+            a.P, a.D, a.M, a.width, a.height = P, int(sh_degree), M, W, H
+            a.tan_fovx, a.tan_fovy, a.scale_modifier, a.debug = float(tanfovx), float(tanfovy), float(scale_modifier), int(bool(debug))
+            a.background, a.means3D, a.shs, a.colors_precomp = _ptr(bg), _ptr(means3D), _ptr(sh), _ptr(colors_precomp)
+            a.scales, a.rotations, a.transMat_precomp = _ptr(scales), _ptr(rotations), _ptr(cov3Ds_precomp)
+            a.viewmatrix, a.projmatrix, a.campos, a.radii = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), _ptr(radii)
+            a.geometry, a.image, a.binning = _ptr(geomBuffer), _ptr(imgBuffer), _ptr(binningBuffer)
+            a.dL_dout_color, a.dL_dout_others = _ptr(grad_out_color), _ptr(grad_depth)
+            a.grad_workspace, a.grad_workspace_bytes = _ptr(gws), gws.numel()
+            a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity = _ptr(dL_dmeans2D), _ptr(dL_dcolors), _ptr(dL_dopacity)
+            a.dL_dmeans3D, a.dL_dtransMat, a.dL_dsh = _ptr(dL_dmeans3D), _ptr(dL_dtransMat), _ptr(dL_dsh)
+            a.dL_dscales, a.dL_drotations = _ptr(dL_dscales), _ptr(dL_drotations)
+            stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            _lib.check(lib.gsm_backward(ctypes.byref(a), stream), "backward")
+    return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dtransMat, dL_dsh, dL_dscales, dL_drotations
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, raster_settings)
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings):
+        args = (raster_settings.bg, means3D, colors_precomp, opacities, scales, rotations,
+                raster_settings.scale_modifier, cov3Ds_precomp, raster_settings.viewmatrix,
+                raster_settings.projmatrix, raster_settings.tanfovx, raster_settings.tanfovy,
+                raster_settings.image_height, raster_settings.image_width, sh, raster_settings.sh_degree,
+                raster_settings.campos, raster_settings.prefiltered, raster_settings.debug)
+        if raster_settings.debug:
+            cpu_args = cpu_deep_copy_tuple(args)  # copy them before they can be corrupted
+            try:
+                num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer = _forward_impl(*args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_fw.dump")
+                print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
+                raise ex
+        else:
+            num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer = _forward_impl(*args)
+
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = num_rendered
+        ctx.opacity_shape = opacities.shape
+        # only the depth-sorted surfel list (first 4*R bytes) of the binning workspace is needed by
+        # backward; keep a compact copy so the transient sort scratch returns to the allocator now
+        point_list = binningBuffer[: 4 * num_rendered + 128].clone() if num_rendered > 0 else binningBuffer[:0]
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
+                              point_list, imgBuffer)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, depth
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_radii, grad_depth):
+        num_rendered = ctx.num_rendered
+        raster_settings = ctx.raster_settings
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer, binningBuffer,
+         imgBuffer) = ctx.saved_tensors
+        H, W = raster_settings.image_height, raster_settings.image_width
+        if grad_out_color is None:
+            grad_out_color = torch.zeros((3, H, W), dtype=torch.float32, device=means3D.device)
+        if grad_depth is None:
+            grad_depth = torch.zeros((7, H, W), dtype=torch.float32, device=means3D.device)
+        args = (raster_settings.bg, means3D, radii, colors_precomp, scales, rotations, raster_settings.scale_modifier,
+                cov3Ds_precomp, raster_settings.viewmatrix, raster_settings.projmatrix, raster_settings.tanfovx,
+                raster_settings.tanfovy, grad_out_color, grad_depth, sh, raster_settings.sh_degree,
+                raster_settings.campos, geomBuffer, num_rendered, binningBuffer, imgBuffer, raster_settings.debug)
+        if raster_settings.debug:
+            cpu_args = cpu_deep_copy_tuple(args)
+            try:
+                out = _backward_impl(*args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_bw.dump")
+                print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
+                raise ex
+        else:
+            out = _backward_impl(*args)
+        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
+         grad_rotations) = out
+        grads = (
+            grad_means3D,
+            grad_means2D,
+            grad_sh if sh.numel() != 0 else None,
+            grad_colors_precomp if colors_precomp.numel() != 0 else None,
+            grad_opacities.reshape(ctx.opacity_shape),
+            grad_scales if scales.numel() != 0 else None,
+            grad_rotations if rotations.numel() != 0 else None,
+            grad_cov3Ds_precomp if cov3Ds_precomp.numel() != 0 else None,
+            None,
+        )
+        return grads
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+
+
+def mark_visible(positions, viewmatrix, projmatrix):
+    """Equivalent of markVisible (rasterize_points.cu:235-254): bool[P], view-space z > 0.2."""
+    lib = _lib.load()
+    _check_cuda("means3D", positions)
+    P = positions.shape[0]
+    dev = positions.device
+    positions = _f32c("means3D", positions)
+    viewmatrix = _f32c("viewmatrix", viewmatrix)
+    projmatrix = _f32c("projmatrix", projmatrix)
+    present = torch.zeros((P,), dtype=torch.bool, device=dev)
+    if P != 0:
+        with torch.cuda.device(dev):
+            stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            _lib.check(lib.gsm_mark_visible(P, _ptr(positions), _ptr(viewmatrix), _ptr(projmatrix), _ptr(present),
+                                            stream), "mark_visible")
+    return present
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        # Mark visible points (based on frustum culling for camera) with a boolean
+        with torch.no_grad():
+            raster_settings = self.raster_settings
+            visible = mark_visible(positions, raster_settings.viewmatrix, raster_settings.projmatrix)
+        return visible
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        raster_settings = self.raster_settings
+
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+
+        dev = means3D.device
+        if shs is None:
+            shs = torch.empty(0, device=dev)
+        if colors_precomp is None:
+            colors_precomp = torch.empty(0, device=dev)
+        if scales is None:
+            scales = torch.empty(0, device=dev)
+        if rotations is None:
+            rotations = torch.empty(0, device=dev)
+        if cov3D_precomp is None:
+            cov3D_precomp = torch.empty(0, device=dev)
+
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                                   cov3D_precomp, raster_settings)

@@ -1,0 +1,151 @@
+/*
+ * gaussmart_b200 -- C ABI of the B200-native 2D Gaussian surfel rasterizer and kNN scale
+ * initialiser.  This is the drop-in boundary: exactly what the reference's pybind module
+ * (submodules/diff-surfel-rasterization/ext.cpp:15-19, submodules/simple-knn/ext.cpp:15-17)
+ * binds, restated with plain pointers and sizes.  No torch types cross this boundary.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - every entry point is asynchronous on `stream` (a cudaStream_t passed as void*) except
+ *     where noted; none of them allocates device memory -- the caller owns all buffers;
+ *   - return value: 0 on success, a cudaError_t (1..9999) on a CUDA failure, or a GSM_ERR_*
+ *     code; gsm_last_error() returns a human-readable description for the calling thread;
+ *   - nothing throws across the boundary.
+ */
+#ifndef GAUSSMART_B200_H
+#define GAUSSMART_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSM_ABI_VERSION 1
+
+#define GSM_OK 0
+#define GSM_ERR_INVALID_ARGUMENT 10001
+#define GSM_ERR_BINNING_OVERFLOW 10002 /* binning_capacity < num_rendered; *num_rendered_host is valid */
+#define GSM_ERR_WORKSPACE_TOO_SMALL 10003
+
+/* Bytes of one packed per-surfel record written by the forward preprocess and read by the
+ * compositing kernels (5 x float4: Tu|x, Tv|y, Tw|opacity, normal|depth, rgb|clamp-bits). */
+#define GSM_SURFEL_RECORD_BYTES 80
+/* Floats of one per-surfel gradient accumulation record written by the backward compositing
+ * kernel (dTu3 dTv3 dTw3 dmean2D2 dcolor3 dnormal3 dopacity1 = 18, padded to 20). */
+#define GSM_GRAD_RECORD_FLOATS 20
+
+const char* gsm_last_error(void);
+int gsm_abi_version(void);
+
+/* ---- workspace sizing (host-only arithmetic, no CUDA calls) ---------------------------- */
+
+/* geometry workspace (must survive until backward): records + tile counts/offsets + scan temp.
+ * Replaces GeometryState::fromChunk / required<GeometryState> (rasterizer_impl.cu:155-170). */
+size_t gsm_geometry_bytes(int P);
+/* image workspace (must survive until backward): final_T[3,H,W], n_contrib[2,H,W], ranges[Nt].
+ * Replaces ImageState::fromChunk (rasterizer_impl.cu:172-179). */
+size_t gsm_image_bytes(int width, int height);
+/* binning workspace for `capacity` (surfel,tile) instances; the first capacity*4 bytes are the
+ * depth-sorted surfel list (must survive until backward), the rest is transient.
+ * Replaces BinningState::fromChunk (rasterizer_impl.cu:181-194). */
+size_t gsm_binning_bytes(size_t capacity, int width, int height);
+/* byte offsets of the sorted keys (u64[R]) inside the binning workspace, for parity tests. */
+size_t gsm_binning_sorted_keys_offset(size_t capacity);
+/* byte offset of ranges (uint2[Nt]) / n_contrib (u32[2,H,W]) inside the image workspace. */
+size_t gsm_image_ranges_offset(int width, int height);
+size_t gsm_image_ncontrib_offset(int width, int height);
+
+/* ---- forward: replaces CudaRasterizer::Rasterizer::forward (rasterizer.h:33-58,
+ *      rasterizer_impl.cu:198-345) as called by RasterizeGaussiansCUDA (rasterize_points.cu:39-134)
+ */
+typedef struct gsm_forward_args {
+  int P;             /* surfels */
+  int D;             /* active SH degree 0..3 */
+  int M;             /* allocated SH coefficients per surfel (0 if shs == NULL) */
+  int width, height;
+  float tan_fovx, tan_fovy;
+  float scale_modifier;
+  int prefiltered;   /* kept for API parity; a culled surfel with prefiltered set is an error flag */
+  int debug;         /* synchronise + check after every stage */
+  const float* background;       /* [3] */
+  const float* means3D;          /* [P,3] */
+  const float* shs;              /* [P,M,3] or NULL */
+  const float* colors_precomp;   /* [P,3] or NULL */
+  const float* opacities;        /* [P] */
+  const float* scales;           /* [P,2] or NULL (then transMat_precomp) */
+  const float* rotations;        /* [P,4] (w,x,y,z) or NULL */
+  const float* transMat_precomp; /* [P,9] rows Tu,Tv,Tw or NULL */
+  const float* viewmatrix;       /* [16] row-major, row-vector convention */
+  const float* projmatrix;       /* [16] */
+  const float* campos;           /* [3] */
+  float* out_color;              /* [3,H,W] */
+  float* out_others;             /* [7,H,W]: depth, alpha, normal xyz, median depth, distortion */
+  int* radii;                    /* [P] */
+  void* geometry; size_t geometry_bytes;
+  void* image;    size_t image_bytes;
+  void* binning;  size_t binning_bytes; size_t binning_capacity;
+  int* num_rendered_host;        /* HOST pointer: receives R (valid on GSM_OK and on overflow) */
+} gsm_forward_args;
+
+/* Runs preprocess + scan, waits for R (one stream synchronisation, as rasterizer_impl.cu:282),
+ * then binning, sort, ranges and compositing.  On GSM_ERR_BINNING_OVERFLOW nothing after the scan
+ * has run; grow the binning workspace to *num_rendered_host and call again. */
+int gsm_forward(const gsm_forward_args* args, void* stream);
+
+/* ---- backward: replaces CudaRasterizer::Rasterizer::backward (rasterizer.h:60-87,
+ *      rasterizer_impl.cu:346-458) as called by RasterizeGaussiansBackwardCUDA
+ *      (rasterize_points.cu:136-233).  Every output is fully written (zeros for culled
+ *      surfels), so the caller may pass uninitialised memory. */
+typedef struct gsm_backward_args {
+  int P, D, M;
+  int width, height;
+  float tan_fovx, tan_fovy;
+  float scale_modifier;
+  int debug;
+  const float* background;
+  const float* means3D;
+  const float* shs;
+  const float* colors_precomp;
+  const float* scales;
+  const float* rotations;
+  const float* transMat_precomp;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  const int* radii;
+  const void* geometry;  /* as left by gsm_forward */
+  const void* image;
+  const void* binning;   /* only the sorted surfel list is read */
+  const float* dL_dout_color;  /* [3,H,W] */
+  const float* dL_dout_others; /* [7,H,W] */
+  void* grad_workspace; size_t grad_workspace_bytes; /* >= gsm_grad_workspace_bytes(P), transient */
+  float* dL_dmeans2D;   /* [P,3] */
+  float* dL_dcolors;    /* [P,3] */
+  float* dL_dopacity;   /* [P] */
+  float* dL_dmeans3D;   /* [P,3] */
+  float* dL_dtransMat;  /* [P,9] */
+  float* dL_dsh;        /* [P,M,3] (may be NULL when M == 0) */
+  float* dL_dscales;    /* [P,2] */
+  float* dL_drotations; /* [P,4] */
+} gsm_backward_args;
+
+size_t gsm_grad_workspace_bytes(int P);
+int gsm_backward(const gsm_backward_args* args, void* stream);
+
+/* ---- markVisible: replaces CudaRasterizer::Rasterizer::markVisible (rasterizer.h:24-31,
+ *      rasterizer_impl.cu:141-153; rasterize_points.cu:235-254).  present is uint8[P]. */
+int gsm_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, uint8_t* present, void* stream);
+
+/* ---- distCUDA2: replaces SimpleKNN::knn (simple_knn.h:18, simple_knn.cu:186-222) as called by
+ *      distCUDA2 (spatial.cu:15-26): mean squared distance to the 3 nearest other points. */
+size_t gsm_knn_workspace_bytes(int P);
+int gsm_knn_dist2(int P, const float* points /*[P,3]*/, float* mean_dist2 /*[P]*/,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GAUSSMART_B200_H */

@@ -30,11 +30,11 @@ __device__ __forceinline__ float3 sh_to_rgb(int D, const float4* __restrict__ sh
   if (D > 0) {
     const float x = dir.x, y = dir.y, z = dir.z;
     float t = MUL(y, C1);
-    r.x = SUB(r.x, MUL(t, __ldg(sh + 3))); r.y = SUB(r.y, MUL(t, __ldg(sh + 4))); r.z = SUB(r.z, MUL(t, __ldg(sh + 5)));
+    r.x = FMA(-t, __ldg(sh + 3), r.x); r.y = FMA(-t, __ldg(sh + 4), r.y); r.z = FMA(-t, __ldg(sh + 5), r.z);
     t = MUL(z, C1);
     r.x = FMA(t, __ldg(sh + 6), r.x); r.y = FMA(t, __ldg(sh + 7), r.y); r.z = FMA(t, __ldg(sh + 8), r.z);
     t = MUL(x, C1);
-    r.x = SUB(r.x, MUL(t, __ldg(sh + 9))); r.y = SUB(r.y, MUL(t, __ldg(sh + 10))); r.z = SUB(r.z, MUL(t, __ldg(sh + 11)));
+    r.x = FMA(-t, __ldg(sh + 9), r.x); r.y = FMA(-t, __ldg(sh + 10), r.y); r.z = FMA(-t, __ldg(sh + 11), r.z);
     if (D > 1) {
       const float xx = MUL(x, x), yy = MUL(y, y), zz = MUL(z, z);
       const float xy = MUL(x, y), yz = MUL(y, z), xz = MUL(x, z);
@@ -56,21 +56,20 @@ __device__ __forceinline__ float3 sh_to_rgb(int D, const float4* __restrict__ sh
         const float C30 = -0.5900435899266435f, C31 = 2.890611442640554f, C32 = -0.4570457994644658f,
                     C33 = 0.3731763325901154f, C34 = -0.4570457994644658f, C35 = 1.445305721320277f,
                     C36 = -0.5900435899266435f;
-        const float xx3 = MUL(xx, 3.0f), yy3 = MUL(yy, 3.0f);
-        const float zz4_xx_yy = SUB(SUB(MUL(zz, 4.0f), xx), yy);
-        t = MUL(MUL(y, C30), SUB(xx3, yy));
+                const float zz4_xx_yy = SUB(FMA(zz, 4.0f, -xx), yy);
+        t = MUL(MUL(y, C30), FMA(xx, 3.0f, -yy));
         r.x = FMA(t, __ldg(sh + 27), r.x); r.y = FMA(t, __ldg(sh + 28), r.y); r.z = FMA(t, __ldg(sh + 29), r.z);
         t = MUL(z, MUL(xy, C31));
         r.x = FMA(t, __ldg(sh + 30), r.x); r.y = FMA(t, __ldg(sh + 31), r.y); r.z = FMA(t, __ldg(sh + 32), r.z);
         t = MUL(MUL(y, C32), zz4_xx_yy);
         r.x = FMA(t, __ldg(sh + 33), r.x); r.y = FMA(t, __ldg(sh + 34), r.y); r.z = FMA(t, __ldg(sh + 35), r.z);
-        t = MUL(MUL(z, C33), SUB(SUB(zz2, xx3), yy3));
+        t = MUL(MUL(z, C33), FMA(yy, -3.0f, FMA(xx, -3.0f, zz2)));
         r.x = FMA(t, __ldg(sh + 36), r.x); r.y = FMA(t, __ldg(sh + 37), r.y); r.z = FMA(t, __ldg(sh + 38), r.z);
         t = MUL(MUL(x, C34), zz4_xx_yy);
         r.x = FMA(t, __ldg(sh + 39), r.x); r.y = FMA(t, __ldg(sh + 40), r.y); r.z = FMA(t, __ldg(sh + 41), r.z);
         t = MUL(MUL(z, C35), xx_yy);
         r.x = FMA(t, __ldg(sh + 42), r.x); r.y = FMA(t, __ldg(sh + 43), r.y); r.z = FMA(t, __ldg(sh + 44), r.z);
-        t = MUL(MUL(x, C36), SUB(xx, yy3));
+        t = MUL(MUL(x, C36), FMA(yy, -3.0f, xx));
         r.x = FMA(t, __ldg(sh + 45), r.x); r.y = FMA(t, __ldg(sh + 46), r.y); r.z = FMA(t, __ldg(sh + 47), r.z);
       }
     }
@@ -89,9 +88,10 @@ __device__ __forceinline__ void build_L(float4 q, float sx, float sy, float3& L0
   const float s = rsqrtf(n2);
   const float w = MUL(q.x, s), x = MUL(q.y, s), y = MUL(q.z, s), z = MUL(q.w, s);
   const float yy = MUL(y, y), zz = MUL(z, z);
-  const float xy = MUL(x, y), wz = MUL(w, z), xz = MUL(x, z), wy = MUL(w, y), yz = MUL(y, z), wx = MUL(w, x);
+  const float wz = MUL(w, z), wy = MUL(w, y), wx = MUL(w, x);
   const float xx_zz = FMA(x, x, zz), xx_yy = FMA(x, x, yy), yy_zz = ADD(yy, zz);
-  const float a = ADD(xy, wz), b = SUB(xy, wz), c = SUB(xz, wy), d = ADD(xz, wy), e = ADD(yz, wx), f = SUB(yz, wx);
+  // ptxas fuses the products of the off-diagonal terms into the add/sub (reference SASS)
+  const float a = FMA(x, y, wz), b = FMA(x, y, -wz), c = FMA(x, z, -wy), d = FMA(x, z, wy), e = FMA(y, z, wx), f = FMA(y, z, -wx);
   const float R00 = SUB(1.0f, ADD(yy_zz, yy_zz)), R01 = ADD(a, a), R02 = ADD(c, c);
   const float R10 = ADD(b, b), R11 = SUB(1.0f, ADD(xx_zz, xx_zz)), R12 = ADD(e, e);
   const float R20 = ADD(d, d), R21 = ADD(f, f), R22 = SUB(1.0f, ADD(xx_yy, xx_yy));
@@ -170,14 +170,14 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const FwdPreprocess
     nx = MUL(nx, mult); ny = MUL(ny, mult); nz = MUL(nz, mult);
 
     // AABB (forward.cu:119-145), cutoff 3 -> t = (9, 9, -1)
-    const float d = SUB(FMA(MUL(Tw0, Tw0), 9.0f, MUL(MUL(Tw1, Tw1), 9.0f)), MUL(Tw2, Tw2));
+    const float d = FMA(-Tw2, Tw2, FMA(MUL(Tw0, Tw0), 9.0f, MUL(MUL(Tw1, Tw1), 9.0f)));
     if (d == 0.0f) break;
     const float inv = __frcp_rn(d);
     const float f9 = MUL(inv, 9.0f);
-    const float cx = SUB(FMA(f9, MUL(Tu0, Tw0), MUL(f9, MUL(Tu1, Tw1))), MUL(inv, MUL(Tu2, Tw2)));
-    const float cy = SUB(FMA(f9, MUL(Tv0, Tw0), MUL(f9, MUL(Tv1, Tw1))), MUL(inv, MUL(Tv2, Tw2)));
-    const float su = SUB(MUL(inv, MUL(Tu2, Tu2)), FMA(f9, MUL(Tu0, Tu0), MUL(f9, MUL(Tu1, Tu1))));
-    const float sv = SUB(MUL(inv, MUL(Tv2, Tv2)), FMA(f9, MUL(Tv0, Tv0), MUL(f9, MUL(Tv1, Tv1))));
+    const float cx = FMA(MUL(Tw2, Tu2), -inv, FMA(f9, MUL(Tu0, Tw0), MUL(f9, MUL(Tu1, Tw1))));
+    const float cy = FMA(MUL(Tw2, Tv2), -inv, FMA(f9, MUL(Tv0, Tw0), MUL(f9, MUL(Tv1, Tw1))));
+    const float su = FMA(MUL(Tu2, Tu2), inv, -FMA(f9, MUL(Tu0, Tu0), MUL(f9, MUL(Tu1, Tu1))));
+    const float sv = FMA(MUL(Tv2, Tv2), inv, -FMA(f9, MUL(Tv0, Tv0), MUL(f9, MUL(Tv1, Tv1))));
     const float hx = __fsqrt_rn(fmaxf(FMA(cx, cx, su), 1e-4f));
     const float hy = __fsqrt_rn(fmaxf(FMA(cy, cy, sv), 1e-4f));
     const float radius = ceilf(fmaxf(fmaxf(hx, hy), __uint_as_float(GSM_MIN_RADIUS_BITS)));

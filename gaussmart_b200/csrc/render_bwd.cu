@@ -160,11 +160,11 @@ __global__ void __launch_bounds__(TILE_PIX, 2) render_bwd_kernel(const BwdRender
       const int k = base_pos - j;  // == the reference's `contributor` after its decrement
       bool active = k < last_contributor;
       const float4 a = sm.q[s][0][j], b = sm.q[s][1][j], c = sm.q[s][2][j];
-      const float kx = SUB(MUL(c.x, pxf), a.x), ky = SUB(MUL(c.y, pxf), a.y), kz = SUB(MUL(c.z, pxf), a.z);
-      const float lx = SUB(MUL(c.x, pyf), b.x), ly = SUB(MUL(c.y, pyf), b.y), lz = SUB(MUL(c.z, pyf), b.z);
-      const float ppx = SUB(MUL(ky, lz), MUL(ly, kz));
-      const float ppy = SUB(MUL(lx, kz), MUL(kx, lz));
-      const float ppz = SUB(MUL(kx, ly), MUL(lx, ky));
+      const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
+      const float lx = FMA(pyf, c.x, -b.x), ly = FMA(pyf, c.y, -b.y), lz = FMA(pyf, c.z, -b.z);
+      const float ppx = FMA(ky, lz, -MUL(kz, ly));
+      const float ppy = FMA(kz, lx, -MUL(kx, lz));
+      const float ppz = FMA(kx, ly, -MUL(ky, lx));
       active = active && (ppz != 0.0f);
       const float sx = __fdiv_rn(ppx, ppz), sy = __fdiv_rn(ppy, ppz);
       const float rho3d = FMA(sx, sx, MUL(sy, sy));

@@ -84,12 +84,13 @@ __global__ void __launch_bounds__(TILE_PIX) render_fwd_kernel(const FwdRenderPar
       for (int j = 0; !done && j < n; j++) {
         contributor++;
         const float4 a = q0[j], b = q1[j], c = q2[j];
-        // k = px*Tw - Tu ; l = py*Tw - Tv ; p = k x l   (forward.cu:355-358)
-        const float kx = SUB(MUL(c.x, pxf), a.x), ky = SUB(MUL(c.y, pxf), a.y), kz = SUB(MUL(c.z, pxf), a.z);
-        const float lx = SUB(MUL(c.x, pyf), b.x), ly = SUB(MUL(c.y, pyf), b.y), lz = SUB(MUL(c.z, pyf), b.z);
-        const float ppx = SUB(MUL(ky, lz), MUL(ly, kz));
-        const float ppy = SUB(MUL(lx, kz), MUL(kx, lz));
-        const float ppz = SUB(MUL(kx, ly), MUL(lx, ky));
+        // k = px*Tw - Tu ; l = py*Tw - Tv ; p = k x l   (forward.cu:355-358), fused as the
+        // reference's SASS fuses them (ptxas contracts the un-suffixed PTX mul/sub pairs)
+        const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
+        const float lx = FMA(pyf, c.x, -b.x), ly = FMA(pyf, c.y, -b.y), lz = FMA(pyf, c.z, -b.z);
+        const float ppx = FMA(ky, lz, -MUL(kz, ly));
+        const float ppy = FMA(kz, lx, -MUL(kx, lz));
+        const float ppz = FMA(kx, ly, -MUL(ky, lx));
         if (ppz == 0.0f) continue;
         const float sx = __fdiv_rn(ppx, ppz), sy = __fdiv_rn(ppy, ppz);
         const float rho3d = FMA(sx, sx, MUL(sy, sy));
@@ -110,7 +111,7 @@ __global__ void __launch_bounds__(TILE_PIX) render_fwd_kernel(const FwdRenderPar
         const float A = SUB(1.0f, T);
         const float m = MUL(ADD(__fdiv_rn(-NEAR_N, depth), 1.0f), far_ratio);
         const float mm = MUL(m, m);
-        distortion = FMA(SUB(FMA(A, mm, M2), MUL(M1, ADD(m, m))), w, distortion);
+        distortion = FMA(w, FMA(-M1, ADD(m, m), FMA(A, mm, M2)), distortion);
         D = FMA(depth, w, D);
         M1 = FMA(m, w, M1);
         M2 = FMA(mm, w, M2);

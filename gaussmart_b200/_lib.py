@@ -23,6 +23,7 @@ EXPORTS = [
     "gsm_binning_sorted_keys_offset", "gsm_image_ranges_offset", "gsm_image_ncontrib_offset",
     "gsm_forward", "gsm_grad_workspace_bytes", "gsm_backward", "gsm_mark_visible",
     "gsm_knn_workspace_bytes", "gsm_knn_dist2",
+    "gsm_stage_count", "gsm_stage_name", "gsm_stage_timing_enable", "gsm_stage_timing_read",
 ]
 
 
@@ -97,10 +98,31 @@ def load():
     lib.gsm_mark_visible.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
     lib.gsm_knn_dist2.restype = c_int
     lib.gsm_knn_dist2.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
+    lib.gsm_stage_count.restype = c_int
+    lib.gsm_stage_name.restype = c_char_p
+    lib.gsm_stage_name.argtypes = [c_int]
+    lib.gsm_stage_timing_enable.restype = c_int
+    lib.gsm_stage_timing_enable.argtypes = [c_int]
+    lib.gsm_stage_timing_read.restype = c_int
+    lib.gsm_stage_timing_read.argtypes = [POINTER(ctypes.c_double), POINTER(ctypes.c_longlong), c_int]
     if lib.gsm_abi_version() != ABI_VERSION:
         raise ImportError(f"gaussmart_b200: ABI version mismatch ({lib.gsm_abi_version()} != {ABI_VERSION})")
     _lib = lib
     return lib
+
+
+def stage_timing_enable(on=True):
+    return bool(load().gsm_stage_timing_enable(1 if on else 0))
+
+
+def stage_timing_read(reset=True):
+    """{stage name: (summed device ms, launches)} for every stage timed since the last reset."""
+    lib = load()
+    n = lib.gsm_stage_count()
+    ms = (ctypes.c_double * n)()
+    calls = (ctypes.c_longlong * n)()
+    check(lib.gsm_stage_timing_read(ms, calls, 1 if reset else 0), "stage_timing_read")
+    return {lib.gsm_stage_name(i).decode(): (ms[i], calls[i]) for i in range(n)}
 
 
 def last_error():

@@ -5,6 +5,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 namespace gsm {
 
@@ -20,6 +22,58 @@ void set_error(const char* fmt, ...) {
 int cuda_fail(cudaError_t e, const char* what) {
   set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
   return (int)e;
+}
+
+// ---- optional per-stage device timing (gsm_stage_timing_*): cudaEvent pairs recorded on the
+// launching stream around every stage, resolved lazily when read.  Off by default.
+static const char* const kStageNames[GSM_NUM_STAGES] = {
+    "preprocess_fwd", "scan", "duplicate", "sort", "ranges", "render_fwd",
+    "grad_zero", "render_bwd", "preprocess_bwd", "knn"};
+
+struct StageTimer {
+  std::mutex mu;
+  bool on = false;
+  struct Pending { int stage; cudaEvent_t a, b; };
+  std::vector<cudaEvent_t> pool;
+  std::vector<Pending> pending;
+  double sum_ms[GSM_NUM_STAGES] = {};
+  long long calls[GSM_NUM_STAGES] = {};
+  cudaEvent_t get() {
+    if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+  }
+  void resolve() {
+    for (auto& p : pending) {
+      float ms = 0.f;
+      if (cudaEventSynchronize(p.b) == cudaSuccess && cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+        sum_ms[p.stage] += ms;
+        calls[p.stage]++;
+      }
+      pool.push_back(p.a);
+      pool.push_back(p.b);
+    }
+    pending.clear();
+  }
+};
+static StageTimer g_timer;
+
+StageMark::StageMark(int stage, cudaStream_t stream) : stage_(stage), stream_(stream), a_(nullptr) {
+  if (!g_timer.on) return;
+  std::lock_guard<std::mutex> lk(g_timer.mu);
+  a_ = g_timer.get();
+  if (a_) cudaEventRecord(a_, stream_);
+}
+StageMark::~StageMark() {
+  if (!a_) return;
+  std::lock_guard<std::mutex> lk(g_timer.mu);
+  cudaEvent_t b = g_timer.get();
+  if (b) {
+    cudaEventRecord(b, stream_);
+    g_timer.pending.push_back({stage_, a_, b});
+    if (g_timer.pending.size() > 8192) g_timer.resolve();
+  }
 }
 
 GeometryLayout geometry_layout(int P) {
@@ -78,6 +132,24 @@ using namespace gsm;
 
 extern "C" const char* gsm_last_error(void) { return g_error; }
 extern "C" int gsm_abi_version(void) { return GSM_ABI_VERSION; }
+extern "C" int gsm_stage_count(void) { return GSM_NUM_STAGES; }
+extern "C" const char* gsm_stage_name(int i) { return (i >= 0 && i < GSM_NUM_STAGES) ? kStageNames[i] : ""; }
+extern "C" int gsm_stage_timing_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_timer.mu);
+  const int was = g_timer.on ? 1 : 0;
+  g_timer.on = on != 0;
+  return was;
+}
+extern "C" int gsm_stage_timing_read(double* sum_ms, long long* calls, int reset) {
+  std::lock_guard<std::mutex> lk(g_timer.mu);
+  g_timer.resolve();
+  for (int i = 0; i < GSM_NUM_STAGES; i++) {
+    if (sum_ms) sum_ms[i] = g_timer.sum_ms[i];
+    if (calls) calls[i] = g_timer.calls[i];
+    if (reset) { g_timer.sum_ms[i] = 0.0; g_timer.calls[i] = 0; }
+  }
+  return GSM_OK;
+}
 extern "C" size_t gsm_geometry_bytes(int P) { return geometry_layout(P).total; }
 extern "C" size_t gsm_image_bytes(int width, int height) { return image_layout(width, height).total; }
 extern "C" size_t gsm_binning_bytes(size_t capacity, int width, int height) {
@@ -138,9 +210,12 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     pp.shs = a->shs; pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;
     pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
     pp.radii = a->radii; pp.records = records; pp.tiles_touched = tiles_touched; pp.flags = flags;
-    launch_preprocess_fwd(pp, stream);
+    { StageMark m(GSM_STAGE_PREPROCESS_FWD, stream); launch_preprocess_fwd(pp, stream); }
     GSM_STAGE("forward preprocess");
-    GSM_CUDA(launch_inclusive_scan(tiles_touched, offsets, P, geom + G.scan_temp, G.scan_temp_bytes, stream));
+    {
+      StageMark m(GSM_STAGE_SCAN, stream);
+      GSM_CUDA(launch_inclusive_scan(tiles_touched, offsets, P, geom + G.scan_temp, G.scan_temp_bytes, stream));
+    }
     GSM_STAGE("tile-count scan");
     // S1: the one host<-device dependency of the forward (rasterizer_impl.cu:282)
     uint32_t host_vals[2] = {0, 0};
@@ -170,13 +245,19 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     uint64_t* keys_sorted = (uint64_t*)(bin + B.keys_sorted);
     uint32_t* values_unsorted = (uint32_t*)(bin + B.values_unsorted);
     uint32_t* point_list = (uint32_t*)(bin + B.point_list);
-    launch_duplicate_with_keys(P, records, offsets, a->radii, keys_unsorted, values_unsorted, grid_x, grid_y, stream);
+    {
+      StageMark m(GSM_STAGE_DUPLICATE, stream);
+      launch_duplicate_with_keys(P, records, offsets, a->radii, keys_unsorted, values_unsorted, grid_x, grid_y, stream);
+    }
     GSM_STAGE("duplicate with keys");
     const int end_bit = 32 + higher_msb((uint32_t)num_tiles);
-    GSM_CUDA(launch_sort_pairs(keys_unsorted, keys_sorted, values_unsorted, point_list, (size_t)R, end_bit,
-                               bin + B.sort_temp, B.sort_temp_bytes, stream));
+    {
+      StageMark m(GSM_STAGE_SORT, stream);
+      GSM_CUDA(launch_sort_pairs(keys_unsorted, keys_sorted, values_unsorted, point_list, (size_t)R, end_bit,
+                                 bin + B.sort_temp, B.sort_temp_bytes, stream));
+    }
     GSM_STAGE("sort");
-    launch_tile_ranges((size_t)R, keys_sorted, ranges, num_tiles, stream);
+    { StageMark m(GSM_STAGE_RANGES, stream); launch_tile_ranges((size_t)R, keys_sorted, ranges, num_tiles, stream); }
     GSM_STAGE("tile ranges");
   } else {
     GSM_CUDA(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream));
@@ -189,7 +270,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     rp.records = records; rp.background = a->background;
     rp.final_T = (float*)(img + I.final_T); rp.n_contrib = (uint32_t*)(img + I.n_contrib);
     rp.out_color = a->out_color; rp.out_others = a->out_others;
-    launch_render_fwd(rp, stream);
+    { StageMark m(GSM_STAGE_RENDER_FWD, stream); launch_render_fwd(rp, stream); }
     GSM_STAGE("forward render");
   } else {
     GSM_CUDA(cudaMemsetAsync(a->out_color, 0, sizeof(float) * 3 * (size_t)W * H, stream));
@@ -215,7 +296,10 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   const char* img = aligned_base(a->image);
   const char* bin = a->binning ? aligned_base(a->binning) : nullptr;
   float* grad_records = (float*)aligned_base(a->grad_workspace);
-  GSM_CUDA(cudaMemsetAsync(grad_records, 0, (size_t)P * GSM_GRAD_RECORD_FLOATS * 4, stream));
+  {
+    StageMark m(GSM_STAGE_GRAD_ZERO, stream);
+    GSM_CUDA(cudaMemsetAsync(grad_records, 0, (size_t)P * GSM_GRAD_RECORD_FLOATS * 4, stream));
+  }
 
   BwdRenderParams rp{};
   rp.W = W; rp.H = H; rp.grid_x = grid_x; rp.grid_y = grid_y;
@@ -227,7 +311,7 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   rp.n_contrib = (const uint32_t*)(img + I.n_contrib);
   rp.dL_dpix = a->dL_dout_color; rp.dL_dothers = a->dL_dout_others;
   rp.grad_records = grad_records;
-  launch_render_bwd(rp, stream);
+  { StageMark m(GSM_STAGE_RENDER_BWD, stream); launch_render_bwd(rp, stream); }
   GSM_STAGE("backward render");
 
   // W,H re-derived in fp32 exactly as backward.cu:613-614 with focal from rasterizer_impl.cu:387-388
@@ -245,7 +329,7 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   pp.dL_dmeans2D = a->dL_dmeans2D; pp.dL_dcolors = a->dL_dcolors; pp.dL_dopacity = a->dL_dopacity;
   pp.dL_dmeans3D = a->dL_dmeans3D; pp.dL_dtransMat = a->dL_dtransMat; pp.dL_dsh = a->dL_dsh;
   pp.dL_dscales = a->dL_dscales; pp.dL_drotations = a->dL_drotations;
-  launch_preprocess_bwd(pp, stream);
+  { StageMark m(GSM_STAGE_PREPROCESS_BWD, stream); launch_preprocess_bwd(pp, stream); }
   GSM_STAGE("backward preprocess");
   return GSM_OK;
 }

@@ -90,6 +90,21 @@ int cuda_fail(cudaError_t e, const char* what);
     if (_e != cudaSuccess) return gsm::cuda_fail(_e, stage_name);               \
   } while (0)
 
+// ---- optional per-stage timing (api.cu) --------------------------------------------------
+enum {
+  GSM_STAGE_PREPROCESS_FWD = 0, GSM_STAGE_SCAN, GSM_STAGE_DUPLICATE, GSM_STAGE_SORT, GSM_STAGE_RANGES,
+  GSM_STAGE_RENDER_FWD, GSM_STAGE_GRAD_ZERO, GSM_STAGE_RENDER_BWD, GSM_STAGE_PREPROCESS_BWD, GSM_STAGE_KNN
+};
+class StageMark {  // RAII: records a cudaEvent pair around a stage when timing is enabled
+ public:
+  StageMark(int stage, cudaStream_t stream);
+  ~StageMark();
+ private:
+  int stage_;
+  cudaStream_t stream_;
+  cudaEvent_t a_;
+};
+
 // ---- stage launchers (one translation unit each) ----------------------------------------
 struct FwdPreprocessParams {
   int P, D, M, W, H;

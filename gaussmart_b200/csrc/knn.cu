@@ -246,6 +246,7 @@ extern "C" int gsm_knn_dist2(int P, const float* points, float* mean_dist2, void
   float4* pts = (float4*)(ws + L.pts);
   float4* boxes = (float4*)(ws + L.boxes);
 
+  StageMark mark(GSM_STAGE_KNN, stream);
   knn_init_minmax<<<1, 32, 0, stream>>>(mm);
   const int nb = (P + 255) / 256;
   knn_minmax_kernel<<<min(nb, 148 * 8), 256, 0, stream>>>(P, points, mm);

@@ -39,6 +39,17 @@ extern "C" {
 const char* gsm_last_error(void);
 int gsm_abi_version(void);
 
+/* ---- optional per-stage device timing (bench / profiling aid; off by default) -----------
+ * When enabled, every stage of gsm_forward / gsm_backward / gsm_knn_dist2 is bracketed by a
+ * cudaEvent pair on the launching stream.  gsm_stage_timing_read synchronises the outstanding
+ * events and returns, per stage, the summed device milliseconds and the number of launches.
+ * The reference has no equivalent (its only hook is debug's sync-after-stage, auxiliary.h:296-303). */
+#define GSM_NUM_STAGES 10
+int gsm_stage_count(void);
+const char* gsm_stage_name(int stage);
+int gsm_stage_timing_enable(int on); /* returns the previous setting */
+int gsm_stage_timing_read(double* sum_ms /*[GSM_NUM_STAGES]*/, long long* calls /*[GSM_NUM_STAGES]*/, int reset);
+
 /* ---- workspace sizing (host-only arithmetic, no CUDA calls) ---------------------------- */
 
 /* geometry workspace (must survive until backward): records + tile counts/offsets + scan temp.

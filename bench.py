@@ -1,0 +1,506 @@
+#!/usr/bin/env python
+"""bench.py -- 2DGS surfel rasterizer fwd+bwd view-iterations/s on the Mip-NeRF-360-bicycle-shaped
+synthetic scene (BASELINE.json config C4: 5 M surfels, 1237x822, SH degree 3).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+A "step" is one forward + backward pass of the hot path over one camera per GPU (view-parallel, weak
+scaling: every rank rasterises its own view of the replicated surfel set, then the per-surfel
+gradients are sum-all-reduced over NCCL).  Prints ONE JSON line on rank 0.
+
+  value     device-resident throughput (inputs in HBM when the clock starts), CUDA events, max over ranks
+  e2e       same metric through the public GaussianRasterizer API with HOST buffers: per step the
+            camera matrices and the ground-truth image are copied from pinned host memory, the loss
+            is read back (train.py:104-152 shape)
+  roofline  dominant kernel, timed live with cudaEvent pairs on the launching stream (gsm_stage_timing_*)
+  cpu_baseline  the CPU oracle (oracle/surfel_oracle.py) on a bounded sample, rank 0 at N=1 only
+
+--impl reference times the UNMODIFIED reference on the same workload: its CUDA build (oracle/_ref,
+the reference has no CPU implementation of this path) when present, else the CPU oracle port.
+Nothing here reads /root/reference at run time.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+METRIC = "2dgs_fwd_bwd_view_iterations_per_sec"
+UNIT = "iter/s"
+N_VIEWS = 8           # cameras on a circle (C5: 8 views/step); rank r, step s uses view (s*N + r) % 8
+WORKLOAD = "C4"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--P", type=int, default=None, help="override the surfel count (debug only; flagged in config)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks: sample nvidia-smi during the timed region
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=f,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        try:
+            self.proc.terminate()
+            self.proc.wait(timeout=5)
+        except Exception:
+            pass
+        try:
+            rows = [r.strip().split(",") for r in open(self.path) if r.strip()]
+            os.unlink(self.path)
+        except Exception:
+            return out
+        sm, reasons, mx, pw = [], set(), None, []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+                pw.append(float(r[2]))
+                for n, v in zip(names, r[3:7]):
+                    if v.strip().lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm),
+                       power_w_max=max(pw) if pw else None)
+        return out
+
+
+# ------------------------------------------------------------------------------------------------
+# workload
+# ------------------------------------------------------------------------------------------------
+def make_workload(args, device):
+    from gaussmart_b200 import synthetic
+    P_cfg, W, H, deg, _ = synthetic.CONFIGS[args.workload]
+    P = P_cfg if args.P is None else args.P
+    idx = list(synthetic.CONFIGS).index(args.workload) + 1
+    scene = synthetic.make_scene(P, W, deg, synthetic.BASE_SEED + idx)   # same seed on every rank: replicas
+    cams = synthetic.make_cameras(W, H, N_VIEWS)
+    params = dict(means3D=scene.means3D.to(device), shs=scene.shs.to(device), opacities=scene.opacities.to(device),
+                  scales=scene.scales.to(device), rotations=scene.rotations.to(device))
+    cams_d = [synthetic.Camera(*[x.to(device) if isinstance(x, torch.Tensor) else x for x in c]) for c in cams]
+    g = torch.Generator(device="cpu").manual_seed(4711)
+    gt_host = [torch.rand(3, H, W, generator=g).pin_memory() for _ in range(2)]
+    cot = synthetic.make_cotangents(W, H, 777)
+    cot_d = (cot[0].to(device), cot[1].to(device))
+    return dict(P=P, W=W, H=H, deg=deg, scene=scene, cams=cams, cams_d=cams_d, params=params, gt_host=gt_host,
+                cot=cot, cot_d=cot_d)
+
+
+def loss_fn(color, allmap, gt):
+    """L1 photometric term + small terms on every allmap channel so that every backward branch is live
+    (train.py:113-143 shape: L1, normal and distortion regularisers)."""
+    return ((color - gt).abs().mean() + 0.05 * allmap[2:5].abs().mean() + 100.0 * allmap[6].mean() +
+            0.01 * (allmap[0].mean() + allmap[1].mean() + allmap[5].mean()))
+
+
+class OursArm:
+    """gaussmart_b200: bucket path for `value` (K6 writes the flat gradient bucket, NCCL all-reduce at N>1),
+    public autograd API for `e2e`."""
+    name = "ours"
+
+    def __init__(self, wl, device, world):
+        import gaussmart_b200 as gb
+        from gaussmart_b200 import view_parallel as vp
+        self.gb, self.vp, self.wl, self.device, self.world = gb, vp, wl, device, world
+        M = wl["params"]["shs"].shape[1]
+        self.bucket = vp.GradBucket(wl["P"], M, device, with_stats=True)
+        self.bg = torch.zeros(3, device=device)
+        self.leaves = {k: v.clone().requires_grad_(True) for k, v in wl["params"].items()}
+        self.means2D = torch.zeros_like(self.leaves["means3D"], requires_grad=True)
+
+    def value_step(self, view):
+        wl = self.wl
+        from gaussmart_b200.rasterizer import rasterize_into_bucket
+        color, radii, allmap, backward = rasterize_into_bucket(wl["params"], wl["cams_d"][view], self.bucket, False,
+                                                               bg=self.bg)
+        d2 = backward(wl["cot_d"][0], wl["cot_d"][1])
+        if self.world > 1:
+            self.bucket.stats.zero_()
+            self.bucket.max_radii.zero_()
+            self.vp.add_densification_stats(self.bucket, d2, radii)
+            self.vp.allreduce_bucket(self.bucket)
+
+    def api_step(self, cam_d, gt):
+        """Public API: GaussianRasterizationSettings / GaussianRasterizer + autograd (gr.py:37-97 shape)."""
+        from gaussmart_b200 import synthetic
+        gb = self.gb
+        S = gb.GaussianRasterizationSettings(**synthetic.settings_kwargs(cam_d, self.wl["deg"], self.bg))
+        for v in self.leaves.values():
+            v.grad = None
+        self.means2D.grad = None
+        L = self.leaves
+        color, radii, allmap = gb.GaussianRasterizer(S)(
+            means3D=L["means3D"], means2D=self.means2D, opacities=L["opacities"], shs=L["shs"], scales=L["scales"],
+            rotations=L["rotations"])
+        loss = loss_fn(color, allmap, gt)
+        loss.backward()
+        if self.world > 1:
+            flat = torch.cat([L[k].grad.reshape(-1) for k in ("means3D", "shs", "opacities", "scales", "rotations")])
+            dist.all_reduce(flat)
+        return loss
+
+
+class ReferenceArm:
+    """The UNMODIFIED reference CUDA build (oracle/_ref) through its own public API and stock code path."""
+    name = "reference"
+
+    def __init__(self, wl, device, world):
+        import ref_loader
+        self.ref = ref_loader.load_dsr()
+        self.wl, self.device, self.world = wl, device, 1
+        self.bg = torch.zeros(3, device=device)
+        self.leaves = {k: v.clone().requires_grad_(True) for k, v in wl["params"].items()}
+        self.means2D = torch.zeros_like(self.leaves["means3D"], requires_grad=True)
+
+    def _render(self, cam_d):
+        from gaussmart_b200 import synthetic
+        ref = self.ref
+        S = ref.GaussianRasterizationSettings(**synthetic.settings_kwargs(cam_d, self.wl["deg"], self.bg))
+        for v in self.leaves.values():
+            v.grad = None
+        self.means2D.grad = None
+        L = self.leaves
+        return ref.GaussianRasterizer(S)(
+            means3D=L["means3D"], means2D=self.means2D, opacities=L["opacities"], shs=L["shs"], scales=L["scales"],
+            rotations=L["rotations"])
+
+    def value_step(self, view):
+        color, radii, allmap = self._render(self.wl["cams_d"][view])
+        torch.autograd.backward([color, allmap], [self.wl["cot_d"][0], self.wl["cot_d"][1]])
+
+    def api_step(self, cam_d, gt):
+        color, radii, allmap = self._render(cam_d)
+        loss = loss_fn(color, allmap, gt)
+        loss.backward()
+        return loss
+
+
+# ------------------------------------------------------------------------------------------------
+# timing helpers
+# ------------------------------------------------------------------------------------------------
+def barrier(world):
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def timed_loop(fn, steps, warmup, world, rank):
+    """W untimed + K timed steps, barrier + synchronize on both sides, CUDA events on the launching
+    stream, MAX over ranks.  Returns total ms of the K steps."""
+    for s in range(warmup):
+        fn(s)
+    barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for s in range(steps):
+        fn(warmup + s)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    barrier(world)
+    return ms.item()
+
+
+def peaks():
+    p = dict(hbm_gbs=6650.0, source="fallback (B200_PROFILING.md)", sm_max_mhz=1965.0)
+    try:
+        j = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        p.update(hbm_gbs=float(j["hbm_gbs"]), source="measured (MEASURED_PEAKS.json)",
+                 sm_max_mhz=float(j.get("sm_max_mhz", 1965.0)))
+    except Exception:
+        pass
+    p["fp32_tflops"] = 148 * 128 * 2 * p["sm_max_mhz"] * 1e6 / 1e12   # SIMT FP32 FMA peak at max clock
+    return p
+
+
+def work_counts(wl, view, device):
+    """Realised P_vis, R, E (list entries evaluated), C (contributing pairs) of one view (un-timed)."""
+    from gaussmart_b200.rasterizer import _forward_impl
+    cam = wl["cams_d"][view]
+    e = torch.empty(0, device=device)
+    p = wl["params"]
+    ctr = torch.zeros(4, dtype=torch.int64, device=device)
+    out = _forward_impl(torch.zeros(3, device=device), p["means3D"], e, p["opacities"], p["scales"], p["rotations"],
+                        1.0, e, cam.world_view_transform, cam.full_proj_transform, cam.tanfovx, cam.tanfovy,
+                        cam.image_height, cam.image_width, p["shs"], wl["deg"], cam.camera_center, False, False,
+                        work_counters=ctr)
+    from gaussmart_b200 import _lib
+    lib = _lib.load()
+    W, H = wl["W"], wl["H"]
+    no = lib.gsm_image_ncontrib_offset(W, H)
+    ncontrib = out[6][no:no + 4 * W * H].view(torch.int32).long().sum().item()
+    c = ctr.tolist()
+    return dict(P_vis=int((out[3] > 0).sum().item()), R=int(out[0]), E_fwd=c[0], C=c[1], R_staged=c[2],
+                E_bwd=int(ncontrib))
+
+
+def stage_model(wl, wc, deg):
+    """ALGORITHMIC bytes / flops per launch of every stage (restated in DESIGN.md)."""
+    P, W, H = wl["P"], wl["W"], wl["H"]
+    Npx, Nt = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+    K = (deg + 1) ** 2
+    Pv, R, C = wc["P_vis"], wc["R"], wc["C"]
+    m = {}
+    m["preprocess_fwd"] = ("hbm", 48 * P + (79 + 12 * K) * Pv)
+    m["scan"] = ("hbm", 8 * P)
+    m["duplicate"] = ("hbm", 20 * Pv + 12 * R)
+    m["sort"] = ("hbm", 24 * R)
+    m["ranges"] = ("hbm", 8 * R + 8 * Nt)
+    m["render_fwd"] = ("fp32", 75 * C + 35 * (wc["E_fwd"] - C))
+    m["grad_zero"] = ("hbm", 80 * P)
+    m["render_bwd"] = ("fp32", 210 * C + 35 * (wc["E_bwd"] - C))
+    m["preprocess_bwd"] = ("hbm", (147 + 12 * K) * Pv + (44 + 12 * K) * Pv + 4 * P)
+    return m
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle port on a bounded sample (rank 0, N=1)
+# ------------------------------------------------------------------------------------------------
+def load_oracle():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("surfel_oracle", os.path.join(ROOT, "oracle", "surfel_oracle.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def cpu_baseline(full_entries_per_iter, deg):
+    """Times the CPU oracle fwd+bwd on a C1-sized crop of the workload (10 k surfels, 128x128, same surfel
+    distribution, same SH degree) and scales to the metric's unit by list entries evaluated:
+    value = (entries/s of the oracle) / (entries per iteration of the full workload).  Extrapolated: flagged."""
+    from gaussmart_b200 import synthetic
+    so = load_oracle()
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    scene = synthetic.make_scene(10_000, 128, deg, synthetic.BASE_SEED + 1)
+    cam = synthetic.make_camera(128, 128, 0.0)
+    cot = synthetic.make_cotangents(128, 128, 777)
+    t0 = time.time()
+    f = so.rasterize_forward(scene.means3D, scene.opacities, cam.world_view_transform, cam.full_proj_transform,
+                             cam.camera_center, 128, 128, cam.tanfovx, cam.tanfovy, torch.zeros(3),
+                             sh_degree=deg, shs=scene.shs, scales=scene.scales, rotations=scene.rotations)
+    so.rasterize_backward(f, cot[0], cot[1])
+    dt = time.time() - t0
+    entries = int(f["n_contrib"].reshape(2, -1)[0].long().sum().item())
+    per_s = entries / dt
+    return dict(value=per_s / max(full_entries_per_iter, 1), unit=UNIT, cores=cores, kind="port",
+                sample=f"oracle fwd+bwd of 10k surfels @128x128 SH{deg} in {dt:.1f} s ({entries} list entries); "
+                       f"extrapolated per list entry to the full workload ({full_entries_per_iter} entries/iter)",
+                sample_seconds=dt)
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference" and rank != 0:
+        return 0  # the reference is single-GPU: rank 0 alone runs it
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback of the product path)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if args.impl == "reference":
+        world = 1
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    wl = make_workload(args, device)
+    ref_kind = None
+    if args.impl == "reference":
+        import ref_loader
+        if not ref_loader.available():
+            # the reference CUDA build did not travel: time the CPU oracle port instead (bounded sample)
+            wc = work_counts(wl, 0, device)
+            cb = cpu_baseline(int(wc["E_bwd"]), wl["deg"])
+            print(json.dumps({
+                "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": 1,
+                "steps": 1, "warmup": 0, "ms_per_step": 1000.0 / cb["value"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": args.workload, "surfels": wl["P"], "width": wl["W"], "height": wl["H"]},
+                "cpu_baseline": cb,
+                "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+            return 0
+        arm = ReferenceArm(wl, device, world)
+        ref_kind = "reference CUDA build (oracle/_ref, unmodified sources, sm_100a) on the GPU"
+    else:
+        arm = OursArm(wl, device, world)
+        from gaussmart_b200 import _lib
+        _lib.stage_timing_enable(True)
+        _lib.stage_timing_read(reset=True)
+
+    view_of = lambda s: (s * world + rank) % N_VIEWS
+
+    # ---- value: device-resident
+    sampler = ClockSampler(local_rank)
+    # warm-up outside the sampler, then reset the stage timers so they cover the timed region only
+    for s in range(args.warmup):
+        arm.value_step(view_of(s))
+    barrier(world)
+    if args.impl == "ours":
+        _lib.stage_timing_read(reset=True)
+    sampler.start()
+    ms_total = timed_loop(lambda s: arm.value_step(view_of(s)), args.steps, 0, world, rank)
+    clocks = sampler.stop()
+    stages = _lib.stage_timing_read(reset=True) if args.impl == "ours" else {}
+    if args.impl == "ours":
+        _lib.stage_timing_enable(False)
+    ms_per_step = ms_total / args.steps
+    value = world * 1000.0 / ms_per_step
+
+    # ---- e2e: public API, host buffers
+    e2e = None
+    if not args.no_e2e:
+        W, H = wl["W"], wl["H"]
+        gt_dev = torch.empty(3, H, W, device=device)
+        mats_host = [torch.cat([c.world_view_transform.reshape(-1), c.full_proj_transform.reshape(-1),
+                                c.camera_center.reshape(-1)]).pin_memory() for c in wl["cams"]]
+        mats_dev = torch.empty(35, device=device)
+        loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+        from gaussmart_b200 import synthetic
+
+        def e2e_step(s):
+            v = view_of(s)
+            gt_dev.copy_(wl["gt_host"][s % 2], non_blocking=True)
+            mats_dev.copy_(mats_host[v], non_blocking=True)
+            c = wl["cams"][v]
+            cam_d = synthetic.Camera(c.image_width, c.image_height, c.FoVx, c.FoVy, c.tanfovx, c.tanfovy,
+                                     mats_dev[0:16].view(4, 4), mats_dev[16:32].view(4, 4), mats_dev[32:35])
+            loss = arm.api_step(cam_d, gt_dev)
+            loss_host.copy_(loss.detach(), non_blocking=False)   # the per-iteration .item() of train.py:149
+
+        ms_e2e = timed_loop(e2e_step, args.steps, max(3, args.warmup), world, rank)
+        e2e = {"value": world * 1000.0 * args.steps / ms_e2e, "unit": UNIT,
+               "h2d_bytes_per_step": int(3 * H * W * 4 + 35 * 4), "d2h_bytes_per_step": 4,
+               "ms_per_step": ms_e2e / args.steps,
+               "api": "GaussianRasterizationSettings/GaussianRasterizer + loss.backward()"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    pk = peaks()
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {wl['P']} surfels, {wl['W']}x{wl['H']}, SH degree {wl['deg']}, "
+                               f"fwd+bwd of one view per GPU per step, {N_VIEWS} cameras cycled",
+                   "surfels": wl["P"], "width": wl["W"], "height": wl["H"], "sh_degree": wl["deg"],
+                   "views_per_step": world, "parallelism": f"view-parallel x{world}" if world > 1 else "single GPU",
+                   "l2": "inputs larger than L2 (surfel parameters %.2f GB >> 126 MB)" %
+                         (wl["P"] * 58 * 4 / 1e9),
+                   "debug_P_override": args.P is not None},
+        "clocks": clocks, "e2e": e2e,
+    }
+    if args.impl == "reference":
+        line["impl"] = "reference"
+        line["gpu_launches"] = None
+        line["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
+                                "sample": f"full workload, every step; {ref_kind}. The reference has no CPU "
+                                          "implementation of this path, so its own implementation is timed where "
+                                          "it runs: on the same B200"}
+        if e2e is None:
+            line["e2e"] = {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+        print(json.dumps(line))
+        return 0
+
+    # ---- roofline of every stage, dominant kernel first
+    wcs = [work_counts(wl, v, device) for v in sorted({view_of(s) for s in range(args.steps)})][:N_VIEWS]
+    wc = {k: sum(w[k] for w in wcs) / len(wcs) for k in wcs[0]}
+    model = stage_model(wl, wc, wl["deg"])
+    rows = []
+    for name, (bound, work) in model.items():
+        ms, calls = stages.get(name, (0.0, 0))
+        if calls == 0:
+            continue
+        avg_ms = ms / calls
+        if bound == "hbm":
+            ach, peak, unit = work / (avg_ms * 1e-3) / 1e9, pk["hbm_gbs"], "GB/s"
+        else:
+            ach, peak, unit = work / (avg_ms * 1e-3) / 1e12, pk["fp32_tflops"], "TFLOP/s"
+        rows.append({"kernel": name, "bound": bound, "ms": avg_ms, "launches": calls, "algorithmic": work,
+                     "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak,
+                     "share_of_step": ms / ms_total})
+    rows.sort(key=lambda r: -r["ms"])
+    top = dict(rows[0]) if rows else {}
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(top.get("kernel"))
+    except Exception:
+        pass
+    line["roofline"] = {"kernel": top.get("kernel"), "bound": top.get("bound"), "achieved": top.get("achieved"),
+                        "peak": top.get("peak"), "unit": top.get("unit"), "frac": top.get("frac"),
+                        "traffic": traffic, "ms": top.get("ms"),
+                        "peak_source": pk["source"] if top.get("bound") == "hbm" else
+                        "derived: 148 SMs x 128 FP32 lanes x 2 x sm_max_mhz (no tensor-core work on this path)"}
+    line["stages"] = rows
+    line["work"] = wc
+    kernels_per_stage = {"preprocess_fwd": 1, "scan": 1, "duplicate": 1, "sort": SORT_KERNELS, "ranges": 1,
+                         "render_fwd": 1, "grad_zero": 0, "render_bwd": 1, "preprocess_bwd": 1}
+    line["gpu_launches"] = int(sum(kernels_per_stage.get(n, 0) * c for n, (_, c) in stages.items()))
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(int(wc["E_bwd"]), wl["deg"])
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+# kernels launched by the sort stage per call (CUB onesweep: histogram + scan + one pass per 8-bit digit)
+SORT_KERNELS = 8
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -16,7 +16,7 @@ GSM_ERR_BINNING_OVERFLOW = 10002
 GSM_ERR_WORKSPACE_TOO_SMALL = 10003
 GSM_SURFEL_RECORD_BYTES = 80
 GSM_GRAD_RECORD_FLOATS = 20
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 EXPORTS = [
     "gsm_last_error", "gsm_abi_version", "gsm_geometry_bytes", "gsm_image_bytes", "gsm_binning_bytes",
@@ -39,7 +39,7 @@ class ForwardArgs(Structure):
         ("geometry", c_void_p), ("geometry_bytes", c_size_t),
         ("image", c_void_p), ("image_bytes", c_size_t),
         ("binning", c_void_p), ("binning_bytes", c_size_t), ("binning_capacity", c_size_t),
-        ("num_rendered_host", POINTER(c_int)),
+        ("num_rendered_host", POINTER(c_int)), ("work_counters", c_void_p),
     ]
 
 
@@ -55,7 +55,7 @@ class BackwardArgs(Structure):
         ("grad_workspace", c_void_p), ("grad_workspace_bytes", c_size_t),
         ("dL_dmeans2D", c_void_p), ("dL_dcolors", c_void_p), ("dL_dopacity", c_void_p),
         ("dL_dmeans3D", c_void_p), ("dL_dtransMat", c_void_p), ("dL_dsh", c_void_p),
-        ("dL_dscales", c_void_p), ("dL_drotations", c_void_p),
+        ("dL_dscales", c_void_p), ("dL_drotations", c_void_p), ("accumulate", c_int),
     ]
 
 

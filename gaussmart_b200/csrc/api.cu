@@ -270,6 +270,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     rp.records = records; rp.background = a->background;
     rp.final_T = (float*)(img + I.final_T); rp.n_contrib = (uint32_t*)(img + I.n_contrib);
     rp.out_color = a->out_color; rp.out_others = a->out_others;
+    rp.stats = (unsigned long long*)a->work_counters;
     { StageMark m(GSM_STAGE_RENDER_FWD, stream); launch_render_fwd(rp, stream); }
     GSM_STAGE("forward render");
   } else {
@@ -320,7 +321,7 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   volatile float wx = focal_x * a->tan_fovx;
   volatile float wy = focal_y * a->tan_fovy;
   BwdPreprocessParams pp{};
-  pp.P = P; pp.D = a->D; pp.M = a->M;
+  pp.P = P; pp.D = a->D; pp.M = a->M; pp.accumulate = a->accumulate;
   pp.W = (int)(wx * 2); pp.H = (int)(wy * 2);
   pp.means3D = a->means3D; pp.scales = a->scales; pp.rotations = a->rotations; pp.shs = a->shs;
   pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;

@@ -153,6 +153,7 @@ struct FwdRenderParams {
   uint32_t* n_contrib;
   float* out_color;
   float* out_others;
+  unsigned long long* stats;  // optional work counters (NULL in production)
 };
 void launch_render_fwd(const FwdRenderParams& p, cudaStream_t stream);
 
@@ -172,6 +173,7 @@ void launch_render_bwd(const BwdRenderParams& p, cudaStream_t stream);
 
 struct BwdPreprocessParams {
   int P, D, M, W, H;  // W,H: the sizes re-derived in fp32 as backward.cu:613-614 does
+  int accumulate;     // outputs (except dL_dmeans2D) += instead of =
   const float* means3D;
   const float* scales;
   const float* rotations;

@@ -18,22 +18,25 @@ __device__ __forceinline__ f3 operator*(f3 a, f3 b) { return mk(a.x * b.x, a.y *
 __device__ __forceinline__ f3 operator*(float s, f3 a) { return mk(s * a.x, s * a.y, s * a.z); }
 __device__ __forceinline__ float dot(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 
-__device__ __forceinline__ void store3(float* dst, f3 v) { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; }
+__device__ __forceinline__ void store3(float* dst, f3 v, bool acc = false) {
+  if (acc) { dst[0] += v.x; dst[1] += v.y; dst[2] += v.z; }
+  else { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; }
+}
 
 // SH backward (backward.cu:20-139). dL_dsh row is fully written (zeros beyond the active degree).
 __device__ void sh_backward(int D, int M, const float* __restrict__ sh, f3 dir_orig, f3 dL_dRGB,
-                            float* __restrict__ dL_dsh, f3& dL_dmean_add) {
+                            float* __restrict__ dL_dsh, f3& dL_dmean_add, bool acc) {
   const float inv_len = 1.0f / sqrtf(dot(dir_orig, dir_orig));
   const float x = dir_orig.x * inv_len, y = dir_orig.y * inv_len, z = dir_orig.z * inv_len;
   const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
   f3 dx = mk(0, 0, 0), dy = mk(0, 0, 0), dz = mk(0, 0, 0);
 #define SH(k) mk(__ldg(sh + 3 * (k)), __ldg(sh + 3 * (k) + 1), __ldg(sh + 3 * (k) + 2))
-  store3(dL_dsh + 0, C0 * dL_dRGB);
+  store3(dL_dsh + 0, C0 * dL_dRGB, acc);
   int written = 1;
   if (D > 0) {
-    store3(dL_dsh + 3, (-C1 * y) * dL_dRGB);
-    store3(dL_dsh + 6, (C1 * z) * dL_dRGB);
-    store3(dL_dsh + 9, (-C1 * x) * dL_dRGB);
+    store3(dL_dsh + 3, (-C1 * y) * dL_dRGB, acc);
+    store3(dL_dsh + 6, (C1 * z) * dL_dRGB, acc);
+    store3(dL_dsh + 9, (-C1 * x) * dL_dRGB, acc);
     dx = (-C1) * SH(3);
     dy = (-C1) * SH(1);
     dz = C1 * SH(2);
@@ -42,11 +45,11 @@ __device__ void sh_backward(int D, int M, const float* __restrict__ sh, f3 dir_o
       const float C20 = 1.0925484305920792f, C21 = -1.0925484305920792f, C22 = 0.31539156525252005f,
                   C23 = -1.0925484305920792f, C24 = 0.5462742152960396f;
       const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-      store3(dL_dsh + 12, (C20 * xy) * dL_dRGB);
-      store3(dL_dsh + 15, (C21 * yz) * dL_dRGB);
-      store3(dL_dsh + 18, (C22 * (2.f * zz - xx - yy)) * dL_dRGB);
-      store3(dL_dsh + 21, (C23 * xz) * dL_dRGB);
-      store3(dL_dsh + 24, (C24 * (xx - yy)) * dL_dRGB);
+      store3(dL_dsh + 12, (C20 * xy) * dL_dRGB, acc);
+      store3(dL_dsh + 15, (C21 * yz) * dL_dRGB, acc);
+      store3(dL_dsh + 18, (C22 * (2.f * zz - xx - yy)) * dL_dRGB, acc);
+      store3(dL_dsh + 21, (C23 * xz) * dL_dRGB, acc);
+      store3(dL_dsh + 24, (C24 * (xx - yy)) * dL_dRGB, acc);
       const f3 s4 = SH(4), s5 = SH(5), s6 = SH(6), s7 = SH(7), s8 = SH(8);
       dx = dx + (C20 * y) * s4 + (C22 * 2.f * -x) * s6 + (C23 * z) * s7 + (C24 * 2.f * x) * s8;
       dy = dy + (C20 * x) * s4 + (C21 * z) * s5 + (C22 * 2.f * -y) * s6 + (C24 * 2.f * -y) * s8;
@@ -56,13 +59,13 @@ __device__ void sh_backward(int D, int M, const float* __restrict__ sh, f3 dir_o
         const float C30 = -0.5900435899266435f, C31 = 2.890611442640554f, C32 = -0.4570457994644658f,
                     C33 = 0.3731763325901154f, C34 = -0.4570457994644658f, C35 = 1.445305721320277f,
                     C36 = -0.5900435899266435f;
-        store3(dL_dsh + 27, (C30 * y * (3.f * xx - yy)) * dL_dRGB);
-        store3(dL_dsh + 30, (C31 * xy * z) * dL_dRGB);
-        store3(dL_dsh + 33, (C32 * y * (4.f * zz - xx - yy)) * dL_dRGB);
-        store3(dL_dsh + 36, (C33 * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB);
-        store3(dL_dsh + 39, (C34 * x * (4.f * zz - xx - yy)) * dL_dRGB);
-        store3(dL_dsh + 42, (C35 * z * (xx - yy)) * dL_dRGB);
-        store3(dL_dsh + 45, (C36 * x * (xx - 3.f * yy)) * dL_dRGB);
+        store3(dL_dsh + 27, (C30 * y * (3.f * xx - yy)) * dL_dRGB, acc);
+        store3(dL_dsh + 30, (C31 * xy * z) * dL_dRGB, acc);
+        store3(dL_dsh + 33, (C32 * y * (4.f * zz - xx - yy)) * dL_dRGB, acc);
+        store3(dL_dsh + 36, (C33 * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB, acc);
+        store3(dL_dsh + 39, (C34 * x * (4.f * zz - xx - yy)) * dL_dRGB, acc);
+        store3(dL_dsh + 42, (C35 * z * (xx - yy)) * dL_dRGB, acc);
+        store3(dL_dsh + 45, (C36 * x * (xx - 3.f * yy)) * dL_dRGB, acc);
         const f3 s9 = SH(9), s10 = SH(10), s11 = SH(11), s12 = SH(12), s13 = SH(13), s14 = SH(14), s15 = SH(15);
         dx = dx + ((C30 * 3.f * 2.f * xy) * s9 + (C31 * yz) * s10 + (C32 * -2.f * xy) * s11 +
                    (C33 * -3.f * 2.f * xz) * s12 + (C34 * (-3.f * xx + 4.f * zz - yy)) * s13 +
@@ -77,7 +80,8 @@ __device__ void sh_backward(int D, int M, const float* __restrict__ sh, f3 dir_o
     }
   }
 #undef SH
-  for (int k = written * 3; k < M * 3; k++) dL_dsh[k] = 0.0f;
+  if (!acc)
+    for (int k = written * 3; k < M * 3; k++) dL_dsh[k] = 0.0f;
 
   const f3 dL_ddir = mk(dot(dx, dL_dRGB), dot(dy, dL_dRGB), dot(dz, dL_dRGB));
   // dnormvdv (auxiliary.h:128-138)
@@ -94,6 +98,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocess
   if (idx >= p.P) return;
   const size_t i = (size_t)idx;
   const bool visible = __ldg(p.radii + idx) > 0;
+  const bool acc = p.accumulate != 0;  // outputs += (view-parallel accumulation over local views)
 
   f3 dmean3D = mk(0, 0, 0);
   float dmean2D_x = 0.f, dmean2D_y = 0.f, dopacity = 0.f;
@@ -233,7 +238,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocess
       if (clamp_bits & 4) dRGB.z = 0.f;
       const f3 dir_orig = mk(pos.x - p.campos[0], pos.y - p.campos[1], pos.z - p.campos[2]);
       f3 add;
-      sh_backward(p.D, p.M, p.shs + i * p.M * 3, dir_orig, dRGB, p.dL_dsh + i * p.M * 3, add);
+      sh_backward(p.D, p.M, p.shs + i * p.M * 3, dir_orig, dRGB, p.dL_dsh + i * p.M * 3, add, acc);
       dmean3D = dmean3D + add;
       sh_written = true;
     }
@@ -246,11 +251,30 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocess
     dmean2D_y = a5 * depth * 0.5f * float(p.H);
   }
 
+  // the view-space gradient is per view (gm.py:551-553 takes its norm per view): never accumulated
+  p.dL_dmeans2D[3 * i] = dmean2D_x; p.dL_dmeans2D[3 * i + 1] = dmean2D_y; p.dL_dmeans2D[3 * i + 2] = 0.f;
+  if (acc) {
+    if (!visible) return;  // adds nothing
+    p.dL_dopacity[i] += dopacity;
+    store3(p.dL_dmeans3D + 3 * i, dmean3D, true);
+    if (p.dL_dcolors) store3(p.dL_dcolors + 3 * i, dcolor, true);
+    if (p.dL_dtransMat) {
+#pragma unroll
+      for (int k = 0; k < 9; k++) p.dL_dtransMat[9 * i + k] += dT[k];
+    }
+    if (p.dL_dscales) { p.dL_dscales[2 * i] += dscale_x; p.dL_dscales[2 * i + 1] += dscale_y; }
+    if (p.dL_drotations) {
+      float4* d = reinterpret_cast<float4*>(p.dL_drotations) + i;
+      float4 o = *d;
+      o.x += drot.x; o.y += drot.y; o.z += drot.z; o.w += drot.w;
+      *d = o;
+    }
+    return;
+  }
   if (p.dL_dsh != nullptr && !sh_written) {
     float* o = p.dL_dsh + i * p.M * 3;
     for (int k = 0; k < p.M * 3; k++) o[k] = 0.f;
   }
-  p.dL_dmeans2D[3 * i] = dmean2D_x; p.dL_dmeans2D[3 * i + 1] = dmean2D_y; p.dL_dmeans2D[3 * i + 2] = 0.f;
   p.dL_dopacity[i] = dopacity;
   store3(p.dL_dmeans3D + 3 * i, dmean3D);
   if (p.dL_dcolors) store3(p.dL_dcolors + 3 * i, dcolor);

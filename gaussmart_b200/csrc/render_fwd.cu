@@ -39,6 +39,7 @@ __device__ __forceinline__ void stage_batch(float4 (*q)[FWD_BATCH], const float4
   }
 }
 
+template <bool STATS>
 __global__ void __launch_bounds__(TILE_PIX) render_fwd_kernel(const FwdRenderParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FwdSmem& sm = *reinterpret_cast<FwdSmem*>(smem_raw);
@@ -58,6 +59,7 @@ __global__ void __launch_bounds__(TILE_PIX) render_fwd_kernel(const FwdRenderPar
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, N0 = 0.f, N1 = 0.f, N2 = 0.f;
   float D = 0.f, M1 = 0.f, M2 = 0.f, distortion = 0.f, median_depth = 0.f;
   float median_contributor = -1.0f;
+  uint32_t n_contributing = 0;  // STATS only
   const float far_ratio = __uint_as_float(GSM_FAR_RATIO_BITS);
 
   if (rounds > 0) stage_batch(sm.q[0], p.records, p.point_list, range.x, range.y, t);
@@ -121,10 +123,22 @@ __global__ void __launch_bounds__(TILE_PIX) render_fwd_kernel(const FwdRenderPar
         C0 = FMA(w, col.x, C0); C1 = FMA(w, col.y, C1); C2 = FMA(w, col.z, C2);
         T = test_T;
         last_contributor = contributor;
+        if (STATS) n_contributing++;
       }
     }
   }
   __pipeline_wait_prior(0);
+
+  if (STATS) {  // work counters for the roofline model (bench only): [0] entries evaluated, [1] contributing pairs
+    unsigned long long e = inside ? contributor : 0u, c = n_contributing;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      e += __shfl_xor_sync(0xffffffffu, e, o);
+      c += __shfl_xor_sync(0xffffffffu, c, o);
+    }
+    if ((t & 31) == 0) { atomicAdd(p.stats + 0, e); atomicAdd(p.stats + 1, c); }
+    if (t == 0) atomicAdd(p.stats + 2, (unsigned long long)total);
+  }
 
   if (inside) {
     const size_t N = (size_t)p.W * p.H;
@@ -150,11 +164,13 @@ __global__ void __launch_bounds__(TILE_PIX) render_fwd_kernel(const FwdRenderPar
 void launch_render_fwd(const FwdRenderParams& p, cudaStream_t stream) {
   static bool configured = false;
   if (!configured) {
-    cudaFuncSetAttribute(render_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem));
+    cudaFuncSetAttribute(render_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem));
+    cudaFuncSetAttribute(render_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem));
     configured = true;
   }
   dim3 grid(p.grid_x, p.grid_y, 1);
-  render_fwd_kernel<<<grid, TILE_PIX, sizeof(FwdSmem), stream>>>(p);
+  if (p.stats) render_fwd_kernel<true><<<grid, TILE_PIX, sizeof(FwdSmem), stream>>>(p);
+  else render_fwd_kernel<false><<<grid, TILE_PIX, sizeof(FwdSmem), stream>>>(p);
 }
 
 }  // namespace gsm

@@ -61,8 +61,9 @@ class _Workspaces(NamedTuple):
 
 def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3Ds_precomp,
                   viewmatrix, projmatrix, tanfovx, tanfovy, image_height, image_width, sh, sh_degree, campos,
-                  prefiltered, debug):
-    """Equivalent of RasterizeGaussiansCUDA (rasterize_points.cu:39-134)."""
+                  prefiltered, debug, work_counters=None):
+    """Equivalent of RasterizeGaussiansCUDA (rasterize_points.cu:39-134).
+    work_counters: optional zeroed int64[4] CUDA tensor receiving work counts (bench only)."""
     lib = _lib.load()
     if means3D.ndim != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
@@ -107,6 +108,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
         a.geometry, a.geometry_bytes = _ptr(geometry), geometry.numel()
         a.image, a.image_bytes = _ptr(image), image.numel()
         a.num_rendered_host = ctypes.pointer(num_rendered)
+        a.work_counters = _ptr(work_counters)
 
         key = (dev.index, )
         capacity = _binning_capacity.get(key, 0)
@@ -125,8 +127,11 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
 
 def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp, viewmatrix,
                    projmatrix, tanfovx, tanfovy, grad_out_color, grad_depth, sh, sh_degree, campos, geomBuffer,
-                   num_rendered, binningBuffer, imgBuffer, debug):
-    """Equivalent of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:136-233)."""
+                   num_rendered, binningBuffer, imgBuffer, debug, out=None, accumulate=False):
+    """Equivalent of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:136-233).
+
+    `out` (optional) maps means3D / shs / opacities / scales / rotations to preallocated tensors the
+    kernel writes into (or adds to, with `accumulate`) -- the view-parallel gradient bucket."""
     lib = _lib.load()
     P = means3D.shape[0]
     H, W = grad_out_color.shape[1], grad_out_color.shape[2]
@@ -136,15 +141,26 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
     grad_depth = _f32c("dL_dout_others", grad_depth)
     with torch.cuda.device(dev):
         f32 = dict(dtype=torch.float32, device=dev)
-        dL_dmeans3D = torch.empty((P, 3), **f32)
+        out = out or {}
+
+        def _out(name, shape):
+            t = out.get(name)
+            if t is None:
+                if accumulate:
+                    raise RuntimeError(f"accumulate=True needs a preallocated output for {name}")
+                return torch.empty(shape, **f32)
+            if tuple(t.shape) != tuple(shape) or t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev:
+                raise RuntimeError(f"output tensor for {name} must be contiguous float32 {tuple(shape)} on {dev}")
+            return t
+
+        dL_dmeans3D = _out("means3D", (P, 3))
         dL_dmeans2D = torch.empty((P, 3), **f32)
-        dL_dcolors = torch.empty((P, 3), **f32)
-        dL_dnormal = None  # folded into the internal gradient record
-        dL_dopacity = torch.empty((P, 1), **f32)
-        dL_dtransMat = torch.empty((P, 9), **f32)
-        dL_dsh = torch.empty((P, M, 3), **f32)
-        dL_dscales = torch.empty((P, 2), **f32)
-        dL_drotations = torch.empty((P, 4), **f32)
+        dL_dcolors = _out("colors_precomp", (P, 3))
+        dL_dopacity = _out("opacities", (P, 1))
+        dL_dtransMat = _out("cov3D_precomp", (P, 9))
+        dL_dsh = _out("shs", (P, M, 3))
+        dL_dscales = _out("scales", (P, 2))
+        dL_drotations = _out("rotations", (P, 4))
         if P != 0:
             gws = torch.empty((lib.gsm_grad_workspace_bytes(P),), dtype=torch.uint8, device=dev)
             a = _lib.BackwardArgs()
@@ -159,6 +175,7 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
             a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity = _ptr(dL_dmeans2D), _ptr(dL_dcolors), _ptr(dL_dopacity)
             a.dL_dmeans3D, a.dL_dtransMat, a.dL_dsh = _ptr(dL_dmeans3D), _ptr(dL_dtransMat), _ptr(dL_dsh)
             a.dL_dscales, a.dL_drotations = _ptr(dL_dscales), _ptr(dL_drotations)
+            a.accumulate = int(bool(accumulate))
             stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
             _lib.check(lib.gsm_backward(ctypes.byref(a), stream), "backward")
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dtransMat, dL_dsh, dL_dscales, dL_drotations
@@ -240,6 +257,42 @@ class _RasterizeGaussians(torch.autograd.Function):
             None,
         )
         return grads
+
+
+def rasterize_into_bucket(params, camera, bucket, accumulate, bg=None, scale_modifier=1.0):
+    """Forward + (deferred) backward of one view with the surfel gradients written by the backward
+    preprocess kernel straight into `bucket.views` (gaussmart_b200.view_parallel.GradBucket) -- no
+    autograd, no pack kernel before the collective.
+
+    params : dict means3D[P,3], shs[P,M,3], opacities[P,1], scales[P,2], rotations[P,4] (CUDA, fp32)
+    camera : object with image_width/height, tanfovx/y, world_view_transform, full_proj_transform,
+             camera_center (scene/cameras.py:17-59 attribute names), tensors on the same device
+    Returns (color, radii, allmap, backward) with backward(dL_dcolor, dL_dallmap) -> dL_dmeans2D[P,3].
+    """
+    dev = params["means3D"].device
+    e = torch.empty(0, device=dev)
+    if bg is None:
+        bg = torch.zeros(3, dtype=torch.float32, device=dev)
+    sh = params["shs"]
+    sh_degree = int(round(sh.shape[1] ** 0.5)) - 1
+    H, W = int(camera.image_height), int(camera.image_width)
+    with torch.no_grad():
+        R, color, allmap, radii, geom, binning, image = _forward_impl(
+            bg, params["means3D"], e, params["opacities"], params["scales"], params["rotations"], scale_modifier, e,
+            camera.world_view_transform, camera.full_proj_transform, camera.tanfovx, camera.tanfovy, H, W, sh,
+            sh_degree, camera.camera_center, False, False)
+
+    def backward(dL_dcolor, dL_dallmap):
+        with torch.no_grad():
+            g = _backward_impl(bg, params["means3D"].contiguous(), radii, e, params["scales"].contiguous(),
+                               params["rotations"].contiguous(), scale_modifier, e,
+                               camera.world_view_transform.contiguous(), camera.full_proj_transform.contiguous(),
+                               camera.tanfovx, camera.tanfovy, dL_dcolor, dL_dallmap, sh.contiguous(), sh_degree,
+                               camera.camera_center.contiguous(), geom, R, binning, image, False,
+                               out=bucket.views, accumulate=accumulate)
+        return g[0]
+
+    return color, radii, allmap, backward
 
 
 class GaussianRasterizationSettings(NamedTuple):

@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 1
+#define GSM_ABI_VERSION 2
 
 #define GSM_OK 0
 #define GSM_ERR_INVALID_ARGUMENT 10001
@@ -98,6 +98,9 @@ typedef struct gsm_forward_args {
   void* image;    size_t image_bytes;
   void* binning;  size_t binning_bytes; size_t binning_capacity;
   int* num_rendered_host;        /* HOST pointer: receives R (valid on GSM_OK and on overflow) */
+  uint64_t* work_counters;       /* optional DEVICE u64[4], caller-zeroed, ADDED to: [0] list entries
+                                    evaluated, [1] contributing (pixel,surfel) pairs, [2] records staged.
+                                    NULL in production; used by bench.py for the roofline model. */
 } gsm_forward_args;
 
 /* Runs preprocess + scan, waits for R (one stream synchronisation, as rasterizer_impl.cu:282),
@@ -140,6 +143,9 @@ typedef struct gsm_backward_args {
   float* dL_dsh;        /* [P,M,3] (may be NULL when M == 0) */
   float* dL_dscales;    /* [P,2] */
   float* dL_drotations; /* [P,4] */
+  int accumulate;       /* 0: outputs are overwritten (reference semantics: fresh zero tensors,
+                           rasterize_points.cu:187-195).  1: every output except dL_dmeans2D is
+                           ADDED to (view-parallel accumulation over a rank's local views) */
 } gsm_backward_args;
 
 size_t gsm_grad_workspace_bytes(int P);

@@ -279,7 +279,7 @@ def work_counts(wl, view, device):
     no = lib.gsm_image_ncontrib_offset(W, H)
     ncontrib = out[6][no:no + 4 * W * H].view(torch.int32).long().sum().item()
     c = ctr.tolist()
-    return dict(P_vis=int((out[3] > 0).sum().item()), R=int(out[0]), E_fwd=c[0], C=c[1], R_staged=c[2],
+    return dict(P_vis=int((out[3] > 0).sum().item()), R=int(out[0]), E_fwd=c[0], C=c[1], R_staged=c[2], E_fwd_culled=c[3],
                 E_bwd=int(ncontrib))
 
 

@@ -82,6 +82,7 @@ GeometryLayout geometry_layout(int P) {
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 128); return o; };
   L.records = take(n * GSM_SURFEL_RECORD_BYTES);
+  L.bbox = take(n * 8);
   L.tiles_touched = take(n * 4);
   L.offsets = take(n * 4);
   L.scan_temp_bytes = scan_temp_bytes(P);
@@ -170,7 +171,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (a == nullptr) { set_error("gsm_forward: null args"); return GSM_ERR_INVALID_ARGUMENT; }
   const int P = a->P, W = a->width, H = a->height;
-  const bool debug = a->debug != 0;
+  const bool debug = (a->debug & 1) != 0;
   if (P < 0 || W <= 0 || H <= 0) { set_error("gsm_forward: bad sizes P=%d W=%d H=%d", P, W, H); return GSM_ERR_INVALID_ARGUMENT; }
   if (a->num_rendered_host == nullptr) { set_error("gsm_forward: num_rendered_host is null"); return GSM_ERR_INVALID_ARGUMENT; }
   if ((a->shs == nullptr) == (a->colors_precomp == nullptr) && P > 0) {
@@ -209,7 +210,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     pp.means3D = a->means3D; pp.scales = a->scales; pp.rotations = a->rotations; pp.opacities = a->opacities;
     pp.shs = a->shs; pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;
     pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
-    pp.radii = a->radii; pp.records = records; pp.tiles_touched = tiles_touched; pp.flags = flags;
+    pp.radii = a->radii; pp.records = records; pp.bbox = (short4*)(geom + G.bbox); pp.tiles_touched = tiles_touched; pp.flags = flags;
     { StageMark m(GSM_STAGE_PREPROCESS_FWD, stream); launch_preprocess_fwd(pp, stream); }
     GSM_STAGE("forward preprocess");
     {
@@ -268,6 +269,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     rp.ranges = ranges;
     rp.point_list = bin ? (const uint32_t*)(bin + B.point_list) : nullptr;
     rp.records = records; rp.background = a->background;
+    rp.bbox = (const short4*)(geom + G.bbox); rp.no_cull = (a->debug & 2) ? 1 : 0;
     rp.final_T = (float*)(img + I.final_T); rp.n_contrib = (uint32_t*)(img + I.n_contrib);
     rp.out_color = a->out_color; rp.out_others = a->out_others;
     rp.stats = (unsigned long long*)a->work_counters;
@@ -284,7 +286,7 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (a == nullptr) { set_error("gsm_backward: null args"); return GSM_ERR_INVALID_ARGUMENT; }
   const int P = a->P, W = a->width, H = a->height;
-  const bool debug = a->debug != 0;
+  const bool debug = (a->debug & 1) != 0;
   if (P < 0 || W <= 0 || H <= 0) { set_error("gsm_backward: bad sizes"); return GSM_ERR_INVALID_ARGUMENT; }
   if (P == 0) return GSM_OK;
   if (a->grad_workspace == nullptr || a->grad_workspace_bytes < gsm_grad_workspace_bytes(P)) {
@@ -307,6 +309,7 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   rp.ranges = (const uint2*)(img + I.ranges);
   rp.point_list = (const uint32_t*)bin;  // point_list sits at offset 0 of the binning workspace
   rp.records = (const float4*)(geom + G.records);
+  rp.bbox = (const short4*)(geom + G.bbox); rp.no_cull = (a->debug & 2) ? 1 : 0;
   rp.background = a->background;
   rp.final_T = (const float*)(img + I.final_T);
   rp.n_contrib = (const uint32_t*)(img + I.n_contrib);

@@ -34,6 +34,16 @@ constexpr float T_EPS = 0.0001f;
 //   q4 = (r,    g,    b,    clamp bits)   clamp bits: int bit c set when channel c was clamped at 0
 constexpr int REC_F4 = 5;
 
+// Conservative contribution box (short4 per surfel: xmin, ymin, xmax, ymax in integer pixel
+// coordinates, inclusive).  A pixel outside it cannot pass the reference's alpha >= 1/255 test
+// (forward.cu:385-392): alpha = opacity*exp(-rho/2) >= 1/255 needs rho = min(rho3d, rho2d) <=
+// 2 ln 255 = 11.083, so the box encloses the perspective-correct image of the disc u^2+v^2 <=
+// CULL_RHO (the reference's own AABB construction, forward.cu:119-145, at a larger cutoff) united
+// with the low-pass disc 2|d|^2 <= CULL_RHO, plus slack; surfels whose disc is not wholly in front
+// of the camera plane get the unbounded box.  Compositing kernels use it only to SKIP work.
+constexpr float CULL_RHO = 11.5f;
+constexpr float CULL_SLACK_PX = 0.75f;
+
 // Gradient accumulation record (GSM_GRAD_RECORD_FLOATS = 20 floats, 80 B):
 //   [0..2] dTu  [3..5] dTv  [6..8] dTw  [9..10] dcentre  [11..13] drgb  [14..16] dnormal
 //   [17] dopacity  [18..19] pad
@@ -45,6 +55,7 @@ __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a -
 // ---- workspace layouts ------------------------------------------------------------------
 struct GeometryLayout {
   size_t records;        // float4[P*5]
+  size_t bbox;           // short4[P]  conservative integer pixel box of possible contribution
   size_t tiles_touched;  // u32[P]
   size_t offsets;        // u32[P]   inclusive scan of tiles_touched
   size_t scan_temp;      // bytes for the scan
@@ -123,6 +134,7 @@ struct FwdPreprocessParams {
   const float* campos;
   int* radii;
   float4* records;
+  short4* bbox;
   uint32_t* tiles_touched;
   uint32_t* flags;
 };
@@ -148,6 +160,8 @@ struct FwdRenderParams {
   const uint2* ranges;
   const uint32_t* point_list;
   const float4* records;
+  const short4* bbox;
+  int no_cull;  // debug: evaluate every (pixel, entry) pair as the reference does
   const float* background;
   float* final_T;
   uint32_t* n_contrib;
@@ -162,6 +176,8 @@ struct BwdRenderParams {
   const uint2* ranges;
   const uint32_t* point_list;
   const float4* records;
+  const short4* bbox;
+  int no_cull;
   const float* background;
   const float* final_T;
   const uint32_t* n_contrib;

@@ -209,6 +209,34 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const FwdPreprocess
       rgb.z = __ldg(p.colors_precomp + 3 * (size_t)idx + 2);
     }
 
+    // conservative contribution box (common.cuh, CULL_RHO); fp64 so that the cancellation in
+    // centre^2 - <f,T^2> cannot shrink it
+    short4 box = make_short4(-32768, -32768, 32767, 32767);
+    {
+      const double c2 = (double)CULL_RHO;
+      const double w0 = Tw0, w1 = Tw1, w2 = Tw2;
+      const double dd = c2 * (w0 * w0 + w1 * w1) - w2 * w2;
+      if (dd < -1e-6 * w2 * w2 && w2 > 0.0) {  // the whole disc is in front of the camera plane
+        const double f0 = c2 / dd, f2 = -1.0 / dd;
+        const double ccx = f0 * ((double)Tu0 * w0 + (double)Tu1 * w1) + f2 * (double)Tu2 * w2;
+        const double ccy = f0 * ((double)Tv0 * w0 + (double)Tv1 * w1) + f2 * (double)Tv2 * w2;
+        const double ex2 = ccx * ccx - (f0 * ((double)Tu0 * Tu0 + (double)Tu1 * Tu1) + f2 * (double)Tu2 * Tu2);
+        const double ey2 = ccy * ccy - (f0 * ((double)Tv0 * Tv0 + (double)Tv1 * Tv1) + f2 * (double)Tv2 * Tv2);
+        const double ex = sqrt(fmax(ex2, 0.0)) * 1.01 + (double)CULL_SLACK_PX;
+        const double ey = sqrt(fmax(ey2, 0.0)) * 1.01 + (double)CULL_SLACK_PX;
+        const double r2d = sqrt(0.5 * c2) + (double)CULL_SLACK_PX;  // low-pass disc around the reference centre
+        const double x0 = fmin(ccx - ex, (double)cx - r2d), x1 = fmax(ccx + ex, (double)cx + r2d);
+        const double y0 = fmin(ccy - ey, (double)cy - r2d), y1 = fmax(ccy + ey, (double)cy + r2d);
+        if (x0 == x0 && x1 == x1 && y0 == y0 && y1 == y1) {  // not NaN
+          box.x = (short)fmax(-32768.0, fmin(32767.0, floor(x0)));
+          box.y = (short)fmax(-32768.0, fmin(32767.0, floor(y0)));
+          box.z = (short)fmax(-32768.0, fmin(32767.0, ceil(x1)));
+          box.w = (short)fmax(-32768.0, fmin(32767.0, ceil(y1)));
+        }
+      }
+    }
+    p.bbox[idx] = box;
+
     float4* rec = p.records + (size_t)idx * REC_F4;
     rec[0] = make_float4(Tu0, Tu1, Tu2, cx);
     rec[1] = make_float4(Tv0, Tv1, Tv2, cy);

@@ -26,10 +26,13 @@ constexpr int BWD_BATCH = 256;
 struct BwdSmem {
   float4 q[2][REC_F4][BWD_BATCH];
   uint32_t id[2][BWD_BATCH];
+  short4 bbox[2][BWD_BATCH];               // conservative contribution boxes (common.cuh)
+  uint8_t list[TILE_PIX / 32][BWD_BATCH];  // per-warp compacted entry indices (back to front)
   int warp_max[TILE_PIX / 32];
 };
 
 __device__ __forceinline__ void stage_batch_rev(BwdSmem& sm, int s, const float4* __restrict__ records,
+                                                const short4* __restrict__ bbox,
                                                 const uint32_t* __restrict__ point_list,
                                                 uint32_t list_begin, int pos, int t) {
   // pos: position (0-based within the tile list) of this thread's entry; negative => none
@@ -39,6 +42,7 @@ __device__ __forceinline__ void stage_batch_rev(BwdSmem& sm, int s, const float4
     const float4* src = records + (size_t)id * REC_F4;
 #pragma unroll
     for (int f = 0; f < REC_F4; f++) __pipeline_memcpy_async(&sm.q[s][f][t], src + f, sizeof(float4));
+    __pipeline_memcpy_async(&sm.bbox[s][t], bbox + id, sizeof(short4));
   }
 }
 
@@ -135,6 +139,10 @@ __global__ void __launch_bounds__(TILE_PIX, 2) render_bwd_kernel(const BwdRender
   for (int w = 0; w < TILE_PIX / 32; w++) start = max(start, sm.warp_max[w]);
   const int rounds = (start + BWD_BATCH - 1) / BWD_BATCH;
 
+  const int sx_lo = blockIdx.x * TILE_X, sx_hi = sx_lo + TILE_X - 1;
+  const int sy_lo = blockIdx.y * TILE_Y + 2 * warp, sy_hi = sy_lo + 1;
+  uint8_t* __restrict__ mylist = sm.list[warp];
+
   float T = T_final;
   float accum_rec[3] = {0.f, 0.f, 0.f}, last_color[3] = {0.f, 0.f, 0.f};
   float last_alpha = 0.f, last_depth = 0.f, last_normal[3] = {0.f, 0.f, 0.f};
@@ -142,7 +150,7 @@ __global__ void __launch_bounds__(TILE_PIX, 2) render_bwd_kernel(const BwdRender
   float last_dL_dT = 0.f;
   const float far_ratio = __uint_as_float(GSM_FAR_RATIO_BITS);
 
-  if (rounds > 0) stage_batch_rev(sm, 0, p.records, p.point_list, range.x, start - 1 - t, t);
+  if (rounds > 0) stage_batch_rev(sm, 0, p.records, p.bbox, p.point_list, range.x, start - 1 - t, t);
   __pipeline_commit();
 
   for (int i = 0; i < rounds; i++) {
@@ -150,13 +158,29 @@ __global__ void __launch_bounds__(TILE_PIX, 2) render_bwd_kernel(const BwdRender
     __pipeline_wait_prior(0);
     __syncthreads();
     if (i + 1 < rounds)
-      stage_batch_rev(sm, s ^ 1, p.records, p.point_list, range.x, start - 1 - ((i + 1) * BWD_BATCH + t), t);
+      stage_batch_rev(sm, s ^ 1, p.records, p.bbox, p.point_list, range.x, start - 1 - ((i + 1) * BWD_BATCH + t), t);
     __pipeline_commit();
 
     const int base_pos = start - 1 - i * BWD_BATCH;  // position of entry j = base_pos - j
     const int n = min(BWD_BATCH, base_pos + 1);
     const int j0 = max(0, base_pos + 1 - warp_last);  // entries before j0 are behind every pixel of the warp
-    for (int j = j0; j < n; j++) {
+    // per-warp compaction of the entries whose contribution box meets this warp's 16x2 strip
+    int cnt = 0;
+#pragma unroll
+    for (int r = 0; r < BWD_BATCH / 32; r++) {
+      const int j = r * 32 + lane;
+      bool hit = false;
+      if (j >= j0 && j < n) {
+        const short4 bx = sm.bbox[s][j];
+        hit = p.no_cull || (bx.x <= sx_hi && bx.z >= sx_lo && bx.y <= sy_hi && bx.w >= sy_lo);
+      }
+      const unsigned m = __ballot_sync(0xffffffffu, hit);
+      if (hit) mylist[cnt + __popc(m & ((1u << lane) - 1u))] = (uint8_t)j;
+      cnt += __popc(m);
+    }
+    __syncwarp();
+    for (int e = 0; e < cnt; e++) {
+      const int j = mylist[e];
       const int k = base_pos - j;  // == the reference's `contributor` after its decrement
       bool active = k < last_contributor;
       const float4 a = sm.q[s][0][j], b = sm.q[s][1][j], c = sm.q[s][2][j];

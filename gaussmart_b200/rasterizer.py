@@ -99,7 +99,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
         a = _lib.ForwardArgs()
         a.P, a.D, a.M, a.width, a.height = P, int(sh_degree), M, W, H
         a.tan_fovx, a.tan_fovy, a.scale_modifier = float(tanfovx), float(tanfovy), float(scale_modifier)
-        a.prefiltered, a.debug = int(bool(prefiltered)), int(bool(debug))
+        a.prefiltered, a.debug = int(bool(prefiltered)), int(debug)
         a.background, a.means3D, a.shs, a.colors_precomp = _ptr(bg), _ptr(means3D), _ptr(sh), _ptr(colors_precomp)
         a.opacities, a.scales, a.rotations = _ptr(opacities), _ptr(scales), _ptr(rotations)
         a.transMat_precomp = _ptr(cov3Ds_precomp)
@@ -165,7 +165,7 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
             gws = torch.empty((lib.gsm_grad_workspace_bytes(P),), dtype=torch.uint8, device=dev)
             a = _lib.BackwardArgs()
             a.P, a.D, a.M, a.width, a.height = P, int(sh_degree), M, W, H
-            a.tan_fovx, a.tan_fovy, a.scale_modifier, a.debug = float(tanfovx), float(tanfovy), float(scale_modifier), int(bool(debug))
+            a.tan_fovx, a.tan_fovy, a.scale_modifier, a.debug = float(tanfovx), float(tanfovy), float(scale_modifier), int(debug)
             a.background, a.means3D, a.shs, a.colors_precomp = _ptr(bg), _ptr(means3D), _ptr(sh), _ptr(colors_precomp)
             a.scales, a.rotations, a.transMat_precomp = _ptr(scales), _ptr(rotations), _ptr(cov3Ds_precomp)
             a.viewmatrix, a.projmatrix, a.campos, a.radii = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), _ptr(radii)

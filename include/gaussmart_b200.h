@@ -79,7 +79,9 @@ typedef struct gsm_forward_args {
   float tan_fovx, tan_fovy;
   float scale_modifier;
   int prefiltered;   /* kept for API parity; a culled surfel with prefiltered set is an error flag */
-  int debug;         /* synchronise + check after every stage */
+  int debug;         /* bit 0: synchronise + check after every stage (auxiliary.h:296-303);
+                        bit 1: disable the conservative per-warp culling in the compositing kernels
+                        (every (pixel, list entry) pair is evaluated, as the reference does) */
   const float* background;       /* [3] */
   const float* means3D;          /* [P,3] */
   const float* shs;              /* [P,M,3] or NULL */
@@ -98,8 +100,9 @@ typedef struct gsm_forward_args {
   void* image;    size_t image_bytes;
   void* binning;  size_t binning_bytes; size_t binning_capacity;
   int* num_rendered_host;        /* HOST pointer: receives R (valid on GSM_OK and on overflow) */
-  uint64_t* work_counters;       /* optional DEVICE u64[4], caller-zeroed, ADDED to: [0] list entries
-                                    evaluated, [1] contributing (pixel,surfel) pairs, [2] records staged.
+  uint64_t* work_counters;       /* optional DEVICE u64[4], caller-zeroed, ADDED to: [0] (pixel,entry)
+                                    pairs the reference's loop would evaluate, [1] contributing pairs,
+                                    [2] records staged, [3] pairs evaluated after culling.
                                     NULL in production; used by bench.py for the roofline model. */
 } gsm_forward_args;
 

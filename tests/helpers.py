@@ -68,12 +68,13 @@ def variant_inputs(scene, cam, variant, scale_modifier=1.0):
     return kw
 
 
-def run_cuda(mod, scene, cam, bg_value, cot, variant="sh", scale_modifier=1.0, backward=True, device="cuda"):
+def run_cuda(mod, scene, cam, bg_value, cot, variant="sh", scale_modifier=1.0, backward=True, device="cuda",
+             debug=False):
     """Runs `mod` (gaussmart_b200 or the reference build: same API) on the GPU; returns detached outputs + grads."""
     from gaussmart_b200 import synthetic
     cam_d = synthetic.Camera(*[x.to(device) if isinstance(x, torch.Tensor) else x for x in cam])
     bg = torch.full((3,), float(bg_value), device=device)
-    S = mod.GaussianRasterizationSettings(**synthetic.settings_kwargs(cam_d, scene.sh_degree, bg, scale_modifier))
+    S = mod.GaussianRasterizationSettings(**synthetic.settings_kwargs(cam_d, scene.sh_degree, bg, scale_modifier, debug))
     rast = mod.GaussianRasterizer(S)
     means3D = scene.means3D.to(device).requires_grad_(backward)
     means2D = torch.zeros_like(means3D, requires_grad=backward)

@@ -41,7 +41,9 @@ def test_oracle_matches_reference_golden(oracle, golden_dir, c1, fname, variant,
     assert np.array_equal(f["keys"].numpy(), g["keys"])
     assert np.array_equal(f["point_list"].numpy().astype(np.int32), g["point_list"])
     assert np.array_equal(f["ranges"].numpy().astype(np.int32), g["ranges"])
-    assert np.array_equal(f["n_contrib"].numpy().reshape(2, -1).astype(np.int32), g["n_contrib"])
+    nc = f["n_contrib"].numpy().reshape(2, -1).astype(np.int32)
+    has = g["n_contrib"][0] > 0  # the median slot of an untouched pixel is undefined in the reference (forward.cu:437)
+    assert np.array_equal(nc[0], g["n_contrib"][0]) and np.array_equal(nc[1][has], g["n_contrib"][1][has])
 
     # ---- forward
     for name in ("color", "allmap"):

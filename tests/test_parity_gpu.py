@@ -39,7 +39,9 @@ def test_cuda_matches_reference_golden(golden_dir, fname, variant, bg):
     assert np.array_equal(im["keys"].cpu().numpy(), g["keys"])
     assert np.array_equal(im["point_list"].cpu().numpy(), g["point_list"])
     assert np.array_equal(im["ranges"].cpu().numpy(), g["ranges"])
-    assert np.array_equal(im["n_contrib"].cpu().numpy(), g["n_contrib"])
+    nc = im["n_contrib"].cpu().numpy()
+    has = g["n_contrib"][0] > 0
+    assert np.array_equal(nc[0], g["n_contrib"][0]) and np.array_equal(nc[1][has], g["n_contrib"][1][has])
     assert fwd_close(o["color"].cpu(), g["color"]).all()
     assert fwd_close(o["allmap"].cpu(), g["allmap"]).all()
     assert fwd_close(im["final_T"].cpu(), g["final_T"]).all()
@@ -81,15 +83,23 @@ def test_cuda_matches_oracle_small(oracle, name, P, W, H, deg, variant, bg, mod,
     scene = scene._replace(scales=scene.scales * 3.0)
     cam = synthetic.make_camera(W, H, 0.3, fovx=_truncating_fov(W) if fov == "truncating" else None)
     cot = synthetic.make_cotangents(W, H, 99)
+    # vs the CPU oracle a tiny mismatch budget on integer outputs (ceil / rect boundary cases: the CPU
+    # cannot reproduce rsqrt.approx); such surfels are dropped from the scene so that
+    # everything downstream can be compared exactly.  (vs the reference BUILD the budget is zero.)
+    o = run_cuda(gb, scene, cam, bg, None, variant, mod, backward=False)
+    f, _ = run_oracle(oracle, scene, cam, bg, None, variant, mod)
+    keep = o["radii"].cpu() == f["radii"]
+    assert (~keep).sum().item() <= max(1, P // 500)
+    if not keep.all():
+        scene = scene._replace(means3D=scene.means3D[keep].contiguous(), scales=scene.scales[keep].contiguous(),
+                               rotations=scene.rotations[keep].contiguous(), opacities=scene.opacities[keep].contiguous(),
+                               shs=scene.shs[keep].contiguous())
     o = run_cuda(gb, scene, cam, bg, cot, variant, mod)
     f, grads = run_oracle(oracle, scene, cam, bg, cot, variant, mod)
     if fov == "truncating":
         assert oracle.bwd_image_size(W, H, cam.tanfovx, cam.tanfovy)[0] == W - 1
     rad = o["radii"].cpu()
-    # vs the oracle a tiny mismatch budget on integer outputs (ceil boundary cases)
-    assert (rad != f["radii"]).sum().item() <= max(1, P // 2000)
-    if (rad != f["radii"]).any():
-        pytest.skip("integer boundary case differs from the CPU oracle; float comparison not meaningful")
+    assert torch.equal(rad, f["radii"])
     im = intermediates(o["settings"], scene, cam, variant, mod)
     assert im["num_rendered"] == f["num_rendered"]
     assert torch.equal(im["keys"].cpu(), f["keys"])
@@ -205,4 +215,42 @@ def test_cuda_matches_reference_build(cfg, P, variant, bg):
     pl, keys = ref_loader.ref_binning_views(binB, R_ref)
     assert torch.equal(keys, im["keys"]) and torch.equal(pl, im["point_list"])
     acc, nc, rg = ref_loader.ref_image_views(imgB, W, H)
-    assert torch.equal(rg, im["ranges"]) and torch.equal(nc, im["n_contrib"])
+    assert torch.equal(rg, im["ranges"]) and torch.equal(nc[0], im["n_contrib"][0])
+    # the median contributor of a pixel nothing contributed to is (uint32_t)(-1.0f) in the reference
+    # (forward.cu:437): undefined, garbage in its sm_100a build; it is only read where last_contributor > 0
+    has = nc[0] > 0
+    assert torch.equal(nc[1][has], im["n_contrib"][1][has])
+
+
+CULL_SCENES = [  # name, P, W, H, scale multiplier, z squeeze (pushes surfels through the near/camera plane)
+    ("bench_like", 200_000, 640, 480, 1.0, 1.0),
+    ("big_splats", 20_000, 320, 240, 8.0, 1.0),
+    ("huge_splats_near_plane", 5_000, 200, 160, 60.0, 0.25),
+    ("needles", 50_000, 320, 240, 1.0, 1.0),
+]
+
+
+@pytest.mark.parametrize("name,P,W,H,smul,zs", CULL_SCENES, ids=[c[0] for c in CULL_SCENES])
+def test_conservative_culling_changes_nothing(name, P, W, H, smul, zs):
+    """The per-warp contribution-box culling (common.cuh CULL_RHO) may only skip pairs that cannot pass
+    the reference's alpha test: rendering with it disabled (debug bit 1) must give identical bits for
+    every output, and gradients equal up to atomic ordering."""
+    scene = synthetic.make_scene(P, W, 1, 4000 + P)
+    sc = scene.scales * smul
+    if name == "needles":  # extreme anisotropy: edge-on / line-like footprints
+        sc = torch.stack([scene.scales[:, 0] * 20.0, scene.scales[:, 1] * 0.02], 1)
+    m = scene.means3D.clone()
+    m[:, 2] = (m[:, 2] - 4.0) * zs + 4.0 * zs
+    scene = scene._replace(scales=sc, means3D=m)
+    cam = synthetic.make_camera(W, H, 0.1)
+    cot = synthetic.make_cotangents(W, H, 3)
+    a = run_cuda(gb, scene, cam, 0.0, cot, "sh")
+    b = run_cuda(gb, scene, cam, 0.0, cot, "sh", debug=2)
+    assert (a["radii"] > 0).sum().item() > 0
+    assert torch.equal(a["radii"], b["radii"])
+    assert torch.equal(a["color"], b["color"])
+    assert torch.equal(a["allmap"], b["allmap"])
+    for k in a:
+        if k.startswith("grad_") and a[k] is not None:
+            viol, _ = grad_violations(a[k].cpu(), b[k].cpu(), rel=1e-4, floor=1e-6)
+            assert viol <= 1e-5 * a[k].numel() + 1, (k, viol)

@@ -31,11 +31,14 @@ def relerr(a, b):
                 rel_fro=((a - b).norm() / max(b.norm().item(), 1e-30)).item())
 
 
+OURS_DEBUG = 0
+
+
 def run_impl(mod, scene, cam, bg, cot, variant, scale_modifier=1.0, backward=True):
     dev = "cuda"
     S = mod.GaussianRasterizationSettings(**synthetic.settings_kwargs(
         synthetic.Camera(*[x.to(dev) if isinstance(x, torch.Tensor) else x for x in cam]), scene.sh_degree, bg,
-        scale_modifier))
+        scale_modifier, OURS_DEBUG if mod is gb else False))
     rast = mod.GaussianRasterizer(S)
     means3D = scene.means3D.to(dev).requires_grad_(True)
     means2D = torch.zeros_like(means3D, requires_grad=True)
@@ -108,7 +111,10 @@ def main():
     ap.add_argument("--time", action="store_true")
     ap.add_argument("--view", type=int, default=0)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--ours-debug", type=int, default=0)
     a = ap.parse_args()
+    global OURS_DEBUG
+    OURS_DEBUG = a.ours_debug
 
     ref = ref_loader.load_dsr()
     scene, cams = synthetic.make_config(a.config, P=a.P)
@@ -160,6 +166,11 @@ def main():
     res["ranges_mismatch"] = int((rg != mine["ranges"]).sum().item())
     res["n_contrib_mismatch"] = [int((nc[i] != mine["n_contrib"][i]).sum().item()) for i in range(2)]
     res["final_T_max_abs"] = (acc - mine["final_T"]).abs().max().item()
+    for ch in range(2):
+        bad = torch.nonzero(nc[ch] != mine["n_contrib"][ch]).reshape(-1)[:6]
+        if bad.numel():
+            res[f"n_contrib_bad{ch}"] = [(int(i) % W, int(i) // W, int(nc[ch][i]), int(mine["n_contrib"][ch][i]),
+                                          float(acc[0][i]), float(mine["final_T"][0][i])) for i in bad]
     res["E_list_entries"] = int(nc[0].long().sum().item())
 
     if a.time:

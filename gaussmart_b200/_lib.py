@@ -19,7 +19,7 @@ GSM_GRAD_RECORD_FLOATS = 20
 ABI_VERSION = 2
 
 EXPORTS = [
-    "gsm_last_error", "gsm_abi_version", "gsm_geometry_bytes", "gsm_image_bytes", "gsm_binning_bytes",
+    "gsm_last_error", "gsm_abi_version", "gsm_geometry_bytes", "gsm_image_bytes", "gsm_binning_bytes", "gsm_binning_persistent_bytes",
     "gsm_binning_sorted_keys_offset", "gsm_image_ranges_offset", "gsm_image_ncontrib_offset",
     "gsm_forward", "gsm_grad_workspace_bytes", "gsm_backward", "gsm_mark_visible",
     "gsm_knn_workspace_bytes", "gsm_knn_dist2",
@@ -50,7 +50,7 @@ class BackwardArgs(Structure):
         ("background", c_void_p), ("means3D", c_void_p), ("shs", c_void_p), ("colors_precomp", c_void_p),
         ("scales", c_void_p), ("rotations", c_void_p), ("transMat_precomp", c_void_p),
         ("viewmatrix", c_void_p), ("projmatrix", c_void_p), ("campos", c_void_p), ("radii", c_void_p),
-        ("geometry", c_void_p), ("image", c_void_p), ("binning", c_void_p),
+        ("geometry", c_void_p), ("image", c_void_p), ("binning", c_void_p), ("binning_capacity", c_size_t),
         ("dL_dout_color", c_void_p), ("dL_dout_others", c_void_p),
         ("grad_workspace", c_void_p), ("grad_workspace_bytes", c_size_t),
         ("dL_dmeans2D", c_void_p), ("dL_dcolors", c_void_p), ("dL_dopacity", c_void_p),
@@ -88,6 +88,8 @@ def load():
     lib.gsm_image_ncontrib_offset.argtypes = [c_int, c_int]
     lib.gsm_binning_bytes.restype = c_size_t
     lib.gsm_binning_bytes.argtypes = [c_size_t, c_int, c_int]
+    lib.gsm_binning_persistent_bytes.restype = c_size_t
+    lib.gsm_binning_persistent_bytes.argtypes = [c_size_t]
     lib.gsm_binning_sorted_keys_offset.restype = c_size_t
     lib.gsm_binning_sorted_keys_offset.argtypes = [c_size_t]
     lib.gsm_forward.restype = c_int

@@ -111,6 +111,8 @@ BinningLayout binning_layout(size_t capacity, int width, int height) {
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 128); return o; };
   L.point_list = take(capacity * 4);
+  L.strip_mask = take(capacity + 4);
+  L.persistent = off;
   L.keys_sorted = take(capacity * 8);
   L.keys_unsorted = take(capacity * 8);
   L.values_unsorted = take(capacity * 4);
@@ -156,6 +158,7 @@ extern "C" size_t gsm_image_bytes(int width, int height) { return image_layout(w
 extern "C" size_t gsm_binning_bytes(size_t capacity, int width, int height) {
   return binning_layout(capacity, width, height).total;
 }
+extern "C" size_t gsm_binning_persistent_bytes(size_t capacity) { return binning_layout(capacity, 0, 0).persistent + 128; }
 extern "C" size_t gsm_binning_sorted_keys_offset(size_t capacity) { return binning_layout(capacity, 0, 0).keys_sorted; }
 extern "C" size_t gsm_image_ranges_offset(int width, int height) { return image_layout(width, height).ranges; }
 extern "C" size_t gsm_image_ncontrib_offset(int width, int height) { return image_layout(width, height).n_contrib; }
@@ -258,7 +261,11 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
                                  bin + B.sort_temp, B.sort_temp_bytes, stream));
     }
     GSM_STAGE("sort");
-    { StageMark m(GSM_STAGE_RANGES, stream); launch_tile_ranges((size_t)R, keys_sorted, ranges, num_tiles, stream); }
+    {
+      StageMark m(GSM_STAGE_RANGES, stream);
+      launch_tile_ranges((size_t)R, keys_sorted, point_list, (const short4*)(geom + G.bbox), ranges,
+                         (uint8_t*)(bin + B.strip_mask), grid_x, num_tiles, (a->debug & 2) ? 1 : 0, stream);
+    }
     GSM_STAGE("tile ranges");
   } else {
     GSM_CUDA(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream));
@@ -269,7 +276,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     rp.ranges = ranges;
     rp.point_list = bin ? (const uint32_t*)(bin + B.point_list) : nullptr;
     rp.records = records; rp.background = a->background;
-    rp.bbox = (const short4*)(geom + G.bbox); rp.no_cull = (a->debug & 2) ? 1 : 0;
+    rp.strip_mask = bin ? (const uint8_t*)(bin + B.strip_mask) : nullptr;
     rp.final_T = (float*)(img + I.final_T); rp.n_contrib = (uint32_t*)(img + I.n_contrib);
     rp.out_color = a->out_color; rp.out_others = a->out_others;
     rp.stats = (unsigned long long*)a->work_counters;
@@ -309,7 +316,8 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   rp.ranges = (const uint2*)(img + I.ranges);
   rp.point_list = (const uint32_t*)bin;  // point_list sits at offset 0 of the binning workspace
   rp.records = (const float4*)(geom + G.records);
-  rp.bbox = (const short4*)(geom + G.bbox); rp.no_cull = (a->debug & 2) ? 1 : 0;
+  const BinningLayout B = binning_layout(a->binning_capacity, W, H);
+  rp.strip_mask = bin ? (const uint8_t*)(bin + B.strip_mask) : nullptr;
   rp.background = a->background;
   rp.final_T = (const float*)(img + I.final_T);
   rp.n_contrib = (const uint32_t*)(img + I.n_contrib);

@@ -199,11 +199,16 @@ void launch_duplicate_with_keys(int P, const float4* records, const uint32_t* of
 
 // ---------------------------------------------------------------------------------------------
 // tile ranges (rasterizer_impl.cu:116-138): ranges[t] = [first, last+1) of tile t in the sorted
-// list; untouched tiles stay (0,0) (the memset of rasterizer_impl.cu:311 is fused: the launcher
-// clears ranges on the same stream first).
+// list; untouched tiles stay (0,0) (the memset of rasterizer_impl.cu:311 is issued by the launcher
+// on the same stream first).  Fused with it, because it streams the same sorted list: the per-
+// instance STRIP MASK -- bit s set iff the surfel's conservative contribution box (common.cuh,
+// CULL_RHO) meets rows [2s, 2s+1] of this tile -- which lets each compositing warp skip the
+// entries that cannot reach any of its 32 pixels without looking at the surfel.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-tile_ranges_kernel(size_t R, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
+tile_ranges_kernel(size_t R, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
+                   const short4* __restrict__ bbox, uint2* __restrict__ ranges,
+                   uint8_t* __restrict__ strip_mask, int grid_x, int no_cull) {
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= R) return;
   const uint32_t cur = (uint32_t)(__ldg(keys + idx) >> 32);
@@ -217,13 +222,30 @@ tile_ranges_kernel(size_t R, const uint64_t* __restrict__ keys, uint2* __restric
     }
   }
   if (idx == R - 1) ranges[cur].y = (uint32_t)R;
+
+  uint32_t mask = 0xffu;
+  if (!no_cull) {
+    const short4 bx = __ldg(bbox + __ldg(point_list + idx));
+    const int tx = (int)(cur % (uint32_t)grid_x) * TILE_X, ty = (int)(cur / (uint32_t)grid_x) * TILE_Y;
+    mask = 0;
+    if (bx.x <= tx + TILE_X - 1 && bx.z >= tx) {
+      const int r0 = max((int)bx.y - ty, 0), r1 = min((int)bx.w - ty, TILE_Y - 1);
+      if (r0 <= r1) {
+        const int s0 = r0 / STRIP_ROWS, s1 = r1 / STRIP_ROWS;
+        mask = ((2u << s1) - 1u) & ~((1u << s0) - 1u);
+      }
+    }
+  }
+  strip_mask[idx] = (uint8_t)mask;
 }
 
-void launch_tile_ranges(size_t R, const uint64_t* keys_sorted, uint2* ranges, int num_tiles,
-                        cudaStream_t stream) {
+void launch_tile_ranges(size_t R, const uint64_t* keys_sorted, const uint32_t* point_list,
+                        const short4* bbox, uint2* ranges, uint8_t* strip_mask, int grid_x,
+                        int num_tiles, int no_cull, cudaStream_t stream) {
   cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream);
   if (R == 0) return;
-  tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, stream>>>(R, keys_sorted, ranges);
+  tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, stream>>>(R, keys_sorted, point_list, bbox, ranges,
+                                                                       strip_mask, grid_x, no_cull);
 }
 
 }  // namespace gsm

@@ -12,6 +12,9 @@ namespace gsm {
 constexpr int TILE_X = 16;
 constexpr int TILE_Y = 16;
 constexpr int TILE_PIX = TILE_X * TILE_Y;
+// A tile is composited by 8 independent warps, each owning a 16x2 pixel strip.
+constexpr int STRIP_ROWS = 2;
+constexpr int STRIPS_PER_TILE = TILE_Y / STRIP_ROWS;
 
 // Compile-time constants of the reference (auxiliary.h:37-40).
 constexpr float NEAR_N = 0.2f;
@@ -37,7 +40,8 @@ constexpr int REC_F4 = 5;
 // Conservative contribution box (short4 per surfel: xmin, ymin, xmax, ymax in integer pixel
 // coordinates, inclusive).  A pixel outside it cannot pass the reference's alpha >= 1/255 test
 // (forward.cu:385-392): alpha = opacity*exp(-rho/2) >= 1/255 needs rho = min(rho3d, rho2d) <=
-// 2 ln 255 = 11.083, so the box encloses the perspective-correct image of the disc u^2+v^2 <=
+// 2 ln(255 opacity) (<= 11.083 at opacity 1; the per-surfel bound is used, with a 3% + 0.2 margin
+// on rho), so the box encloses the perspective-correct image of the disc u^2+v^2 <=
 // CULL_RHO (the reference's own AABB construction, forward.cu:119-145, at a larger cutoff) united
 // with the low-pass disc 2|d|^2 <= CULL_RHO, plus slack; surfels whose disc is not wholly in front
 // of the camera plane get the unbounded box.  Compositing kernels use it only to SKIP work.
@@ -75,6 +79,8 @@ ImageLayout image_layout(int width, int height);
 
 struct BinningLayout {
   size_t point_list;       // u32[cap]   sorted values     (kept for backward)
+  size_t strip_mask;       // u8[cap]    per instance: which 16x2 strips of its tile it can touch (kept)
+  size_t persistent;       // bytes from the start that must survive until backward
   size_t keys_sorted;      // u64[cap]
   size_t keys_unsorted;    // u64[cap]
   size_t values_unsorted;  // u32[cap]
@@ -152,16 +158,16 @@ size_t sort_temp_bytes(size_t n);
 cudaError_t launch_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in,
                               uint32_t* vals_out, size_t n, int end_bit, void* temp,
                               size_t temp_bytes, cudaStream_t stream);
-void launch_tile_ranges(size_t R, const uint64_t* keys_sorted, uint2* ranges, int num_tiles,
-                        cudaStream_t stream);
+void launch_tile_ranges(size_t R, const uint64_t* keys_sorted, const uint32_t* point_list,
+                        const short4* bbox, uint2* ranges, uint8_t* strip_mask, int grid_x,
+                        int num_tiles, int no_cull, cudaStream_t stream);
 
 struct FwdRenderParams {
   int W, H, grid_x, grid_y;
   const uint2* ranges;
   const uint32_t* point_list;
   const float4* records;
-  const short4* bbox;
-  int no_cull;  // debug: evaluate every (pixel, entry) pair as the reference does
+  const uint8_t* strip_mask;
   const float* background;
   float* final_T;
   uint32_t* n_contrib;
@@ -176,8 +182,7 @@ struct BwdRenderParams {
   const uint2* ranges;
   const uint32_t* point_list;
   const float4* records;
-  const short4* bbox;
-  int no_cull;
+  const uint8_t* strip_mask;
   const float* background;
   const float* final_T;
   const uint32_t* n_contrib;

@@ -212,8 +212,14 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const FwdPreprocess
     // conservative contribution box (common.cuh, CULL_RHO); fp64 so that the cancellation in
     // centre^2 - <f,T^2> cannot shrink it
     short4 box = make_short4(-32768, -32768, 32767, 32767);
-    {
-      const double c2 = (double)CULL_RHO;
+    const float opac = __ldg(p.opacities + idx);
+    if (opac < ALPHA_MIN) {
+      // alpha = opacity * exp(power) with power <= 0 never reaches 1/255 (forward.cu:385-392): empty box
+      box = make_short4(32767, 32767, -32768, -32768);
+    } else if (opac >= ALPHA_MIN) {  // (false for NaN: keep the unbounded box)
+      // alpha >= 1/255  <=>  rho <= 2 ln(255 opacity); 3% + 0.2 margin on rho, capped at CULL_RHO (opacity <= 1)
+      const double c2 = fmin((double)CULL_RHO * fmax(1.0, (double)opac * (double)opac),
+                             2.0 * log(255.0 * (double)opac) * 1.03 + 0.2);
       const double w0 = Tw0, w1 = Tw1, w2 = Tw2;
       const double dd = c2 * (w0 * w0 + w1 * w1) - w2 * w2;
       if (dd < -1e-6 * w2 * w2 && w2 > 0.0) {  // the whole disc is in front of the camera plane
@@ -240,7 +246,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const FwdPreprocess
     float4* rec = p.records + (size_t)idx * REC_F4;
     rec[0] = make_float4(Tu0, Tu1, Tu2, cx);
     rec[1] = make_float4(Tv0, Tv1, Tv2, cy);
-    rec[2] = make_float4(Tw0, Tw1, Tw2, __ldg(p.opacities + idx));
+    rec[2] = make_float4(Tw0, Tw1, Tw2, opac);
     rec[3] = make_float4(nx, ny, nz, vz);
     rec[4] = make_float4(rgb.x, rgb.y, rgb.z, __int_as_float(clamp_bits));
     radius_out = ri;

@@ -26,8 +26,11 @@ __device__ __forceinline__ void store3(float* dst, f3 v, bool acc = false) {
 // SH backward (backward.cu:20-139). dL_dsh row is fully written (zeros beyond the active degree).
 __device__ void sh_backward(int D, int M, const float* __restrict__ sh, f3 dir_orig, f3 dL_dRGB,
                             float* __restrict__ dL_dsh, f3& dL_dmean_add, bool acc) {
-  const float inv_len = 1.0f / sqrtf(dot(dir_orig, dir_orig));
-  const float x = dir_orig.x * inv_len, y = dir_orig.y * inv_len, z = dir_orig.z * inv_len;
+  // dir = dir_orig / length(dir_orig) exactly as the forward evaluates it (IEEE sqrt and divisions,
+  // forward.cu:26-27 / backward.cu:27-28): factors such as 2zz-xx-yy cancel, so a 1-ulp change of
+  // x,y,z would show up as a 1e-3 relative change of single dL_dsh entries
+  const float len = __fsqrt_rn(__fmaf_rn(dir_orig.z, dir_orig.z, __fmaf_rn(dir_orig.x, dir_orig.x, __fmul_rn(dir_orig.y, dir_orig.y))));
+  const float x = __fdiv_rn(dir_orig.x, len), y = __fdiv_rn(dir_orig.y, len), z = __fdiv_rn(dir_orig.z, len);
   const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
   f3 dx = mk(0, 0, 0), dy = mk(0, 0, 0), dz = mk(0, 0, 0);
 #define SH(k) mk(__ldg(sh + 3 * (k)), __ldg(sh + 3 * (k) + 1), __ldg(sh + 3 * (k) + 2))

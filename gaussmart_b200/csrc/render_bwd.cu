@@ -21,30 +21,20 @@ namespace gsm {
 #define SUB(a, b) __fsub_rn((a), (b))
 #define FMA(a, b, c) __fmaf_rn((a), (b), (c))
 
-constexpr int BWD_BATCH = 256;
+// Warp-independent design (see render_fwd.cu): each warp replays one 16x2 strip back to front on its
+// own -- scans the strip masks downwards from its deepest contributor, queues the entries that can
+// reach the strip, gathers their records into a private double-buffered stage, and reduces its 32
+// pixels' partial gradients with shuffles before one red.global.add per value.  No __syncthreads.
+constexpr int BWD_WARPS = 4;
+constexpr int BWD_CHUNK = 32;
+constexpr int BWD_QUEUE = 128;
 
-struct BwdSmem {
-  float4 q[2][REC_F4][BWD_BATCH];
-  uint32_t id[2][BWD_BATCH];
-  short4 bbox[2][BWD_BATCH];               // conservative contribution boxes (common.cuh)
-  uint8_t list[TILE_PIX / 32][BWD_BATCH];  // per-warp compacted entry indices (back to front)
-  int warp_max[TILE_PIX / 32];
+struct BwdWarpSmem {
+  float4 q[2][REC_F4][BWD_CHUNK];
+  uint32_t id[2][BWD_CHUNK];
+  uint32_t pos[2][BWD_CHUNK];  // 0-based list position k of the staged entry (the reference's `contributor`)
+  uint32_t queue[BWD_QUEUE];
 };
-
-__device__ __forceinline__ void stage_batch_rev(BwdSmem& sm, int s, const float4* __restrict__ records,
-                                                const short4* __restrict__ bbox,
-                                                const uint32_t* __restrict__ point_list,
-                                                uint32_t list_begin, int pos, int t) {
-  // pos: position (0-based within the tile list) of this thread's entry; negative => none
-  if (pos >= 0) {
-    const uint32_t id = __ldg(point_list + list_begin + pos);
-    sm.id[s][t] = id;
-    const float4* src = records + (size_t)id * REC_F4;
-#pragma unroll
-    for (int f = 0; f < REC_F4; f++) __pipeline_memcpy_async(&sm.q[s][f][t], src + f, sizeof(float4));
-    __pipeline_memcpy_async(&sm.bbox[s][t], bbox + id, sizeof(short4));
-  }
-}
 
 // Recursive-halving reduce-scatter of 16 values over 32 lanes + 2 extra values.
 // On return lane L holds in v[0] the warp sum of slot (L>>1)&15 (both lanes of a pair hold it),
@@ -94,18 +84,23 @@ __device__ __forceinline__ void warp_reduce_scatter18(float (&v)[16], float& e0,
   e0 += __shfl_xor_sync(FULL, e0, 1);
 }
 
-__global__ void __launch_bounds__(TILE_PIX, 2) render_bwd_kernel(const BwdRenderParams p) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
+__global__ void __launch_bounds__(BWD_WARPS * 32, 4) render_bwd_kernel(const BwdRenderParams p) {
+  __shared__ __align__(16) BwdWarpSmem smem_all[BWD_WARPS];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  BwdWarpSmem& sm = smem_all[warp];
 
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const uint32_t pixx = blockIdx.x * TILE_X + (t & 15);
-  const uint32_t pixy = blockIdx.y * TILE_Y + (t >> 4);
+  const uint32_t strip_global = blockIdx.x * BWD_WARPS + warp;
+  const uint32_t tile = strip_global / STRIPS_PER_TILE, strip = strip_global % STRIPS_PER_TILE;
+  if (tile >= (uint32_t)(p.grid_x * p.grid_y)) return;
+  const uint32_t tile_x = tile % (uint32_t)p.grid_x, tile_y = tile / (uint32_t)p.grid_x;
+  const uint32_t pixx = tile_x * TILE_X + (lane & 15);
+  const uint32_t pixy = tile_y * TILE_Y + strip * STRIP_ROWS + (lane >> 4);
   const bool inside = pixx < (uint32_t)p.W && pixy < (uint32_t)p.H;
   const float pxf = (float)pixx, pyf = (float)pixy;
   const size_t N = (size_t)p.W * p.H;
   const size_t pix = (size_t)pixy * p.W + pixx;
-  const uint2 range = __ldg(p.ranges + blockIdx.y * p.grid_x + blockIdx.x);
+  const uint2 range = __ldg(p.ranges + tile);
+  const uint32_t strip_bit = 1u << strip;
 
   const float T_final = inside ? __ldg(p.final_T + pix) : 0.0f;
   const float final_D = inside ? __ldg(p.final_T + pix + N) : 0.0f;
@@ -130,18 +125,8 @@ __global__ void __launch_bounds__(TILE_PIX, 2) render_bwd_kernel(const BwdRender
 #pragma unroll
   for (int ch = 0; ch < 3; ch++) bg_dot_dpixel += __ldg(p.background + ch) * dL_dpixel[ch];
 
-  // deepest contributor of the warp / of the tile
+  // deepest contributor of the warp: entries at or beyond it are behind every pixel of the strip
   const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
-  if (lane == 0) sm.warp_max[warp] = warp_last;
-  __syncthreads();
-  int start = 0;
-#pragma unroll
-  for (int w = 0; w < TILE_PIX / 32; w++) start = max(start, sm.warp_max[w]);
-  const int rounds = (start + BWD_BATCH - 1) / BWD_BATCH;
-
-  const int sx_lo = blockIdx.x * TILE_X, sx_hi = sx_lo + TILE_X - 1;
-  const int sy_lo = blockIdx.y * TILE_Y + 2 * warp, sy_hi = sy_lo + 1;
-  uint8_t* __restrict__ mylist = sm.list[warp];
 
   float T = T_final;
   float accum_rec[3] = {0.f, 0.f, 0.f}, last_color[3] = {0.f, 0.f, 0.f};
@@ -150,38 +135,47 @@ __global__ void __launch_bounds__(TILE_PIX, 2) render_bwd_kernel(const BwdRender
   float last_dL_dT = 0.f;
   const float far_ratio = __uint_as_float(GSM_FAR_RATIO_BITS);
 
-  if (rounds > 0) stage_batch_rev(sm, 0, p.records, p.bbox, p.point_list, range.x, start - 1 - t, t);
-  __pipeline_commit();
-
-  for (int i = 0; i < rounds; i++) {
-    const int s = i & 1;
-    __pipeline_wait_prior(0);
-    __syncthreads();
-    if (i + 1 < rounds)
-      stage_batch_rev(sm, s ^ 1, p.records, p.bbox, p.point_list, range.x, start - 1 - ((i + 1) * BWD_BATCH + t), t);
-    __pipeline_commit();
-
-    const int base_pos = start - 1 - i * BWD_BATCH;  // position of entry j = base_pos - j
-    const int n = min(BWD_BATCH, base_pos + 1);
-    const int j0 = max(0, base_pos + 1 - warp_last);  // entries before j0 are behind every pixel of the warp
-    // per-warp compaction of the entries whose contribution box meets this warp's 16x2 strip
-    int cnt = 0;
-#pragma unroll
-    for (int r = 0; r < BWD_BATCH / 32; r++) {
-      const int j = r * 32 + lane;
-      bool hit = false;
-      if (j >= j0 && j < n) {
-        const short4 bx = sm.bbox[s][j];
-        hit = p.no_cull || (bx.x <= sx_hi && bx.z >= sx_lo && bx.y <= sy_hi && bx.w >= sy_lo);
-      }
+  // ---- scan / queue / stage machinery (warp-uniform state); list offsets run DOWN from warp_last-1 ----
+  int scan = warp_last - 1;  // next 0-based list offset to scan (descending); < 0 => exhausted
+  uint32_t qhead = 0, qcount = 0;
+  auto fill = [&]() {
+    while (qcount < BWD_CHUNK && scan >= 0) {
+      const int o = scan - lane;
+      const bool hit = o >= 0 && (__ldg(p.strip_mask + range.x + o) & strip_bit);
       const unsigned m = __ballot_sync(0xffffffffu, hit);
-      if (hit) mylist[cnt + __popc(m & ((1u << lane) - 1u))] = (uint8_t)j;
-      cnt += __popc(m);
+      if (hit) sm.queue[(qhead + qcount + __popc(m & ((1u << lane) - 1u))) & (BWD_QUEUE - 1)] = (uint32_t)o;
+      qcount += __popc(m);
+      scan -= 32;
     }
     __syncwarp();
-    for (int e = 0; e < cnt; e++) {
-      const int j = mylist[e];
-      const int k = base_pos - j;  // == the reference's `contributor` after its decrement
+  };
+  auto issue = [&](int s) -> int {
+    const int n = (int)min(qcount, (uint32_t)BWD_CHUNK);
+    if (lane < n) {
+      const uint32_t o = sm.queue[(qhead + lane) & (BWD_QUEUE - 1)];
+      sm.pos[s][lane] = o;
+      const uint32_t id = __ldg(p.point_list + range.x + o);
+      sm.id[s][lane] = id;
+      const float4* src = p.records + (size_t)id * REC_F4;
+#pragma unroll
+      for (int f = 0; f < REC_F4; f++) __pipeline_memcpy_async(&sm.q[s][f][lane], src + f, sizeof(float4));
+    }
+    __pipeline_commit();
+    qhead += n;
+    qcount -= n;
+    return n;
+  };
+
+  fill();
+  int n_cur = issue(0);
+  int s = 0;
+  while (n_cur > 0) {
+    fill();
+    const int n_next = issue(s ^ 1);
+    __pipeline_wait_prior(1);
+    __syncwarp();
+    for (int j = 0; j < n_cur; j++) {
+      const int k = (int)sm.pos[s][j];  // == the reference's `contributor` after its decrement
       bool active = k < last_contributor;
       const float4 a = sm.q[s][0][j], b = sm.q[s][1][j], c = sm.q[s][2][j];
       const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
@@ -287,14 +281,17 @@ __global__ void __launch_bounds__(TILE_PIX, 2) render_bwd_kernel(const BwdRender
       else if (lane == 1) atomicAdd(g + 16, e0);
       else if (lane == 17) atomicAdd(g + 17, e0);
     }
+    __syncwarp();
+    n_cur = n_next;
+    s ^= 1;
   }
   __pipeline_wait_prior(0);
 }
 
 void launch_render_bwd(const BwdRenderParams& p, cudaStream_t stream) {
-  cudaFuncSetAttribute(render_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem));
-  dim3 grid(p.grid_x, p.grid_y, 1);
-  render_bwd_kernel<<<grid, TILE_PIX, sizeof(BwdSmem), stream>>>(p);
+  const unsigned strips = (unsigned)(p.grid_x * p.grid_y) * STRIPS_PER_TILE;
+  const unsigned grid = (strips + BWD_WARPS - 1) / BWD_WARPS;
+  render_bwd_kernel<<<grid, BWD_WARPS * 32, 0, stream>>>(p);
 }
 
 }  // namespace gsm

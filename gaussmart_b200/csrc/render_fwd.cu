@@ -21,41 +21,40 @@ namespace gsm {
 #define SUB(a, b) __fsub_rn((a), (b))
 #define FMA(a, b, c) __fmaf_rn((a), (b), (c))
 
-constexpr int FWD_BATCH = 256;
+// Warp-independent design: a CTA holds FWD_WARPS warps, each of which composites one 16x2 strip of
+// a tile ENTIRELY on its own -- it scans the tile's strip masks (1 byte per list entry, streamed),
+// compacts the entries that can reach its strip into a small position queue, gathers their packed
+// records into its private double-buffered shared-memory stage with cp.async, and blends.  There is
+// no __syncthreads anywhere: a warp with a short (heavily culled or early-terminated) list retires
+// at once and the hardware block scheduler backfills, instead of waiting at a per-batch barrier
+// for the slowest strip of the tile.
+constexpr int FWD_WARPS = 4;
+constexpr int FWD_CHUNK = 32;   // entries blended per stage
+constexpr int FWD_QUEUE = 128;  // position queue (power of two, >= FWD_CHUNK + 32)
 
-struct FwdSmem {
-  float4 q[2][REC_F4][FWD_BATCH];       // [stage][field][entry]   2*5*256*16 = 40 KB
-  short4 bbox[2][FWD_BATCH];            // conservative contribution boxes of the staged entries
-  uint8_t list[TILE_PIX / 32][FWD_BATCH];  // per-warp compacted entry indices (ascending = depth order)
+struct FwdWarpSmem {
+  float4 q[2][REC_F4][FWD_CHUNK];  // [stage][field][entry]  5 KB
+  uint32_t pos[2][FWD_CHUNK];      // 1-based position of the staged entry in the tile list
+  uint32_t queue[FWD_QUEUE];
 };
 
-__device__ __forceinline__ void stage_batch(float4 (*q)[FWD_BATCH], short4* sbox,
-                                            const float4* __restrict__ records, const short4* __restrict__ bbox,
-                                            const uint32_t* __restrict__ point_list, uint32_t begin,
-                                            uint32_t end, int t) {
-  const uint32_t i = begin + t;
-  if (i < end) {
-    const uint32_t id = __ldg(point_list + i);
-    const float4* src = records + (size_t)id * REC_F4;
-#pragma unroll
-    for (int f = 0; f < REC_F4; f++) __pipeline_memcpy_async(&q[f][t], src + f, sizeof(float4));
-    __pipeline_memcpy_async(&sbox[t], bbox + id, sizeof(short4));
-  }
-}
-
 template <bool STATS>
-__global__ void __launch_bounds__(TILE_PIX) render_fwd_kernel(const FwdRenderParams p) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  FwdSmem& sm = *reinterpret_cast<FwdSmem*>(smem_raw);
+__global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRenderParams p) {
+  __shared__ __align__(16) FwdWarpSmem smem_all[FWD_WARPS];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  FwdWarpSmem& sm = smem_all[warp];
 
-  const int t = threadIdx.x;
-  const uint32_t pixx = blockIdx.x * TILE_X + (t & 15);
-  const uint32_t pixy = blockIdx.y * TILE_Y + (t >> 4);
+  const uint32_t strip_global = blockIdx.x * FWD_WARPS + warp;
+  const uint32_t tile = strip_global / STRIPS_PER_TILE, strip = strip_global % STRIPS_PER_TILE;
+  if (tile >= (uint32_t)(p.grid_x * p.grid_y)) return;
+  const uint32_t tile_x = tile % (uint32_t)p.grid_x, tile_y = tile / (uint32_t)p.grid_x;
+  const uint32_t pixx = tile_x * TILE_X + (lane & 15);
+  const uint32_t pixy = tile_y * TILE_Y + strip * STRIP_ROWS + (lane >> 4);
   const bool inside = pixx < (uint32_t)p.W && pixy < (uint32_t)p.H;
   const float pxf = (float)pixx, pyf = (float)pixy;
-  const uint2 range = __ldg(p.ranges + blockIdx.y * p.grid_x + blockIdx.x);
-  const int total = (int)(range.y - range.x);
-  const int rounds = (total + FWD_BATCH - 1) / FWD_BATCH;
+  const uint2 range = __ldg(p.ranges + tile);
+  const uint32_t total = range.y - range.x;
+  const uint32_t strip_bit = 1u << strip;
 
   bool done = !inside;
   float T = 1.0f;
@@ -68,99 +67,100 @@ __global__ void __launch_bounds__(TILE_PIX) render_fwd_kernel(const FwdRenderPar
   bool stopped = false;                          // STATS only: terminated by the transmittance test
   const float far_ratio = __uint_as_float(GSM_FAR_RATIO_BITS);
 
-  // this warp's pixel strip (16 x 2), inclusive integer pixel bounds
-  const int warp = t >> 5, lane = t & 31;
-  const int sx_lo = blockIdx.x * TILE_X, sx_hi = sx_lo + TILE_X - 1;
-  const int sy_lo = blockIdx.y * TILE_Y + 2 * warp, sy_hi = sy_lo + 1;
-  uint8_t* __restrict__ mylist = sm.list[warp];
-
-  if (rounds > 0) stage_batch(sm.q[0], sm.bbox[0], p.records, p.bbox, p.point_list, range.x, range.y, t);
-  __pipeline_commit();
-
-  int toDo = total;
-  for (int i = 0; i < rounds; i++, toDo -= FWD_BATCH) {
-    const int s = i & 1;
-    // batch i has landed for this thread's own copies; the CTA-wide vote (forward.cu:325-327)
-    // doubles as the barrier that publishes stage s and proves stage s^1 (read in round i-1) free
-    __pipeline_wait_prior(0);
-    if (__syncthreads_count(done) == TILE_PIX) break;
-    if (i + 1 < rounds)
-      stage_batch(sm.q[s ^ 1], sm.bbox[s ^ 1], p.records, p.bbox, p.point_list,
-                  range.x + (uint32_t)(i + 1) * FWD_BATCH, range.y, t);
+  // ---- scan / queue / stage machinery (all warp-uniform state) ----
+  uint32_t scan = 0;           // next list offset (0-based within the tile list) to scan
+  uint32_t qhead = 0, qcount = 0;
+  auto fill = [&]() {          // scan strip masks until a full chunk is queued or the list ends
+    while (qcount < FWD_CHUNK && scan < total) {
+      const uint32_t o = scan + lane;
+      const bool hit = o < total && (__ldg(p.strip_mask + range.x + o) & strip_bit);
+      const unsigned m = __ballot_sync(0xffffffffu, hit);
+      if (hit) sm.queue[(qhead + qcount + __popc(m & ((1u << lane) - 1u))) & (FWD_QUEUE - 1)] = o + 1u;
+      qcount += __popc(m);
+      scan += 32;
+    }
+    __syncwarp();
+  };
+  auto issue = [&](int s) -> int {  // gather up to FWD_CHUNK queued entries into stage s
+    const int n = (int)min(qcount, (uint32_t)FWD_CHUNK);
+    if (lane < n) {
+      const uint32_t pos1 = sm.queue[(qhead + lane) & (FWD_QUEUE - 1)];
+      sm.pos[s][lane] = pos1;
+      const uint32_t id = __ldg(p.point_list + range.x + pos1 - 1u);
+      const float4* src = p.records + (size_t)id * REC_F4;
+#pragma unroll
+      for (int f = 0; f < REC_F4; f++) __pipeline_memcpy_async(&sm.q[s][f][lane], src + f, sizeof(float4));
+    }
     __pipeline_commit();
+    qhead += n;
+    qcount -= n;
+    return n;
+  };
 
-    const int n = min(FWD_BATCH, toDo);
+  fill();
+  int n_cur = issue(0);
+  int s = 0;
+  while (n_cur > 0) {
+    fill();
+    const int n_next = issue(s ^ 1);  // prefetch the next chunk while this one is blended
+    __pipeline_wait_prior(1);
+    __syncwarp();
     const float4* __restrict__ q0 = sm.q[s][0];
     const float4* __restrict__ q1 = sm.q[s][1];
     const float4* __restrict__ q2 = sm.q[s][2];
     const float4* __restrict__ q3 = sm.q[s][3];
     const float4* __restrict__ q4 = sm.q[s][4];
-    if (!__all_sync(0xffffffffu, done)) {
-      // compact, per warp, the entries whose contribution box meets this warp's strip; entries
-      // outside cannot pass the alpha test for any of its pixels, and a skipped entry has no side
-      // effect in the reference either (every `continue` of forward.cu:355-392 precedes all updates)
-      int cnt = 0;
-#pragma unroll
-      for (int r = 0; r < FWD_BATCH / 32; r++) {
-        const int j = r * 32 + lane;
-        bool hit = false;
-        if (j < n) {
-          const short4 bx = sm.bbox[s][j];
-          hit = p.no_cull || (bx.x <= sx_hi && bx.z >= sx_lo && bx.y <= sy_hi && bx.w >= sy_lo);
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, hit);
-        if (hit) mylist[cnt + __popc(m & ((1u << lane) - 1u))] = (uint8_t)j;
-        cnt += __popc(m);
-      }
-      __syncwarp();
-      const uint32_t base = (uint32_t)i * FWD_BATCH + 1u;
-      for (int e = 0; e < cnt; e++) {
-        if (__all_sync(0xffffffffu, done)) break;
-        if (done) continue;
-        const int j = mylist[e];
-        contributor = base + (uint32_t)j;  // position in the tile list, 1-based (forward.cu:350)
-        if (STATS) n_evaluated++;
-        const float4 a = q0[j], b = q1[j], c = q2[j];
-        // k = px*Tw - Tu ; l = py*Tw - Tv ; p = k x l   (forward.cu:355-358), fused as the
-        // reference's SASS fuses them (ptxas contracts the un-suffixed PTX mul/sub pairs)
-        const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
-        const float lx = FMA(pyf, c.x, -b.x), ly = FMA(pyf, c.y, -b.y), lz = FMA(pyf, c.z, -b.z);
-        const float ppx = FMA(ky, lz, -MUL(kz, ly));
-        const float ppy = FMA(kz, lx, -MUL(kx, lz));
-        const float ppz = FMA(kx, ly, -MUL(ky, lx));
-        if (ppz == 0.0f) continue;
-        const float sx = __fdiv_rn(ppx, ppz), sy = __fdiv_rn(ppy, ppz);
-        const float rho3d = FMA(sx, sx, MUL(sy, sy));
-        const float dx = SUB(a.w, pxf), dy = SUB(b.w, pyf);
-        const float r2 = FMA(dy, dy, MUL(dx, dx));
-        const float rho2d = ADD(r2, r2);
-        const float rho = fminf(rho3d, rho2d);
-        const float depth = ADD(c.z, FMA(c.x, sx, MUL(c.y, sy)));
-        if (depth < NEAR_N) continue;
-        const float power = MUL(rho, -0.5f);
-        if (power > 0.0f) continue;
-        const float alpha = fminf(MUL(c.w, expf(power)), ALPHA_MAX);
-        if (alpha < ALPHA_MIN) continue;
-        const float test_T = MUL(T, SUB(1.0f, alpha));
-        if (test_T < T_EPS) { done = true; if (STATS) stopped = true; continue; }
+    const uint32_t* __restrict__ qpos = sm.pos[s];
+    bool all_done = false;
+    for (int j = 0; j < n_cur; j++) {
+      if (__all_sync(0xffffffffu, done)) { all_done = true; break; }
+      if (done) continue;
+      contributor = qpos[j];  // position in the tile list, 1-based (forward.cu:350)
+      if (STATS) n_evaluated++;
+      const float4 a = q0[j], b = q1[j], c = q2[j];
+      // k = px*Tw - Tu ; l = py*Tw - Tv ; p = k x l   (forward.cu:355-358), fused as the
+      // reference's SASS fuses them (ptxas contracts the un-suffixed PTX mul/sub pairs)
+      const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
+      const float lx = FMA(pyf, c.x, -b.x), ly = FMA(pyf, c.y, -b.y), lz = FMA(pyf, c.z, -b.z);
+      const float ppx = FMA(ky, lz, -MUL(kz, ly));
+      const float ppy = FMA(kz, lx, -MUL(kx, lz));
+      const float ppz = FMA(kx, ly, -MUL(ky, lx));
+      if (ppz == 0.0f) continue;
+      const float sx = __fdiv_rn(ppx, ppz), sy = __fdiv_rn(ppy, ppz);
+      const float rho3d = FMA(sx, sx, MUL(sy, sy));
+      const float dx = SUB(a.w, pxf), dy = SUB(b.w, pyf);
+      const float r2 = FMA(dy, dy, MUL(dx, dx));
+      const float rho2d = ADD(r2, r2);
+      const float rho = fminf(rho3d, rho2d);
+      const float depth = ADD(c.z, FMA(c.x, sx, MUL(c.y, sy)));
+      if (depth < NEAR_N) continue;
+      const float power = MUL(rho, -0.5f);
+      if (power > 0.0f) continue;
+      const float alpha = fminf(MUL(c.w, expf(power)), ALPHA_MAX);
+      if (alpha < ALPHA_MIN) continue;
+      const float test_T = MUL(T, SUB(1.0f, alpha));
+      if (test_T < T_EPS) { done = true; if (STATS) stopped = true; continue; }
 
-        const float w = MUL(T, alpha);
-        const float A = SUB(1.0f, T);
-        const float m = MUL(ADD(__fdiv_rn(-NEAR_N, depth), 1.0f), far_ratio);
-        const float mm = MUL(m, m);
-        distortion = FMA(w, FMA(-M1, ADD(m, m), FMA(A, mm, M2)), distortion);
-        D = FMA(depth, w, D);
-        M1 = FMA(m, w, M1);
-        M2 = FMA(mm, w, M2);
-        if (T > 0.5f) { median_depth = depth; median_contributor = contributor; }
-        const float4 nrm = q3[j], col = q4[j];
-        N0 = FMA(w, nrm.x, N0); N1 = FMA(w, nrm.y, N1); N2 = FMA(w, nrm.z, N2);
-        C0 = FMA(w, col.x, C0); C1 = FMA(w, col.y, C1); C2 = FMA(w, col.z, C2);
-        T = test_T;
-        last_contributor = contributor;
-        if (STATS) n_contributing++;
-      }
+      const float w = MUL(T, alpha);
+      const float A = SUB(1.0f, T);
+      const float m = MUL(ADD(__fdiv_rn(-NEAR_N, depth), 1.0f), far_ratio);
+      const float mm = MUL(m, m);
+      distortion = FMA(w, FMA(-M1, ADD(m, m), FMA(A, mm, M2)), distortion);
+      D = FMA(depth, w, D);
+      M1 = FMA(m, w, M1);
+      M2 = FMA(mm, w, M2);
+      if (T > 0.5f) { median_depth = depth; median_contributor = contributor; }
+      const float4 nrm = q3[j], col = q4[j];
+      N0 = FMA(w, nrm.x, N0); N1 = FMA(w, nrm.y, N1); N2 = FMA(w, nrm.z, N2);
+      C0 = FMA(w, col.x, C0); C1 = FMA(w, col.y, C1); C2 = FMA(w, col.z, C2);
+      T = test_T;
+      last_contributor = contributor;
+      if (STATS) n_contributing++;
     }
+    if (all_done) break;
+    __syncwarp();  // every lane is done reading stage s before it is refilled two issues from now
+    n_cur = n_next;
+    s ^= 1;
   }
   __pipeline_wait_prior(0);
 
@@ -174,8 +174,8 @@ __global__ void __launch_bounds__(TILE_PIX) render_fwd_kernel(const FwdRenderPar
       c += __shfl_xor_sync(0xffffffffu, c, o);
       v += __shfl_xor_sync(0xffffffffu, v, o);
     }
-    if ((t & 31) == 0) { atomicAdd(p.stats + 0, e); atomicAdd(p.stats + 1, c); atomicAdd(p.stats + 3, v); }
-    if (t == 0) atomicAdd(p.stats + 2, (unsigned long long)total);
+    if (lane == 0) { atomicAdd(p.stats + 0, e); atomicAdd(p.stats + 1, c); atomicAdd(p.stats + 3, v); }
+    if (lane == 0 && strip == 0) atomicAdd(p.stats + 2, (unsigned long long)total);
   }
 
   if (inside) {
@@ -200,15 +200,10 @@ __global__ void __launch_bounds__(TILE_PIX) render_fwd_kernel(const FwdRenderPar
 }
 
 void launch_render_fwd(const FwdRenderParams& p, cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
-    cudaFuncSetAttribute(render_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem));
-    cudaFuncSetAttribute(render_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem));
-    configured = true;
-  }
-  dim3 grid(p.grid_x, p.grid_y, 1);
-  if (p.stats) render_fwd_kernel<true><<<grid, TILE_PIX, sizeof(FwdSmem), stream>>>(p);
-  else render_fwd_kernel<false><<<grid, TILE_PIX, sizeof(FwdSmem), stream>>>(p);
+  const unsigned strips = (unsigned)(p.grid_x * p.grid_y) * STRIPS_PER_TILE;
+  const unsigned grid = (strips + FWD_WARPS - 1) / FWD_WARPS;
+  if (p.stats) render_fwd_kernel<true><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
+  else render_fwd_kernel<false><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
 }
 
 }  // namespace gsm

@@ -122,12 +122,14 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
                 continue
             _lib.check(code, "forward")
             break
+    # the capacity the forward ran with travels with the buffer (backward needs it to find the strip masks)
+    binning.gsm_capacity = capacity
     return num_rendered.value, out_color, out_others, radii, geometry, binning, image
 
 
 def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp, viewmatrix,
                    projmatrix, tanfovx, tanfovy, grad_out_color, grad_depth, sh, sh_degree, campos, geomBuffer,
-                   num_rendered, binningBuffer, imgBuffer, debug, out=None, accumulate=False):
+                   num_rendered, binningBuffer, imgBuffer, debug, out=None, accumulate=False, binning_capacity=None):
     """Equivalent of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:136-233).
 
     `out` (optional) maps means3D / shs / opacities / scales / rotations to preallocated tensors the
@@ -170,6 +172,11 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
             a.scales, a.rotations, a.transMat_precomp = _ptr(scales), _ptr(rotations), _ptr(cov3Ds_precomp)
             a.viewmatrix, a.projmatrix, a.campos, a.radii = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), _ptr(radii)
             a.geometry, a.image, a.binning = _ptr(geomBuffer), _ptr(imgBuffer), _ptr(binningBuffer)
+            if binning_capacity is None:
+                binning_capacity = getattr(binningBuffer, "gsm_capacity", None)
+            if binning_capacity is None:
+                raise RuntimeError("backward needs the binning capacity of the forward call")
+            a.binning_capacity = int(binning_capacity)
             a.dL_dout_color, a.dL_dout_others = _ptr(grad_out_color), _ptr(grad_depth)
             a.grad_workspace, a.grad_workspace_bytes = _ptr(gws), gws.numel()
             a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity = _ptr(dL_dmeans2D), _ptr(dL_dcolors), _ptr(dL_dopacity)
@@ -212,7 +219,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.opacity_shape = opacities.shape
         # only the depth-sorted surfel list (first 4*R bytes) of the binning workspace is needed by
         # backward; keep a compact copy so the transient sort scratch returns to the allocator now
-        point_list = binningBuffer[: 4 * num_rendered + 128].clone() if num_rendered > 0 else binningBuffer[:0]
+        ctx.binning_capacity = binningBuffer.gsm_capacity
+        keep = _lib.load().gsm_binning_persistent_bytes(ctx.binning_capacity)
+        point_list = binningBuffer[:keep].clone() if num_rendered > 0 else binningBuffer[:0]
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
                               point_list, imgBuffer)
         ctx.mark_non_differentiable(radii)
@@ -233,16 +242,17 @@ class _RasterizeGaussians(torch.autograd.Function):
                 cov3Ds_precomp, raster_settings.viewmatrix, raster_settings.projmatrix, raster_settings.tanfovx,
                 raster_settings.tanfovy, grad_out_color, grad_depth, sh, raster_settings.sh_degree,
                 raster_settings.campos, geomBuffer, num_rendered, binningBuffer, imgBuffer, raster_settings.debug)
+        kw = dict(binning_capacity=ctx.binning_capacity)
         if raster_settings.debug:
             cpu_args = cpu_deep_copy_tuple(args)
             try:
-                out = _backward_impl(*args)
+                out = _backward_impl(*args, **kw)
             except Exception as ex:
                 torch.save(cpu_args, "snapshot_bw.dump")
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise ex
         else:
-            out = _backward_impl(*args)
+            out = _backward_impl(*args, **kw)
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
          grad_rotations) = out
         grads = (

@@ -58,10 +58,13 @@ size_t gsm_geometry_bytes(int P);
 /* image workspace (must survive until backward): final_T[3,H,W], n_contrib[2,H,W], ranges[Nt].
  * Replaces ImageState::fromChunk (rasterizer_impl.cu:172-179). */
 size_t gsm_image_bytes(int width, int height);
-/* binning workspace for `capacity` (surfel,tile) instances; the first capacity*4 bytes are the
- * depth-sorted surfel list (must survive until backward), the rest is transient.
+/* binning workspace for `capacity` (surfel,tile) instances.  Its first
+ * gsm_binning_persistent_bytes(capacity) bytes (the depth-sorted surfel list u32[capacity] and the
+ * per-instance strip masks u8[capacity]) must survive until backward -- a copy of that prefix is as
+ * good as the original; the rest (keys, sort scratch) is transient.
  * Replaces BinningState::fromChunk (rasterizer_impl.cu:181-194). */
 size_t gsm_binning_bytes(size_t capacity, int width, int height);
+size_t gsm_binning_persistent_bytes(size_t capacity);
 /* byte offsets of the sorted keys (u64[R]) inside the binning workspace, for parity tests. */
 size_t gsm_binning_sorted_keys_offset(size_t capacity);
 /* byte offset of ranges (uint2[Nt]) / n_contrib (u32[2,H,W]) inside the image workspace. */
@@ -134,7 +137,8 @@ typedef struct gsm_backward_args {
   const int* radii;
   const void* geometry;  /* as left by gsm_forward */
   const void* image;
-  const void* binning;   /* only the sorted surfel list is read */
+  const void* binning;   /* the persistent prefix of the forward's binning workspace (or a copy) */
+  size_t binning_capacity; /* the capacity the forward was called with (locates the strip masks) */
   const float* dL_dout_color;  /* [3,H,W] */
   const float* dL_dout_others; /* [7,H,W] */
   void* grad_workspace; size_t grad_workspace_bytes; /* >= gsm_grad_workspace_bytes(P), transient */

@@ -111,3 +111,34 @@ def run_oracle(oracle, scene, cam, bg_value, cot=None, variant="sh", scale_modif
 ORACLE_GRAD_KEYS = dict(means3D="dL_dmeans3D", means2D="dL_dmeans2D", opacities="dL_dopacity", shs="dL_dsh",
                         colors_precomp="dL_dcolors", scales="dL_dscales", rotations="dL_drotations",
                         cov3D_precomp="dL_dtransMat")
+
+
+def robust_rel_fro(a, b, drop_frac=0.002):
+    """rel. Frobenius error after dropping the `drop_frac` rows (surfels) with the largest deviation: the
+    CPU oracle and the GPU can take a different discrete decision (alpha >= 1/255, T < 1e-4, median) for
+    a pixel of an ill-conditioned surfel, which moves that surfel's gradient by ~1e-3 rel."""
+    a = torch.as_tensor(a).double()
+    b = torch.as_tensor(b).double()
+    a = a.reshape(a.shape[0], -1)
+    b = b.reshape(b.shape[0], -1)
+    d = (a - b).abs().max(1).values
+    k = int(drop_frac * a.shape[0]) + 1
+    keep = torch.ones(a.shape[0], dtype=torch.bool)
+    keep[torch.topk(d, min(k, a.shape[0])).indices] = False
+    return rel_fro(a[keep], b[keep])
+
+
+def assert_grads_match_reference(new, ref, ref_again=None, what=""):
+    """Gradient bar against the reference BUILD: |a-b| <= 1e-4 max(|a|,|b|) + 1e-7 scale element-wise.
+    Both builds accumulate with unordered fp32 atomics, so the reference does not even reproduce itself
+    element-wise: the budget is twice what two runs of the reference differ by, + 2
+    entries, and the tensor as a whole must agree to 1e-5 rel."""
+    for k in ref:
+        if not k.startswith("grad_") or ref[k] is None:
+            continue
+        viol, _ = grad_violations(new[k].cpu(), ref[k].cpu())
+        noise = 0
+        if ref_again is not None:
+            noise, _ = grad_violations(ref_again[k].cpu(), ref[k].cpu())
+        assert viol <= 2 * noise + 2 + int(1e-7 * ref[k].numel()), (what, k, viol, noise)
+        assert rel_fro(new[k].cpu(), ref[k].cpu()) < 1e-5, (what, k)

@@ -10,7 +10,7 @@ import torch
 
 import gaussmart_b200 as gb
 from gaussmart_b200 import debug, synthetic
-from helpers import grad_violations, run_cuda, variant_inputs
+from helpers import assert_grads_match_reference, grad_violations, run_cuda, variant_inputs
 import ref_loader
 
 pytestmark = pytest.mark.gpu
@@ -87,10 +87,8 @@ def test_c4_full_matches_reference_build(c4):
     assert torch.equal(o_ref["radii"], o_new["radii"])
     assert (o_ref["color"] - o_new["color"]).abs().max().item() <= 1e-5
     assert ((o_ref["allmap"] - o_new["allmap"]).abs() <= 1e-5 * o_ref["allmap"].abs().clamp(min=1)).all()
-    for k in o_ref:
-        if k.startswith("grad_") and o_ref[k] is not None:
-            viol, _ = grad_violations(o_new[k].cpu(), o_ref[k].cpu())
-            assert viol == 0, (k, viol)
+    o_ref2 = run_cuda(ref, scene, cam, 0.0, cot, "sh")
+    assert_grads_match_reference(o_new, o_ref, o_ref2, "C4")
 
 
 # ---------------------------------------------------------------------------------------- distCUDA2

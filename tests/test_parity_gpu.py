@@ -13,7 +13,8 @@ import torch
 
 import gaussmart_b200 as gb
 from gaussmart_b200 import debug, synthetic
-from helpers import (ORACLE_GRAD_KEYS, fwd_close, grad_violations, rel_fro, run_cuda, run_oracle, variant_inputs)
+from helpers import (ORACLE_GRAD_KEYS, assert_grads_match_reference, fwd_close, grad_violations, rel_fro,
+                     robust_rel_fro, run_cuda, run_oracle, variant_inputs)
 import ref_loader
 
 pytestmark = pytest.mark.gpu
@@ -108,7 +109,8 @@ def test_cuda_matches_oracle_small(oracle, name, P, W, H, deg, variant, bg, mod,
     for nm in ("color", "allmap"):
         ok = fwd_close(o[nm].cpu(), f[nm])
         assert (~ok).double().mean().item() <= 0.005, nm  # CPU exp/rsqrt differ in the last ulp
-        assert rel_fro(o[nm].cpu(), f[nm]) < 1e-5, nm
+        assert rel_fro(o[nm].cpu()[ok], f[nm][ok]) < 1e-5, nm
+        assert rel_fro(o[nm].cpu(), f[nm]) < 1e-4, nm             # ill-conditioned (grazing) pixels included
     for leaf, key in ORACLE_GRAD_KEYS.items():
         gk = "grad_" + leaf
         if o.get(gk) is None:
@@ -116,7 +118,28 @@ def test_cuda_matches_oracle_small(oracle, name, P, W, H, deg, variant, bg, mod,
         ref = grads[key].reshape(o[gk].shape)
         viol, _ = grad_violations(o[gk].cpu(), ref)
         assert viol <= 0.005 * ref.numel(), (leaf, viol)
-        assert rel_fro(o[gk].cpu(), ref) < 1e-4, leaf
+        assert robust_rel_fro(o[gk].cpu(), ref) < 1e-4, leaf
+        assert rel_fro(o[gk].cpu(), ref) < 1e-2, leaf
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="oracle/_ref (reference CUDA build) not present")
+@pytest.mark.parametrize("W,H", [(128, 128), (800, 600)])
+def test_truncating_fov_matches_reference_build(W, H):
+    """backward.cu:613-614 re-derives W,H as int(focal*tan*2), which is W-1 for some FoVs (SURVEY.md A.5 #6)."""
+    ref = ref_loader.load_dsr()
+    scene = synthetic.make_scene(20_000, W, 2, 321)
+    scene = scene._replace(scales=scene.scales * 2.0)
+    cam = synthetic.make_camera(W, H, 0.3, fovx=_truncating_fov(W))
+    cot = synthetic.make_cotangents(W, H, 99)
+    o_ref = run_cuda(ref, scene, cam, 0.0, cot, "sh")
+    o_ref2 = run_cuda(ref, scene, cam, 0.0, cot, "sh")
+    o_new = run_cuda(gb, scene, cam, 0.0, cot, "sh")
+    assert torch.equal(o_ref["radii"], o_new["radii"])
+    assert torch.equal(o_ref["color"], o_new["color"]) and torch.equal(o_ref["allmap"], o_new["allmap"])
+    assert_grads_match_reference(o_new, o_ref, o_ref2, "trunc")
+    # the truncation is live: the view-space gradient scales with the re-derived W-1, not W
+    vis = o_ref["radii"] > 0
+    assert o_ref["grad_means2D"][vis].abs().sum().item() > 0
 
 
 def test_scale_modifier_forward_only(oracle):
@@ -193,14 +216,12 @@ def test_cuda_matches_reference_build(cfg, P, variant, bg):
     W, H = cam.image_width, cam.image_height
     cot = synthetic.make_cotangents(W, H, 777)
     o_ref = run_cuda(ref, scene, cam, bg, cot, variant)
+    o_ref2 = run_cuda(ref, scene, cam, bg, cot, variant)
     o_new = run_cuda(gb, scene, cam, bg, cot, variant)
     assert torch.equal(o_ref["radii"], o_new["radii"])
     assert fwd_close(o_new["color"].cpu(), o_ref["color"].cpu()).all()
     assert fwd_close(o_new["allmap"].cpu(), o_ref["allmap"].cpu()).all()
-    for k in o_ref:
-        if k.startswith("grad_") and o_ref[k] is not None:
-            viol, _ = grad_violations(o_new[k].cpu(), o_ref[k].cpu())
-            assert viol == 0, (k, viol)
+    assert_grads_match_reference(o_new, o_ref, o_ref2, cfg)
     # bit-exact intermediates out of the reference's scratch buffers
     S = o_ref["settings"]
     e = torch.empty(0, device="cuda")

@@ -21,56 +21,55 @@ namespace gsm {
 #define FMA(a, b, c) __fmaf_rn((a), (b), (c))
 
 // SH basis constants as fp32 (auxiliary.h:43-60)
-__device__ __forceinline__ float3 sh_to_rgb(int D, const float4* __restrict__ sh4, float3 dir) {
-  // sh4 points at this surfel's M*3 floats (16-byte aligned when M*3*4 % 16 == 0, else scalar path)
-  const float* sh = reinterpret_cast<const float*>(sh4);
+__device__ __forceinline__ float3 sh_to_rgb(int D, const float* sh, float3 dir) {
+  // sh: this surfel's 3M coefficients, staged in shared memory by the warp (coalesced 128-bit loads)
   const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
   float3 r;
-  r.x = MUL(C0, __ldg(sh + 0)); r.y = MUL(C0, __ldg(sh + 1)); r.z = MUL(C0, __ldg(sh + 2));
+  r.x = MUL(C0, sh[0]); r.y = MUL(C0, sh[1]); r.z = MUL(C0, sh[2]);
   if (D > 0) {
     const float x = dir.x, y = dir.y, z = dir.z;
     float t = MUL(y, C1);
-    r.x = FMA(-t, __ldg(sh + 3), r.x); r.y = FMA(-t, __ldg(sh + 4), r.y); r.z = FMA(-t, __ldg(sh + 5), r.z);
+    r.x = FMA(-t, sh[3], r.x); r.y = FMA(-t, sh[4], r.y); r.z = FMA(-t, sh[5], r.z);
     t = MUL(z, C1);
-    r.x = FMA(t, __ldg(sh + 6), r.x); r.y = FMA(t, __ldg(sh + 7), r.y); r.z = FMA(t, __ldg(sh + 8), r.z);
+    r.x = FMA(t, sh[6], r.x); r.y = FMA(t, sh[7], r.y); r.z = FMA(t, sh[8], r.z);
     t = MUL(x, C1);
-    r.x = FMA(-t, __ldg(sh + 9), r.x); r.y = FMA(-t, __ldg(sh + 10), r.y); r.z = FMA(-t, __ldg(sh + 11), r.z);
+    r.x = FMA(-t, sh[9], r.x); r.y = FMA(-t, sh[10], r.y); r.z = FMA(-t, sh[11], r.z);
     if (D > 1) {
       const float xx = MUL(x, x), yy = MUL(y, y), zz = MUL(z, z);
       const float xy = MUL(x, y), yz = MUL(y, z), xz = MUL(x, z);
       const float C20 = 1.0925484305920792f, C21 = -1.0925484305920792f, C22 = 0.31539156525252005f,
                   C23 = -1.0925484305920792f, C24 = 0.5462742152960396f;
       t = MUL(xy, C20);
-      r.x = FMA(t, __ldg(sh + 12), r.x); r.y = FMA(t, __ldg(sh + 13), r.y); r.z = FMA(t, __ldg(sh + 14), r.z);
+      r.x = FMA(t, sh[12], r.x); r.y = FMA(t, sh[13], r.y); r.z = FMA(t, sh[14], r.z);
       t = MUL(yz, C21);
-      r.x = FMA(t, __ldg(sh + 15), r.x); r.y = FMA(t, __ldg(sh + 16), r.y); r.z = FMA(t, __ldg(sh + 17), r.z);
+      r.x = FMA(t, sh[15], r.x); r.y = FMA(t, sh[16], r.y); r.z = FMA(t, sh[17], r.z);
       const float zz2 = ADD(zz, zz);
       t = MUL(SUB(SUB(zz2, xx), yy), C22);
-      r.x = FMA(t, __ldg(sh + 18), r.x); r.y = FMA(t, __ldg(sh + 19), r.y); r.z = FMA(t, __ldg(sh + 20), r.z);
+      r.x = FMA(t, sh[18], r.x); r.y = FMA(t, sh[19], r.y); r.z = FMA(t, sh[20], r.z);
       t = MUL(xz, C23);
-      r.x = FMA(t, __ldg(sh + 21), r.x); r.y = FMA(t, __ldg(sh + 22), r.y); r.z = FMA(t, __ldg(sh + 23), r.z);
+      r.x = FMA(t, sh[21], r.x); r.y = FMA(t, sh[22], r.y); r.z = FMA(t, sh[23], r.z);
       const float xx_yy = SUB(xx, yy);
       t = MUL(xx_yy, C24);
-      r.x = FMA(t, __ldg(sh + 24), r.x); r.y = FMA(t, __ldg(sh + 25), r.y); r.z = FMA(t, __ldg(sh + 26), r.z);
+      r.x = FMA(t, sh[24], r.x); r.y = FMA(t, sh[25], r.y); r.z = FMA(t, sh[26], r.z);
       if (D > 2) {
         const float C30 = -0.5900435899266435f, C31 = 2.890611442640554f, C32 = -0.4570457994644658f,
                     C33 = 0.3731763325901154f, C34 = -0.4570457994644658f, C35 = 1.445305721320277f,
                     C36 = -0.5900435899266435f;
                 const float zz4_xx_yy = SUB(FMA(zz, 4.0f, -xx), yy);
         t = MUL(MUL(y, C30), FMA(xx, 3.0f, -yy));
-        r.x = FMA(t, __ldg(sh + 27), r.x); r.y = FMA(t, __ldg(sh + 28), r.y); r.z = FMA(t, __ldg(sh + 29), r.z);
+        r.x = FMA(t, sh[27], r.x); r.y = FMA(t, sh[28], r.y); r.z = FMA(t, sh[29], r.z);
         t = MUL(z, MUL(xy, C31));
-        r.x = FMA(t, __ldg(sh + 30), r.x); r.y = FMA(t, __ldg(sh + 31), r.y); r.z = FMA(t, __ldg(sh + 32), r.z);
+        r.x = FMA(t, sh[30], r.x); r.y = FMA(t, sh[31], r.y); r.z = FMA(t, sh[32], r.z);
         t = MUL(MUL(y, C32), zz4_xx_yy);
-        r.x = FMA(t, __ldg(sh + 33), r.x); r.y = FMA(t, __ldg(sh + 34), r.y); r.z = FMA(t, __ldg(sh + 35), r.z);
+        r.x = FMA(t, sh[33], r.x); r.y = FMA(t, sh[34], r.y); r.z = FMA(t, sh[35], r.z);
         t = MUL(MUL(z, C33), FMA(yy, -3.0f, FMA(xx, -3.0f, zz2)));
-        r.x = FMA(t, __ldg(sh + 36), r.x); r.y = FMA(t, __ldg(sh + 37), r.y); r.z = FMA(t, __ldg(sh + 38), r.z);
+        r.x = FMA(t, sh[36], r.x); r.y = FMA(t, sh[37], r.y); r.z = FMA(t, sh[38], r.z);
         t = MUL(MUL(x, C34), zz4_xx_yy);
-        r.x = FMA(t, __ldg(sh + 39), r.x); r.y = FMA(t, __ldg(sh + 40), r.y); r.z = FMA(t, __ldg(sh + 41), r.z);
+        r.x = FMA(t, sh[39], r.x); r.y = FMA(t, sh[40], r.y); r.z = FMA(t, sh[41], r.z);
         t = MUL(MUL(z, C35), xx_yy);
-        r.x = FMA(t, __ldg(sh + 42), r.x); r.y = FMA(t, __ldg(sh + 43), r.y); r.z = FMA(t, __ldg(sh + 44), r.z);
+        r.x = FMA(t, sh[42], r.x); r.y = FMA(t, sh[43], r.y); r.z = FMA(t, sh[44], r.z);
         t = MUL(MUL(x, C36), FMA(yy, -3.0f, xx));
-        r.x = FMA(t, __ldg(sh + 45), r.x); r.y = FMA(t, __ldg(sh + 46), r.y); r.z = FMA(t, __ldg(sh + 47), r.z);
+        r.x = FMA(t, sh[45], r.x); r.y = FMA(t, sh[46], r.y); r.z = FMA(t, sh[47], r.z);
       }
     }
   }
@@ -105,12 +104,45 @@ __device__ __forceinline__ float dot3_ref(float a0, float a1, float a2, float b0
   return FMA(a2, b2, FMA(a0, b0, MUL(a1, b1)));
 }
 
-__global__ void __launch_bounds__(256) preprocess_fwd_kernel(const FwdPreprocessParams p) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= p.P) return;
+constexpr int PFWD_THREADS = 128;
+
+// Cooperative, coalesced load of the SH rows of the warp's visible surfels into shared memory
+// (row r at wsm[r * (3M + 1)]: odd stride, conflict-free per-lane reads).
+__device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict__ g, int M, int rows,
+                                             unsigned vis_mask, int lane) {
+  const int rl = 3 * M, rs = rl + 1, total = rows * rl;
+  if (rows == 32 && (reinterpret_cast<size_t>(g) & 15) == 0) {
+    const float4* g4 = reinterpret_cast<const float4*>(g);
+    for (int f = lane; f < total / 4; f += 32) {
+      const int e0 = 4 * f, r0 = e0 / rl, r3 = (e0 + 3) / rl;
+      if (!((vis_mask >> r0) & 1u) && !((vis_mask >> r3) & 1u)) continue;
+      const float4 v = __ldg(g4 + f);
+      const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int e = 0; e < 4; e++) { const int i = e0 + e, r = i / rl; wsm[r * rs + (i - r * rl)] = vv[e]; }
+    }
+  } else {
+    for (int i = lane; i < total; i += 32) {
+      const int r = i / rl;
+      if ((vis_mask >> r) & 1u) wsm[r * rs + (i - r * rl)] = __ldg(g + i);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdPreprocessParams p) {
+  extern __shared__ float sh_smem[];
+  const int gidx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int warp_first = gidx - lane;
+  if (warp_first >= p.P) return;
+  const bool valid = gidx < p.P;
+  const int idx = valid ? gidx : p.P - 1;  // out-of-range lanes shadow the last surfel and write nothing
 
   int radius_out = 0;
   uint32_t tiles_out = 0;
+  float Tu0 = 0, Tu1 = 0, Tu2 = 0, Tv0 = 0, Tv1 = 0, Tv2 = 0, Tw0 = 0, Tw1 = 0, Tw2 = 0;
+  float nx = 0, ny = 0, nz = 0, cx = 0, cy = 0, opac = 0;
+  short4 box = make_short4(-32768, -32768, 32767, 32767);
 
   // camera matrices are 16 floats each: uniform, served by the constant/L1 path
   const float* __restrict__ vm = p.viewmatrix;
@@ -126,13 +158,12 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const FwdPreprocess
   const float vz = ADD(vm[14], FMA(pz, vm[10], FMA(px, vm[2], MUL(py, vm[6]))));
 
   do {
+    if (!valid) break;
     if (vz <= NEAR_N) {  // auxiliary.h:200
       if (p.prefiltered) atomicOr(p.flags, 1u);
       break;
     }
 
-    float Tu0, Tu1, Tu2, Tv0, Tv1, Tv2, Tw0, Tw1, Tw2;
-    float nx, ny, nz;
     if (p.transMat_precomp == nullptr) {
       const float2 sc = __ldg(reinterpret_cast<const float2*>(p.scales) + idx);
       const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
@@ -174,8 +205,8 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const FwdPreprocess
     if (d == 0.0f) break;
     const float inv = __frcp_rn(d);
     const float f9 = MUL(inv, 9.0f);
-    const float cx = FMA(MUL(Tw2, Tu2), -inv, FMA(f9, MUL(Tu0, Tw0), MUL(f9, MUL(Tu1, Tw1))));
-    const float cy = FMA(MUL(Tw2, Tv2), -inv, FMA(f9, MUL(Tv0, Tw0), MUL(f9, MUL(Tv1, Tw1))));
+    cx = FMA(MUL(Tw2, Tu2), -inv, FMA(f9, MUL(Tu0, Tw0), MUL(f9, MUL(Tu1, Tw1))));
+    cy = FMA(MUL(Tw2, Tv2), -inv, FMA(f9, MUL(Tv0, Tw0), MUL(f9, MUL(Tv1, Tw1))));
     const float su = FMA(MUL(Tu2, Tu2), inv, -FMA(f9, MUL(Tu0, Tu0), MUL(f9, MUL(Tu1, Tu1))));
     const float sv = FMA(MUL(Tv2, Tv2), inv, -FMA(f9, MUL(Tv0, Tv0), MUL(f9, MUL(Tv1, Tv1))));
     const float hx = __fsqrt_rn(fmaxf(FMA(cx, cx, su), 1e-4f));
@@ -192,27 +223,9 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const FwdPreprocess
     const uint32_t area = (uint32_t)((maxx - minx) * (maxy - miny));
     if (area == 0) break;
 
-    float3 rgb;
-    int clamp_bits = 0;
-    if (p.colors_precomp == nullptr) {
-      const float* cp = p.campos;
-      const float dx = SUB(px, cp[0]), dy = SUB(py, cp[1]), dz = SUB(pz, cp[2]);
-      const float len = __fsqrt_rn(FMA(dz, dz, FMA(dx, dx, MUL(dy, dy))));
-      const float3 dir = make_float3(__fdiv_rn(dx, len), __fdiv_rn(dy, len), __fdiv_rn(dz, len));
-      rgb = sh_to_rgb(p.D, reinterpret_cast<const float4*>(p.shs + (size_t)idx * p.M * 3), dir);
-      if (rgb.x < 0.0f) { clamp_bits |= 1; rgb.x = 0.0f; }
-      if (rgb.y < 0.0f) { clamp_bits |= 2; rgb.y = 0.0f; }
-      if (rgb.z < 0.0f) { clamp_bits |= 4; rgb.z = 0.0f; }
-    } else {
-      rgb.x = __ldg(p.colors_precomp + 3 * (size_t)idx + 0);
-      rgb.y = __ldg(p.colors_precomp + 3 * (size_t)idx + 1);
-      rgb.z = __ldg(p.colors_precomp + 3 * (size_t)idx + 2);
-    }
-
     // conservative contribution box (common.cuh, CULL_RHO); fp64 so that the cancellation in
     // centre^2 - <f,T^2> cannot shrink it
-    short4 box = make_short4(-32768, -32768, 32767, 32767);
-    const float opac = __ldg(p.opacities + idx);
+    opac = __ldg(p.opacities + idx);
     if (opac < ALPHA_MIN) {
       // alpha = opacity * exp(power) with power <= 0 never reaches 1/255 (forward.cu:385-392): empty box
       box = make_short4(32767, 32767, -32768, -32768);
@@ -241,25 +254,60 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const FwdPreprocess
         }
       }
     }
-    p.bbox[idx] = box;
+    radius_out = ri;
+    tiles_out = area;
+  } while (false);
 
+  // ---- colour (forward.cu:20-71): SH rows of the warp's visible surfels go through shared memory ----
+  const bool visible = tiles_out != 0;
+  const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
+  float3 rgb = make_float3(0.f, 0.f, 0.f);
+  int clamp_bits = 0;
+  if (p.colors_precomp == nullptr) {
+    float* wsm = sh_smem + (size_t)warp * 32 * (3 * p.M + 1);
+    if (vis_mask != 0) {
+      sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, p.M, min(32, p.P - warp_first), vis_mask, lane);
+      __syncwarp();
+    }
+    if (visible) {
+      const float* cp = p.campos;
+      const float dx = SUB(px, cp[0]), dy = SUB(py, cp[1]), dz = SUB(pz, cp[2]);
+      const float len = __fsqrt_rn(FMA(dz, dz, FMA(dx, dx, MUL(dy, dy))));
+      const float3 dir = make_float3(__fdiv_rn(dx, len), __fdiv_rn(dy, len), __fdiv_rn(dz, len));
+      rgb = sh_to_rgb(p.D, wsm + lane * (3 * p.M + 1), dir);
+      if (rgb.x < 0.0f) { clamp_bits |= 1; rgb.x = 0.0f; }
+      if (rgb.y < 0.0f) { clamp_bits |= 2; rgb.y = 0.0f; }
+      if (rgb.z < 0.0f) { clamp_bits |= 4; rgb.z = 0.0f; }
+    }
+  } else if (visible) {
+    rgb.x = __ldg(p.colors_precomp + 3 * (size_t)idx + 0);
+    rgb.y = __ldg(p.colors_precomp + 3 * (size_t)idx + 1);
+    rgb.z = __ldg(p.colors_precomp + 3 * (size_t)idx + 2);
+  }
+  if (!valid) return;
+  if (visible) {
+    p.bbox[idx] = box;
     float4* rec = p.records + (size_t)idx * REC_F4;
     rec[0] = make_float4(Tu0, Tu1, Tu2, cx);
     rec[1] = make_float4(Tv0, Tv1, Tv2, cy);
     rec[2] = make_float4(Tw0, Tw1, Tw2, opac);
     rec[3] = make_float4(nx, ny, nz, vz);
     rec[4] = make_float4(rgb.x, rgb.y, rgb.z, __int_as_float(clamp_bits));
-    radius_out = ri;
-    tiles_out = area;
-  } while (false);
-
+  }
   p.radii[idx] = radius_out;
   p.tiles_touched[idx] = tiles_out;
 }
 
 void launch_preprocess_fwd(const FwdPreprocessParams& p, cudaStream_t stream) {
   if (p.P <= 0) return;
-  preprocess_fwd_kernel<<<(p.P + 255) / 256, 256, 0, stream>>>(p);
+  const size_t smem = (p.colors_precomp == nullptr)
+                          ? (size_t)(PFWD_THREADS / 32) * 32 * (3 * p.M + 1) * sizeof(float) : 0;
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    configured = smem;
+  }
+  preprocess_fwd_kernel<<<(p.P + PFWD_THREADS - 1) / PFWD_THREADS, PFWD_THREADS, smem, stream>>>(p);
 }
 
 // markVisible (rasterizer_impl.cu:54-66): present = view_z > 0.2

@@ -23,37 +23,37 @@ __device__ __forceinline__ void store3(float* dst, f3 v, bool acc = false) {
   else { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; }
 }
 
-// SH backward (backward.cu:20-139). dL_dsh row is fully written (zeros beyond the active degree).
-__device__ void sh_backward(int D, int M, const float* __restrict__ sh, f3 dir_orig, f3 dL_dRGB,
-                            float* __restrict__ dL_dsh, f3& dL_dmean_add, bool acc) {
-  // dir = dir_orig / length(dir_orig) exactly as the forward evaluates it (IEEE sqrt and divisions,
-  // forward.cu:26-27 / backward.cu:27-28): factors such as 2zz-xx-yy cancel, so a 1-ulp change of
-  // x,y,z would show up as a 1e-3 relative change of single dL_dsh entries
+// SH backward (backward.cu:20-139), in place on a shared-memory row: on entry `row` holds this
+// surfel's SH coefficients (3M floats), on exit dL_dsh (zeros beyond the active degree).  Every
+// coefficient is read before its slot is overwritten.
+__device__ void sh_backward(int D, int M, float* row, f3 dir_orig, f3 dL_dRGB, f3& dL_dmean_add) {
+  float* dL_dsh = row;
+  const float* sh = row;
   const float len = __fsqrt_rn(__fmaf_rn(dir_orig.z, dir_orig.z, __fmaf_rn(dir_orig.x, dir_orig.x, __fmul_rn(dir_orig.y, dir_orig.y))));
   const float x = __fdiv_rn(dir_orig.x, len), y = __fdiv_rn(dir_orig.y, len), z = __fdiv_rn(dir_orig.z, len);
   const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
   f3 dx = mk(0, 0, 0), dy = mk(0, 0, 0), dz = mk(0, 0, 0);
-#define SH(k) mk(__ldg(sh + 3 * (k)), __ldg(sh + 3 * (k) + 1), __ldg(sh + 3 * (k) + 2))
-  store3(dL_dsh + 0, C0 * dL_dRGB, acc);
+#define SH(k) mk(sh[3 * (k)], sh[3 * (k) + 1], sh[3 * (k) + 2])
+  store3(dL_dsh + 0, C0 * dL_dRGB);
   int written = 1;
   if (D > 0) {
-    store3(dL_dsh + 3, (-C1 * y) * dL_dRGB, acc);
-    store3(dL_dsh + 6, (C1 * z) * dL_dRGB, acc);
-    store3(dL_dsh + 9, (-C1 * x) * dL_dRGB, acc);
     dx = (-C1) * SH(3);
     dy = (-C1) * SH(1);
     dz = C1 * SH(2);
+    store3(dL_dsh + 3, (-C1 * y) * dL_dRGB);
+    store3(dL_dsh + 6, (C1 * z) * dL_dRGB);
+    store3(dL_dsh + 9, (-C1 * x) * dL_dRGB);
     written = 4;
     if (D > 1) {
       const float C20 = 1.0925484305920792f, C21 = -1.0925484305920792f, C22 = 0.31539156525252005f,
                   C23 = -1.0925484305920792f, C24 = 0.5462742152960396f;
       const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-      store3(dL_dsh + 12, (C20 * xy) * dL_dRGB, acc);
-      store3(dL_dsh + 15, (C21 * yz) * dL_dRGB, acc);
-      store3(dL_dsh + 18, (C22 * (2.f * zz - xx - yy)) * dL_dRGB, acc);
-      store3(dL_dsh + 21, (C23 * xz) * dL_dRGB, acc);
-      store3(dL_dsh + 24, (C24 * (xx - yy)) * dL_dRGB, acc);
       const f3 s4 = SH(4), s5 = SH(5), s6 = SH(6), s7 = SH(7), s8 = SH(8);
+      store3(dL_dsh + 12, (C20 * xy) * dL_dRGB);
+      store3(dL_dsh + 15, (C21 * yz) * dL_dRGB);
+      store3(dL_dsh + 18, (C22 * (2.f * zz - xx - yy)) * dL_dRGB);
+      store3(dL_dsh + 21, (C23 * xz) * dL_dRGB);
+      store3(dL_dsh + 24, (C24 * (xx - yy)) * dL_dRGB);
       dx = dx + (C20 * y) * s4 + (C22 * 2.f * -x) * s6 + (C23 * z) * s7 + (C24 * 2.f * x) * s8;
       dy = dy + (C20 * x) * s4 + (C21 * z) * s5 + (C22 * 2.f * -y) * s6 + (C24 * 2.f * -y) * s8;
       dz = dz + (C21 * y) * s5 + (C22 * 2.f * 2.f * z) * s6 + (C23 * x) * s7;
@@ -62,14 +62,14 @@ __device__ void sh_backward(int D, int M, const float* __restrict__ sh, f3 dir_o
         const float C30 = -0.5900435899266435f, C31 = 2.890611442640554f, C32 = -0.4570457994644658f,
                     C33 = 0.3731763325901154f, C34 = -0.4570457994644658f, C35 = 1.445305721320277f,
                     C36 = -0.5900435899266435f;
-        store3(dL_dsh + 27, (C30 * y * (3.f * xx - yy)) * dL_dRGB, acc);
-        store3(dL_dsh + 30, (C31 * xy * z) * dL_dRGB, acc);
-        store3(dL_dsh + 33, (C32 * y * (4.f * zz - xx - yy)) * dL_dRGB, acc);
-        store3(dL_dsh + 36, (C33 * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB, acc);
-        store3(dL_dsh + 39, (C34 * x * (4.f * zz - xx - yy)) * dL_dRGB, acc);
-        store3(dL_dsh + 42, (C35 * z * (xx - yy)) * dL_dRGB, acc);
-        store3(dL_dsh + 45, (C36 * x * (xx - 3.f * yy)) * dL_dRGB, acc);
         const f3 s9 = SH(9), s10 = SH(10), s11 = SH(11), s12 = SH(12), s13 = SH(13), s14 = SH(14), s15 = SH(15);
+        store3(dL_dsh + 27, (C30 * y * (3.f * xx - yy)) * dL_dRGB);
+        store3(dL_dsh + 30, (C31 * xy * z) * dL_dRGB);
+        store3(dL_dsh + 33, (C32 * y * (4.f * zz - xx - yy)) * dL_dRGB);
+        store3(dL_dsh + 36, (C33 * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB);
+        store3(dL_dsh + 39, (C34 * x * (4.f * zz - xx - yy)) * dL_dRGB);
+        store3(dL_dsh + 42, (C35 * z * (xx - yy)) * dL_dRGB);
+        store3(dL_dsh + 45, (C36 * x * (xx - 3.f * yy)) * dL_dRGB);
         dx = dx + ((C30 * 3.f * 2.f * xy) * s9 + (C31 * yz) * s10 + (C32 * -2.f * xy) * s11 +
                    (C33 * -3.f * 2.f * xz) * s12 + (C34 * (-3.f * xx + 4.f * zz - yy)) * s13 +
                    (C35 * 2.f * xz) * s14 + (C36 * 3.f * (xx - yy)) * s15);
@@ -83,8 +83,7 @@ __device__ void sh_backward(int D, int M, const float* __restrict__ sh, f3 dir_o
     }
   }
 #undef SH
-  if (!acc)
-    for (int k = written * 3; k < M * 3; k++) dL_dsh[k] = 0.0f;
+  for (int k = written * 3; k < M * 3; k++) dL_dsh[k] = 0.0f;
 
   const f3 dL_ddir = mk(dot(dx, dL_dRGB), dot(dy, dL_dRGB), dot(dz, dL_dRGB));
   // dnormvdv (auxiliary.h:128-138)
@@ -96,12 +95,87 @@ __device__ void sh_backward(int D, int M, const float* __restrict__ sh, f3 dir_o
   dL_dmean_add.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
 }
 
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocessParams p) {
+constexpr int PBWD_THREADS = 128;
+
+// SH rows travel through shared memory so that the 12*M-byte-per-surfel streams (shs in, dL_dsh out)
+// are read and written as fully coalesced 128-bit accesses by the warp instead of 3M scalar accesses
+// per thread at a 12*M-byte stride.  Row r of the warp sits at smem[r * (3M + 1)] (odd stride: the
+// per-lane accesses of the SH polynomial are bank-conflict free).
+__device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict__ g, int M, int rows,
+                                             unsigned vis_mask, int lane) {
+  const int rl = 3 * M, rs = rl + 1, total = rows * rl;
+  if (rows == 32 && (reinterpret_cast<size_t>(g) & 15) == 0) {
+    const float4* g4 = reinterpret_cast<const float4*>(g);
+    for (int f = lane; f < total / 4; f += 32) {
+      const int e0 = 4 * f, r0 = e0 / rl, r3 = (e0 + 3) / rl;
+      if (!((vis_mask >> r0) & 1u) && !((vis_mask >> r3) & 1u)) continue;
+      const float4 v = __ldg(g4 + f);
+      const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int e = 0; e < 4; e++) { const int idx = e0 + e, r = idx / rl; wsm[r * rs + (idx - r * rl)] = vv[e]; }
+    }
+  } else {
+    for (int idx = lane; idx < total; idx += 32) {
+      const int r = idx / rl;
+      if ((vis_mask >> r) & 1u) wsm[r * rs + (idx - r * rl)] = __ldg(g + idx);
+    }
+  }
+}
+
+__device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restrict__ g, int M, int rows,
+                                              unsigned vis_mask, bool acc, int lane) {
+  const int rl = 3 * M, rs = rl + 1, total = rows * rl;
+  if (rows == 32 && (reinterpret_cast<size_t>(g) & 15) == 0) {
+    float4* g4 = reinterpret_cast<float4*>(g);
+    for (int f = lane; f < total / 4; f += 32) {
+      const int e0 = 4 * f;
+      float vv[4];
+      bool any = false;
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        const int idx = e0 + e, r = idx / rl;
+        const bool vis = (vis_mask >> r) & 1u;
+        vv[e] = vis ? wsm[r * rs + (idx - r * rl)] : 0.0f;
+        any |= vis;
+      }
+      if (acc) {
+        if (!any) continue;
+        const float4 o = g4[f];
+        g4[f] = make_float4(o.x + vv[0], o.y + vv[1], o.z + vv[2], o.w + vv[3]);
+      } else {
+        g4[f] = make_float4(vv[0], vv[1], vv[2], vv[3]);
+      }
+    }
+  } else {
+    for (int idx = lane; idx < total; idx += 32) {
+      const int r = idx / rl;
+      const bool vis = (vis_mask >> r) & 1u;
+      const float v = vis ? wsm[r * rs + (idx - r * rl)] : 0.0f;
+      if (acc) { if (vis) g[idx] += v; }
+      else g[idx] = v;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(PBWD_THREADS) preprocess_bwd_kernel(const BwdPreprocessParams p) {
+  extern __shared__ float sh_smem[];
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= p.P) return;
-  const size_t i = (size_t)idx;
-  const bool visible = __ldg(p.radii + idx) > 0;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int warp_first = idx - lane;
+  if (warp_first >= p.P) return;  // whole warp out of range
+  const bool valid = idx < p.P;
+  const size_t i = (size_t)(valid ? idx : p.P - 1);
+  const bool visible = valid && __ldg(p.radii + idx) > 0;
   const bool acc = p.accumulate != 0;  // outputs += (view-parallel accumulation over local views)
+  const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
+  const int rows = min(32, p.P - warp_first);
+  float* wsm = sh_smem + (size_t)warp * 32 * (3 * p.M + 1);
+  float* my_row = wsm + lane * (3 * p.M + 1);
+  const bool has_sh = p.shs != nullptr && p.dL_dsh != nullptr;
+  if (has_sh) {
+    sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, p.M, rows, vis_mask, lane);
+    __syncwarp();
+  }
 
   f3 dmean3D = mk(0, 0, 0);
   float dmean2D_x = 0.f, dmean2D_y = 0.f, dopacity = 0.f;
@@ -109,7 +183,6 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocess
   float dscale_x = 0.f, dscale_y = 0.f;
   float4 drot = make_float4(0, 0, 0, 0);
   float dT[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-  bool sh_written = false;
 
   if (visible) {
     const float* g = p.grad_records + i * GREC;
@@ -233,7 +306,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocess
       dmean3D = dM[2];
     }
 
-    if (p.shs != nullptr) {
+    if (has_sh) {
       const int clamp_bits = __float_as_int(__ldg(&rec[4].w));
       f3 dRGB = dcolor;
       if (clamp_bits & 1) dRGB.x = 0.f;
@@ -241,9 +314,8 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocess
       if (clamp_bits & 4) dRGB.z = 0.f;
       const f3 dir_orig = mk(pos.x - p.campos[0], pos.y - p.campos[1], pos.z - p.campos[2]);
       f3 add;
-      sh_backward(p.D, p.M, p.shs + i * p.M * 3, dir_orig, dRGB, p.dL_dsh + i * p.M * 3, add, acc);
+      sh_backward(p.D, p.M, my_row, dir_orig, dRGB, add);
       dmean3D = dmean3D + add;
-      sh_written = true;
     }
 
     // densification heuristic (backward.cu:632-635); in the precomputed-T case the reference reads
@@ -254,6 +326,14 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocess
     dmean2D_y = a5 * depth * 0.5f * float(p.H);
   }
 
+  if (has_sh) {
+    __syncwarp();
+    sh_rows_store(wsm, p.dL_dsh + (size_t)warp_first * p.M * 3, p.M, rows, vis_mask, acc, lane);
+  } else if (p.dL_dsh != nullptr && valid && !acc) {
+    float* o = p.dL_dsh + i * p.M * 3;
+    for (int k = 0; k < p.M * 3; k++) o[k] = 0.f;
+  }
+  if (!valid) return;
   // the view-space gradient is per view (gm.py:551-553 takes its norm per view): never accumulated
   p.dL_dmeans2D[3 * i] = dmean2D_x; p.dL_dmeans2D[3 * i + 1] = dmean2D_y; p.dL_dmeans2D[3 * i + 2] = 0.f;
   if (acc) {
@@ -274,10 +354,6 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocess
     }
     return;
   }
-  if (p.dL_dsh != nullptr && !sh_written) {
-    float* o = p.dL_dsh + i * p.M * 3;
-    for (int k = 0; k < p.M * 3; k++) o[k] = 0.f;
-  }
   p.dL_dopacity[i] = dopacity;
   store3(p.dL_dmeans3D + 3 * i, dmean3D);
   if (p.dL_dcolors) store3(p.dL_dcolors + 3 * i, dcolor);
@@ -291,7 +367,13 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const BwdPreprocess
 
 void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream) {
   if (p.P <= 0) return;
-  preprocess_bwd_kernel<<<(p.P + 255) / 256, 256, 0, stream>>>(p);
+  const size_t smem = (size_t)(PBWD_THREADS / 32) * 32 * (3 * p.M + 1) * sizeof(float);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    cudaFuncSetAttribute(preprocess_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    configured = smem;
+  }
+  preprocess_bwd_kernel<<<(p.P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(p);
 }
 
 }  // namespace gsm

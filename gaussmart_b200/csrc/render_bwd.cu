@@ -208,7 +208,11 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, 4) render_bwd_kernel(const Bwd
         const float4 nrm = sm.q[s][3][j], col = sm.q[s][4][j];
         const float normal[3] = {nrm.x, nrm.y, nrm.z};
         const float color[3] = {col.x, col.y, col.z};
-        T = __fdiv_rn(T, SUB(1.0f, alpha));
+        // T is reconstructed by IEEE division exactly as the reference does (backward.cu:319): its error
+        // compounds along the list.  The other quotients below feed single gradient terms (bar: 1e-4 rel)
+        // and use the 2-ulp MUFU reciprocal instead of the reference's 8 div.rn per pair.
+        const float one_m_alpha = SUB(1.0f, alpha);
+        T = __fdiv_rn(T, one_m_alpha);
         const float w = alpha * T;
         float dL_dalpha = 0.0f;
 #pragma unroll
@@ -219,8 +223,9 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, 4) render_bwd_kernel(const Bwd
           v[11 + ch] = w * dL_dpixel[ch];
         }
         float dL_dz = 0.0f;
-        const float m_d = far_ratio * (1.0f - NEAR_N / c_d);
-        const float dmd_dd = (FAR_N * NEAR_N) / ((FAR_N - NEAR_N) * c_d * c_d);
+        const float near_over_d = __fdiv_rn(NEAR_N, c_d);  // exact: m_d enters a cancelling sum below
+        const float m_d = far_ratio * (1.0f - near_over_d);
+        const float dmd_dd = (FAR_N / ((FAR_N - NEAR_N) * NEAR_N)) * near_over_d * near_over_d;
         if (k == median_contributor - 1) dL_dz += dL_dmedian_depth;
         const float dL_dweight = (final_D2 + m_d * m_d * final_A - 2.0f * m_d * final_D) * dL_dreg;
         dL_dalpha += dL_dweight - last_dL_dT;
@@ -245,7 +250,7 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, 4) render_bwd_kernel(const Bwd
 
         dL_dalpha *= T;
         last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+        dL_dalpha += (-T_final * __fdividef(1.0f, one_m_alpha)) * bg_dot_dpixel;
 
         const float dL_dG = c.w * dL_dalpha;
         dL_dz += alpha * T * dL_ddepth;
@@ -253,7 +258,8 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, 4) render_bwd_kernel(const Bwd
         if (rho3d <= rho2d) {
           const float dL_dsx = dL_dG * -G * sx + dL_dz * c.x;
           const float dL_dsy = dL_dG * -G * sy + dL_dz * c.y;
-          const float dsx_pz = dL_dsx / ppz, dsy_pz = dL_dsy / ppz;
+          const float rpz = __fdividef(1.0f, ppz);
+          const float dsx_pz = dL_dsx * rpz, dsy_pz = dL_dsy * rpz;
           const float dpx = dsx_pz, dpy = dsy_pz, dpz = -(dsx_pz * sx + dsy_pz * sy);
           // dL_dk = l x dL_dp ; dL_dl = dL_dp x k
           const float dkx = ly * dpz - lz * dpy, dky = lz * dpx - lx * dpz, dkz = lx * dpy - ly * dpx;

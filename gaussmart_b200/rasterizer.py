@@ -155,14 +155,16 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
                 raise RuntimeError(f"output tensor for {name} must be contiguous float32 {tuple(shape)} on {dev}")
             return t
 
+        # gradients of inputs that were not given are neither allocated nor written (NULL selects that
+        # in the kernel); autograd returns None for them, as the reference's front end does (dsr.py:144-154)
         dL_dmeans3D = _out("means3D", (P, 3))
         dL_dmeans2D = torch.empty((P, 3), **f32)
-        dL_dcolors = _out("colors_precomp", (P, 3))
+        dL_dcolors = _out("colors_precomp", (P, 3)) if colors_precomp.numel() != 0 else None
         dL_dopacity = _out("opacities", (P, 1))
-        dL_dtransMat = _out("cov3D_precomp", (P, 9))
-        dL_dsh = _out("shs", (P, M, 3))
-        dL_dscales = _out("scales", (P, 2))
-        dL_drotations = _out("rotations", (P, 4))
+        dL_dtransMat = _out("cov3D_precomp", (P, 9)) if cov3Ds_precomp.numel() != 0 else None
+        dL_dsh = _out("shs", (P, M, 3)) if M != 0 else None
+        dL_dscales = _out("scales", (P, 2)) if scales.numel() != 0 else None
+        dL_drotations = _out("rotations", (P, 4)) if rotations.numel() != 0 else None
         if P != 0:
             gws = torch.empty((lib.gsm_grad_workspace_bytes(P),), dtype=torch.uint8, device=dev)
             a = _lib.BackwardArgs()

@@ -38,17 +38,21 @@ class GradBucket:
 
     def __init__(self, P: int, M: int, device, with_stats: bool = True):
         self.P, self.M = P, M
-        n = P * floats_per_surfel(M)
-        self.flat = torch.zeros(n, dtype=torch.float32, device=device)
-        self.views: Dict[str, torch.Tensor] = {}
-        off = 0
+        # every segment starts on a 128-byte boundary (the kernels use 128-bit accesses)
+        sizes = []
         for name, shape_of in SEGMENTS:
             shape = (P,) + shape_of(M)
             cnt = 1
             for s in shape:
                 cnt *= s
+            sizes.append((name, shape, cnt))
+        n = sum((cnt + 31) // 32 * 32 for _, _, cnt in sizes)
+        self.flat = torch.zeros(n, dtype=torch.float32, device=device)
+        self.views: Dict[str, torch.Tensor] = {}
+        off = 0
+        for name, shape, cnt in sizes:
             self.views[name] = self.flat[off:off + cnt].view(shape)
-            off += cnt
+            off += (cnt + 31) // 32 * 32
         assert off == n
         # densification statistics (gm.py:551-553): [0] sum of per-view ||dL_dmean2D.xy||, [1] visibility count
         self.stats = torch.zeros(2, P, dtype=torch.float32, device=device) if with_stats else None

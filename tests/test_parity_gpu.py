@@ -275,3 +275,37 @@ def test_conservative_culling_changes_nothing(name, P, W, H, smul, zs):
         if k.startswith("grad_") and a[k] is not None:
             viol, _ = grad_violations(a[k].cpu(), b[k].cpu(), rel=1e-4, floor=1e-6)
             assert viol <= 1e-5 * a[k].numel() + 1, (k, viol)
+
+
+@pytest.mark.parametrize("P", [5000, 4999 + 32 * 7])  # a partial last warp as well
+def test_bucket_path_matches_autograd_and_accumulates(P):
+    """rasterize_into_bucket (K6 writes the flat view-parallel gradient bucket, optionally accumulating)
+    against the public autograd API."""
+    from gaussmart_b200 import view_parallel as vp
+    from gaussmart_b200.rasterizer import rasterize_into_bucket
+    W, H, deg = 160, 120, 3
+    scene = synthetic.make_scene(P, W, deg, 91)
+    scene = scene._replace(scales=scene.scales * 2.0)
+    cams = [synthetic.make_camera(W, H, th) for th in (0.0, 0.7)]
+    cot = synthetic.make_cotangents(W, H, 17)
+    outs = [run_cuda(gb, scene, c, 0.0, cot, "sh") for c in cams]
+    params = dict(means3D=scene.means3D.cuda(), shs=scene.shs.cuda(), opacities=scene.opacities.cuda(),
+                  scales=scene.scales.cuda(), rotations=scene.rotations.cuda())
+    bucket = vp.GradBucket(P, 16, "cuda")
+    bucket.flat.fill_(float("nan"))  # the first view must overwrite everything
+    for j, c in enumerate(cams):
+        cam_d = synthetic.Camera(*[x.cuda() if isinstance(x, torch.Tensor) else x for x in c])
+        color, radii, allmap, backward = rasterize_into_bucket(params, cam_d, bucket, j > 0)
+        assert torch.equal(color, outs[j]["color"]) and torch.equal(radii, outs[j]["radii"])
+        d2 = backward(cot[0].cuda(), cot[1].cuda())
+        viol, _ = grad_violations(d2.cpu(), outs[j]["grad_means2D"].cpu())
+        assert viol == 0
+        if j == 0:
+            for k in ("means3D", "shs", "opacities", "scales", "rotations"):
+                viol, _ = grad_violations(bucket.views[k].cpu(), outs[0]["grad_" + k].cpu())
+                assert viol <= 2, (k, viol)
+    for k in ("means3D", "shs", "opacities", "scales", "rotations"):
+        want = outs[0]["grad_" + k] + outs[1]["grad_" + k]
+        assert torch.isfinite(bucket.views[k]).all()
+        viol, _ = grad_violations(bucket.views[k].cpu(), want.cpu(), rel=1e-4, floor=1e-6)
+        assert viol <= 2, (k, viol)

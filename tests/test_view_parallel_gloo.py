@@ -24,9 +24,11 @@ def test_shard_views_partition():
 
 
 def test_bucket_layout():
-    P, M = 10, 16
+    P, M = 32, 16
     b = vp.GradBucket(P, M, "cpu")
     assert vp.floats_per_surfel(M) == 58 and b.flat.numel() == 58 * P  # 232 B/surfel
+    assert all(v.data_ptr() % 128 == b.flat.data_ptr() % 128 for v in b.views.values())
+    assert vp.GradBucket(33, M, "cpu").flat.numel() >= 58 * 33  # odd sizes: segments padded to 128 B
     assert b.views["shs"].shape == (P, 16, 3) and b.views["rotations"].shape == (P, 4)
     # segments alias the flat buffer, are disjoint and cover it
     for i, (name, _) in enumerate(vp.SEGMENTS):
@@ -70,7 +72,8 @@ def _worker(rank, world, port, n_views, P, q):
         res = vp.view_parallel_step(params, list(range(n_views)), bucket,
                                     cotangent_fn=lambda v, c, a: (torch.ones(3, 4, 4) / 48.0, torch.zeros(7, 4, 4)),
                                     raster_fn=_stub_raster)
-        q.put((rank, [int(r.color[0, 0, 0].item()) for r in res], bucket.flat.clone(), bucket.stats.clone(),
+        q.put((rank, [int(r.color[0, 0, 0].item()) for r in res],
+               torch.cat([v.reshape(-1) for v in bucket.views.values()]), bucket.stats.clone(),
                bucket.max_radii.clone()))
     finally:
         dist.destroy_process_group()

@@ -325,15 +325,21 @@ def cpu_baseline(full_entries_per_iter, deg):
     cam = synthetic.make_camera(128, 128, 0.0)
     cot = synthetic.make_cotangents(128, 128, 777)
     t0 = time.time()
-    f = so.rasterize_forward(scene.means3D, scene.opacities, cam.world_view_transform, cam.full_proj_transform,
-                             cam.camera_center, 128, 128, cam.tanfovx, cam.tanfovy, torch.zeros(3),
-                             sh_degree=deg, shs=scene.shs, scales=scene.scales, rotations=scene.rotations)
-    so.rasterize_backward(f, cot[0], cot[1])
+    entries, reps = 0, 0
+    while True:  # >= 10 s of CPU work (bounded: each repetition is a fresh crop of the same distribution)
+        scene = synthetic.make_scene(10_000, 128, deg, synthetic.BASE_SEED + 1 + reps)
+        f = so.rasterize_forward(scene.means3D, scene.opacities, cam.world_view_transform, cam.full_proj_transform,
+                                 cam.camera_center, 128, 128, cam.tanfovx, cam.tanfovy, torch.zeros(3),
+                                 sh_degree=deg, shs=scene.shs, scales=scene.scales, rotations=scene.rotations)
+        so.rasterize_backward(f, cot[0], cot[1])
+        entries += int(f["n_contrib"].reshape(2, -1)[0].long().sum().item())
+        reps += 1
+        if time.time() - t0 >= 10.0 or reps >= 20:
+            break
     dt = time.time() - t0
-    entries = int(f["n_contrib"].reshape(2, -1)[0].long().sum().item())
     per_s = entries / dt
     return dict(value=per_s / max(full_entries_per_iter, 1), unit=UNIT, cores=cores, kind="port",
-                sample=f"oracle fwd+bwd of 10k surfels @128x128 SH{deg} in {dt:.1f} s ({entries} list entries); "
+                sample=f"oracle fwd+bwd of {reps} x (10k surfels @128x128 SH{deg}) in {dt:.1f} s ({entries} list entries); "
                        f"extrapolated per list entry to the full workload ({full_entries_per_iter} entries/iter)",
                 sample_seconds=dt)
 

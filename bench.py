@@ -290,11 +290,10 @@ def stage_model(wl, wc, deg):
     K = (deg + 1) ** 2
     Pv, R, C = wc["P_vis"], wc["R"], wc["C"]
     m = {}
-    m["preprocess_fwd"] = ("hbm", 48 * P + (79 + 12 * K) * Pv)
-    m["scan"] = ("hbm", 8 * P)
-    m["duplicate"] = ("hbm", 20 * Pv + 12 * R)
-    m["sort"] = ("hbm", 24 * R)
-    m["ranges"] = ("hbm", 8 * R + 8 * Nt)
+    m["preprocess_fwd"] = ("hbm", 48 * P + (79 + 8 + 12 * K) * Pv)
+    m["tile_scan"] = ("hbm", 20 * Nt)
+    m["scatter"] = ("hbm", 4 * P + 20 * Pv + 8 * R)          # radii + (centre, depth) in, 8-B pairs out
+    m["tile_sort"] = ("hbm", 8 * R + 13 * R + 8 * R)          # pairs in; list + keys + mask out; box gathered
     m["render_fwd"] = ("fp32", 75 * C + 35 * (wc["E_fwd"] - C))
     m["grad_zero"] = ("hbm", 80 * P)
     m["render_bwd"] = ("fp32", 210 * C + 35 * (wc["E_bwd"] - C))
@@ -494,7 +493,7 @@ def main():
                         "derived: 148 SMs x 128 FP32 lanes x 2 x sm_max_mhz (no tensor-core work on this path)"}
     line["stages"] = rows
     line["work"] = wc
-    kernels_per_stage = {"preprocess_fwd": 1, "scan": 1, "duplicate": 1, "sort": SORT_KERNELS, "ranges": 1,
+    kernels_per_stage = {"preprocess_fwd": 1, "tile_scan": 1, "scatter": 1, "tile_sort": 3,
                          "render_fwd": 1, "grad_zero": 0, "render_bwd": 1, "preprocess_bwd": 1}
     line["gpu_launches"] = int(sum(kernels_per_stage.get(n, 0) * c for n, (_, c) in stages.items()))
     if world == 1 and not args.no_cpu_baseline:
@@ -504,9 +503,6 @@ def main():
         dist.destroy_process_group()
     return 0
 
-
-# kernels launched by the sort stage per call (CUB onesweep: histogram + scan + one pass per 8-bit digit)
-SORT_KERNELS = 8
 
 if __name__ == "__main__":
     sys.exit(main())

@@ -8,7 +8,8 @@ import os
 from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libgaussmart_b200.so")
+# GAUSSMART_B200_LIB selects a tuning variant built by `python -m gaussmart_b200.build --tag=... -D...`
+LIB_PATH = os.environ.get("GAUSSMART_B200_LIB") or os.path.join(_HERE, "lib", "libgaussmart_b200.so")
 
 GSM_OK = 0
 GSM_ERR_INVALID_ARGUMENT = 10001

@@ -25,9 +25,13 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_native(force=False, verbose=False):
+def build_native(force=False, verbose=False, defines=(), tag=None):
+    """tag/defines: build a tuning variant lib/libgaussmart_b200_<tag>.so with extra -D flags (selected at run
+    time with GAUSSMART_B200_LIB=<path>); the default build takes neither."""
     os.makedirs(LIBDIR, exist_ok=True)
-    objdir = os.path.join(LIBDIR, "obj")
+    objdir = os.path.join(LIBDIR, "obj" if tag is None else "obj_" + tag)
+    lib = LIB if tag is None else os.path.join(LIBDIR, f"libgaussmart_b200_{tag}.so")
+    flags = NVCC_FLAGS + ["-D" + d for d in defines]
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, "common.cuh"),
                os.path.join(HERE, "..", "include", "gaussmart_b200.h")]
@@ -37,7 +41,7 @@ def build_native(force=False, verbose=False):
         obj = os.path.join(objdir, s + ".o")
         objs.append(obj)
         if force or _stale(obj, [src] + headers):
-            cmds.append(["nvcc"] + NVCC_FLAGS + ["-c", src, "-o", obj])
+            cmds.append(["nvcc"] + flags + ["-c", src, "-o", obj])
     if cmds:
         with ThreadPoolExecutor(8) as ex:
             for cmd, r in zip(cmds, ex.map(lambda c: subprocess.run(c, capture_output=True, text=True), cmds)):
@@ -45,11 +49,13 @@ def build_native(force=False, verbose=False):
                     print(r.stderr)
                 if r.returncode != 0:
                     raise RuntimeError("nvcc failed: %s\n%s" % (" ".join(cmd), r.stderr[-6000:]))
-    if cmds or not os.path.exists(LIB):
-        subprocess.check_call(["nvcc", "-shared", "-o", LIB] + objs +
+    if cmds or not os.path.exists(lib):
+        subprocess.check_call(["nvcc", "-shared", "-o", lib] + objs +
                               ["-gencode", "arch=compute_100a,code=sm_100a"])
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    print(build_native(force="--force" in sys.argv, verbose=True))
+    defs = [a[2:] for a in sys.argv[1:] if a.startswith("-D")]
+    tags = [a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--tag=")]
+    print(build_native(force="--force" in sys.argv, verbose=True, defines=defs, tag=tags[0] if tags else None))

@@ -27,7 +27,7 @@ int cuda_fail(cudaError_t e, const char* what) {
 // ---- optional per-stage device timing (gsm_stage_timing_*): cudaEvent pairs recorded on the
 // launching stream around every stage, resolved lazily when read.  Off by default.
 static const char* const kStageNames[GSM_NUM_STAGES] = {
-    "preprocess_fwd", "scan", "duplicate", "sort", "ranges", "render_fwd",
+    "preprocess_fwd", "tile_scan", "scatter", "tile_sort", "unused", "render_fwd",
     "grad_zero", "render_bwd", "preprocess_bwd", "knn"};
 
 struct StageTimer {
@@ -83,10 +83,7 @@ GeometryLayout geometry_layout(int P) {
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 128); return o; };
   L.records = take(n * GSM_SURFEL_RECORD_BYTES);
   L.bbox = take(n * 8);
-  L.tiles_touched = take(n * 4);
-  L.offsets = take(n * 4);
-  L.scan_temp_bytes = scan_temp_bytes(P);
-  L.scan_temp = take(L.scan_temp_bytes);
+  L.rects = take(n * 16);
   L.flags = take(16);
   L.total = off + 128;
   return L;
@@ -101,6 +98,9 @@ ImageLayout image_layout(int width, int height) {
   L.final_T = take(N * 3 * 4);
   L.n_contrib = take(N * 2 * 4);
   L.ranges = take(Nt * 8);
+  L.tile_count = take(Nt * 4 * TILE_SUBS);
+  L.tile_cursor = take(Nt * 4 * TILE_SUBS);
+  L.num_rendered = take(16);
   L.total = off + 128;
   return L;
 }
@@ -114,19 +114,9 @@ BinningLayout binning_layout(size_t capacity, int width, int height) {
   L.strip_mask = take(capacity + 4);
   L.persistent = off;
   L.keys_sorted = take(capacity * 8);
-  L.keys_unsorted = take(capacity * 8);
-  L.values_unsorted = take(capacity * 4);
-  L.sort_temp_bytes = sort_temp_bytes(capacity);
-  L.sort_temp = take(L.sort_temp_bytes);
+  L.pairs = take(capacity * 8);
   L.total = off + 128;
   return L;
-}
-
-// same function as getHigherMsb (rasterizer_impl.cu:35-50): number of bits needed for n
-static int higher_msb(uint32_t n) {
-  int bits = 0;
-  while (bits < 32 && (n >> bits)) bits++;
-  return bits;
 }
 
 }  // namespace gsm
@@ -199,39 +189,44 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
   char* geom = aligned_base(a->geometry);
   char* img = aligned_base(a->image);
   float4* records = (float4*)(geom + G.records);
-  uint32_t* tiles_touched = (uint32_t*)(geom + G.tiles_touched);
-  uint32_t* offsets = (uint32_t*)(geom + G.offsets);
   uint32_t* flags = (uint32_t*)(geom + G.flags);
   uint2* ranges = (uint2*)(img + I.ranges);
+  uint32_t* tile_count = (uint32_t*)(img + I.tile_count);
+  uint32_t* tile_cursor = (uint32_t*)(img + I.tile_cursor);
+  unsigned long long* total_dev = (unsigned long long*)(img + I.num_rendered);
 
   int R = 0;
   if (P > 0) {
     GSM_CUDA(cudaMemsetAsync(flags, 0, 16, stream));
+    GSM_CUDA(cudaMemsetAsync(tile_count, 0, sizeof(uint32_t) * (size_t)num_tiles * TILE_SUBS, stream));
     FwdPreprocessParams pp{};
     pp.P = P; pp.D = a->D; pp.M = a->M; pp.W = W; pp.H = H; pp.grid_x = grid_x; pp.grid_y = grid_y;
     pp.scale_modifier = a->scale_modifier; pp.prefiltered = a->prefiltered;
     pp.means3D = a->means3D; pp.scales = a->scales; pp.rotations = a->rotations; pp.opacities = a->opacities;
     pp.shs = a->shs; pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;
     pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
-    pp.radii = a->radii; pp.records = records; pp.bbox = (short4*)(geom + G.bbox); pp.tiles_touched = tiles_touched; pp.flags = flags;
+    pp.radii = a->radii; pp.records = records; pp.bbox = (short4*)(geom + G.bbox); pp.rects = (uint4*)(geom + G.rects); pp.tile_count = tile_count; pp.flags = flags;
     { StageMark m(GSM_STAGE_PREPROCESS_FWD, stream); launch_preprocess_fwd(pp, stream); }
     GSM_STAGE("forward preprocess");
     {
       StageMark m(GSM_STAGE_SCAN, stream);
-      GSM_CUDA(launch_inclusive_scan(tiles_touched, offsets, P, geom + G.scan_temp, G.scan_temp_bytes, stream));
+      launch_tile_scan(tile_count, tile_cursor, ranges, num_tiles, total_dev, stream);
     }
     GSM_STAGE("tile-count scan");
     // S1: the one host<-device dependency of the forward (rasterizer_impl.cu:282)
-    uint32_t host_vals[2] = {0, 0};
-    GSM_CUDA(cudaMemcpyAsync(&host_vals[0], offsets + P - 1, 4, cudaMemcpyDeviceToHost, stream));
-    GSM_CUDA(cudaMemcpyAsync(&host_vals[1], flags, 4, cudaMemcpyDeviceToHost, stream));
+    unsigned long long host_total = 0;
+    uint32_t host_flag = 0;
+    GSM_CUDA(cudaMemcpyAsync(&host_total, total_dev, 8, cudaMemcpyDeviceToHost, stream));
+    GSM_CUDA(cudaMemcpyAsync(&host_flag, flags, 4, cudaMemcpyDeviceToHost, stream));
     GSM_CUDA(cudaStreamSynchronize(stream));
-    if (host_vals[1] != 0) {
+    if (host_flag != 0) {
       set_error("Point is filtered although prefiltered is set. This shouldn't happen!");
       return GSM_ERR_INVALID_ARGUMENT;
     }
-    if (host_vals[0] > 0x7fffffffu) { set_error("gsm_forward: too many instances"); return GSM_ERR_INVALID_ARGUMENT; }
-    R = (int)host_vals[0];
+    if (host_total > 0x7fffffffull) { set_error("gsm_forward: too many instances"); return GSM_ERR_INVALID_ARGUMENT; }
+    R = (int)host_total;
+  } else {
+    GSM_CUDA(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream));
   }
   *a->num_rendered_host = R;
   if ((size_t)R > a->binning_capacity) {
@@ -245,30 +240,19 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
       set_error("gsm_forward: binning workspace too small"); return GSM_ERR_WORKSPACE_TOO_SMALL;
     }
     bin = aligned_base(a->binning);
-    uint64_t* keys_unsorted = (uint64_t*)(bin + B.keys_unsorted);
-    uint64_t* keys_sorted = (uint64_t*)(bin + B.keys_sorted);
-    uint32_t* values_unsorted = (uint32_t*)(bin + B.values_unsorted);
-    uint32_t* point_list = (uint32_t*)(bin + B.point_list);
+    uint2* pairs = (uint2*)(bin + B.pairs);
     {
       StageMark m(GSM_STAGE_DUPLICATE, stream);
-      launch_duplicate_with_keys(P, records, offsets, a->radii, keys_unsorted, values_unsorted, grid_x, grid_y, stream);
+      launch_scatter(P, (const uint4*)(geom + G.rects), a->radii, tile_cursor, pairs, grid_x, stream);
     }
-    GSM_STAGE("duplicate with keys");
-    const int end_bit = 32 + higher_msb((uint32_t)num_tiles);
+    GSM_STAGE("scatter");
     {
       StageMark m(GSM_STAGE_SORT, stream);
-      GSM_CUDA(launch_sort_pairs(keys_unsorted, keys_sorted, values_unsorted, point_list, (size_t)R, end_bit,
-                                 bin + B.sort_temp, B.sort_temp_bytes, stream));
+      launch_tile_sort(ranges, pairs, (uint64_t*)(bin + B.keys_sorted), (uint32_t*)(bin + B.point_list),
+                       (uint8_t*)(bin + B.strip_mask), (const short4*)(geom + G.bbox), grid_x, num_tiles,
+                       (a->debug & 2) ? 1 : 0, stream);
     }
-    GSM_STAGE("sort");
-    {
-      StageMark m(GSM_STAGE_RANGES, stream);
-      launch_tile_ranges((size_t)R, keys_sorted, point_list, (const short4*)(geom + G.bbox), ranges,
-                         (uint8_t*)(bin + B.strip_mask), grid_x, num_tiles, (a->debug & 2) ? 1 : 0, stream);
-    }
-    GSM_STAGE("tile ranges");
-  } else {
-    GSM_CUDA(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream));
+    GSM_STAGE("tile sort");
   }
   if (P > 0) {  // the reference returns zero images without launching when P == 0 (rasterize_points.cu:99)
     FwdRenderParams rp{};

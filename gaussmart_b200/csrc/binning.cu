@@ -1,173 +1,120 @@
-// Tile binning for sm_100a: inclusive scan of tile counts, duplicate-with-keys, tile ranges.
+// Tile binning for sm_100a: (tile | depth) ordering of the (surfel, tile) instances, tile ranges,
+// strip masks.
 //
-// Restates rasterizer_impl.cu:70-138 (duplicateWithKeys, identifyTileRanges) and the
-// cub::DeviceScan::InclusiveSum call site rasterizer_impl.cu:278.  All integer work: results are
-// bit-exact by construction (key = tile_id << 32 | bits(depth), emitted y-major / x-minor in
-// surfel order, so a stable sort reproduces the reference's permutation).
+// WHAT it produces is exactly what the reference produces with duplicateWithKeys +
+// cub::DeviceRadixSort::SortPairs + identifyTileRanges (rasterizer_impl.cu:70-138,278-319):
+//   keys_sorted[R]  = (tile_id << 32 | bits(view depth)) ascending,
+//   point_list[R]   = surfel index of every instance, ties (equal tile AND equal depth bits) in
+//                     ascending surfel index (what a stable sort of the reference's emission order gives),
+//   ranges[t]       = [first, last+1) of tile t, (0,0) for untouched tiles.
+// All integer work: bit-exact by construction.
+//
+// HOW is different.  The reference sorts R 96-bit pairs globally with a 6-pass LSD radix sort over
+// 44 bits (152 B of HBM traffic per instance).  The key has structure the global sort ignores: its
+// high part is a small dense integer (the tile) that the compositing kernels only ever need as a
+// PARTITION.  So:
+//   1. the forward preprocess counts instances per tile (one red.global.add per instance);
+//   2. tile_scan_kernel turns the counts into ranges (exclusive scan over the Nt tiles, not over
+//      the P surfels) -- this replaces cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:278);
+//   3. scatter_kernel reads every visible surfel's tile rect (computed by the forward preprocess
+//      exactly as getRect does, auxiliary.h:67-77) and appends (depth bits, surfel) to its tiles' segments through a
+//      per-tile cursor (order inside a segment is arbitrary at this point);
+//   4. tile_sort_kernel sorts each segment by depth bits with a block-wide LSD radix sort held
+//      entirely in shared memory (only as many 8-bit passes as the segment's depth bits actually
+//      differ in, typically 4), fixes the order of equal-depth runs to ascending surfel index,
+//      and writes point_list, keys_sorted and the strip mask of every instance.
+// HBM traffic: 8 B written + 8 B read + 13 B written per instance (29 B vs 152 B).
 #include "common.cuh"
 
 namespace gsm {
 
 // ---------------------------------------------------------------------------------------------
-// Inclusive scan: single-pass decoupled look-back (one kernel, 2 x 4 bytes/elem of HBM traffic).
-// Tile state word: bits 31..30 = status (0 invalid, 1 aggregate, 2 inclusive prefix), 29..0 value
-// is not enough for R up to 2^32, so state is a 64-bit word: high 32 = status, low 32 = value.
+// 2. exclusive scan of the per-tile instance counts -> ranges, total R; resets the cursors
 // ---------------------------------------------------------------------------------------------
-constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_ITEMS = 16;  // 4 x uint4 per thread
-constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+constexpr int TSCAN_THREADS = 1024;
 
-size_t scan_temp_bytes(int P) {
-  const size_t tiles = ((size_t)P + SCAN_TILE - 1) / SCAN_TILE;
-  return align_up(sizeof(unsigned long long) * (tiles + 1) + 16, 128);
-}
-
-__global__ void __launch_bounds__(SCAN_THREADS)
-scan_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int P,
-            unsigned long long* __restrict__ state, unsigned int* __restrict__ ticket) {
-  __shared__ uint32_t warp_sums[SCAN_THREADS / 32];
-  __shared__ uint32_t s_tile, s_prefix;
-  if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);  // dynamic tile id => forward progress
-  __syncthreads();
-  const uint32_t tile = s_tile;
-  const size_t base = (size_t)tile * SCAN_TILE;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-
-  // blocked arrangement within a warp-striped layout: thread t owns items [t*16, t*16+16)
-  uint32_t v[SCAN_ITEMS];
-  const size_t tbase = base + (size_t)threadIdx.x * SCAN_ITEMS;
-  if (tbase + SCAN_ITEMS <= (size_t)P) {
-    const uint4* src = reinterpret_cast<const uint4*>(in + tbase);
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS / 4; i++) {
-      const uint4 q = __ldg(src + i);
-      v[4 * i] = q.x; v[4 * i + 1] = q.y; v[4 * i + 2] = q.z; v[4 * i + 3] = q.w;
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (tbase + i < (size_t)P) ? __ldg(in + tbase + i) : 0u;
+// tile_count / tile_cursor are [Nt][TILE_SUBS]: a tile's instances are counted and appended through
+// TILE_SUBS sub-cursors selected by the surfel index, because same-address atomics WITH return
+// serialise in L2 (~27 cycles each): one cursor per tile makes the hottest tile the critical path.
+__global__ void __launch_bounds__(TSCAN_THREADS)
+tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_cursor,
+                 uint2* __restrict__ ranges, int num_tiles, unsigned long long* __restrict__ total_out) {
+  __shared__ unsigned long long warp_sums[TSCAN_THREADS / 32];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int per = (num_tiles + TSCAN_THREADS - 1) / TSCAN_THREADS;
+  const int begin = min(t * per, num_tiles), end = min(begin + per, num_tiles);
+  unsigned long long local = 0;
+  static_assert(TILE_SUBS % 4 == 0, "tile counters are read as uint4");
+  const uint4* cnt4 = reinterpret_cast<const uint4*>(tile_count);
+  for (int i = begin * (TILE_SUBS / 4); i < end * (TILE_SUBS / 4); i++) {
+    const uint4 c = __ldg(cnt4 + i);
+    local += (unsigned long long)c.x + c.y + c.z + c.w;
   }
-  uint32_t tsum = 0;
-#pragma unroll
-  for (int i = 0; i < SCAN_ITEMS; i++) { tsum += v[i]; v[i] = tsum; }
-
-  // warp inclusive scan of thread sums
-  uint32_t inc = tsum;
+  unsigned long long inc = local;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += n;
+    const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
   }
   if (lane == 31) warp_sums[warp] = inc;
   __syncthreads();
-  uint32_t warp_off = 0, block_sum = 0;
-#pragma unroll
-  for (int w = 0; w < SCAN_THREADS / 32; w++) {
-    const uint32_t s = warp_sums[w];
+  unsigned long long warp_off = 0, total = 0;
+  for (int w = 0; w < TSCAN_THREADS / 32; w++) {
+    const unsigned long long s = warp_sums[w];
     if (w < warp) warp_off += s;
-    block_sum += s;
+    total += s;
   }
-  const uint32_t thread_excl = warp_off + inc - tsum;
-
-  // publish aggregate, look back for the exclusive prefix (warp 0)
-  if (warp == 0) {
-    if (lane == 0) {
-      const unsigned long long st = ((tile == 0 ? 2ull : 1ull) << 32) | block_sum;
-      atomicExch(&state[tile], st);
+  unsigned long long run = warp_off + inc - local;
+  for (int i = begin; i < end; i++) {
+    const unsigned long long first = run;
+    uint4* cur4 = reinterpret_cast<uint4*>(tile_cursor) + (size_t)i * (TILE_SUBS / 4);
+#pragma unroll
+    for (int k = 0; k < TILE_SUBS / 4; k++) {
+      const uint4 c = __ldg(cnt4 + (size_t)i * (TILE_SUBS / 4) + k);
+      uint4 o;  // absolute slot of each sub-segment's next pair
+      o.x = (uint32_t)run; run += c.x;
+      o.y = (uint32_t)run; run += c.y;
+      o.z = (uint32_t)run; run += c.z;
+      o.w = (uint32_t)run; run += c.w;
+      cur4[k] = o;
     }
-    uint32_t prefix = 0;
-    if (tile > 0) {
-      int look = (int)tile - 1;
-      while (true) {
-        const int j = look - lane;
-        unsigned long long st = 0;
-        if (j >= 0) {
-          do { st = *reinterpret_cast<volatile unsigned long long*>(&state[j]); } while ((st >> 32) == 0);
-        } else {
-          st = 2ull << 32;  // virtual tile before the first: inclusive prefix 0
-        }
-        const uint32_t status = (uint32_t)(st >> 32), val = (uint32_t)st;
-        const unsigned full = __ballot_sync(0xffffffffu, status == 2);
-        // sum values of lanes up to and including the first lane with an inclusive prefix
-        const int first = full ? (__ffs(full) - 1) : 32;
-        uint32_t contrib = (lane <= first) ? val : 0u;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
-        prefix += contrib;
-        if (full) break;
-        look -= 32;
-      }
-      if (lane == 0) {
-        atomicExch(&state[tile], (2ull << 32) | (unsigned long long)(uint32_t)(prefix + block_sum));
-      }
-    }
-    if (lane == 0) s_prefix = prefix;
+    ranges[i] = run > first ? make_uint2((uint32_t)first, (uint32_t)run) : make_uint2(0u, 0u);
   }
-  __syncthreads();
-  const uint32_t off = s_prefix + thread_excl;
-  if (tbase + SCAN_ITEMS <= (size_t)P) {
-    uint4* dst = reinterpret_cast<uint4*>(out + tbase);
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS / 4; i++)
-      dst[i] = make_uint4(v[4 * i] + off, v[4 * i + 1] + off, v[4 * i + 2] + off, v[4 * i + 3] + off);
-  } else {
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++)
-      if (tbase + i < (size_t)P) out[tbase + i] = v[i] + off;
-  }
+  if (t == 0) *total_out = total;
 }
 
-cudaError_t launch_inclusive_scan(const uint32_t* in, uint32_t* out, int P, void* temp,
-                                  size_t temp_bytes, cudaStream_t stream) {
-  if (P <= 0) return cudaSuccess;
-  const size_t need = scan_temp_bytes(P);
-  if (temp_bytes < need) return cudaErrorInvalidValue;
-  cudaError_t e = cudaMemsetAsync(temp, 0, need, stream);
-  if (e != cudaSuccess) return e;
-  const int tiles = (P + SCAN_TILE - 1) / SCAN_TILE;
-  unsigned int* ticket = reinterpret_cast<unsigned int*>(temp);
-  unsigned long long* state = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(temp) + 16);
-  scan_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(in, out, P, state, ticket);
-  return cudaGetLastError();
+void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* ranges, int num_tiles,
+                      unsigned long long* total_out, cudaStream_t stream) {
+  tile_scan_kernel<<<1, TSCAN_THREADS, 0, stream>>>(tile_count, tile_cursor, ranges, num_tiles, total_out);
 }
 
 // ---------------------------------------------------------------------------------------------
-// duplicate-with-keys (rasterizer_impl.cu:70-111).  One warp per 32 surfels; each surfel's tile
-// rect is re-derived from the record's AABB centre and its integer radius exactly as getRect
-// (auxiliary.h:67-77) does, then the warp cooperatively emits the instances of its 32 surfels so
-// the 12-byte pair stores of one surfel are issued by adjacent lanes.
+// 3. scatter (the reference's duplicateWithKeys, rasterizer_impl.cu:70-111): one thread per
+//    surfel; rects of more than 16 tiles are spread over the warp.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-duplicate_kernel(int P, const float4* __restrict__ records, const uint32_t* __restrict__ offsets,
-                 const int* __restrict__ radii, uint64_t* __restrict__ keys,
-                 uint32_t* __restrict__ values, int grid_x, int grid_y) {
+scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ radii,
+               uint32_t* __restrict__ tile_cursor, uint2* __restrict__ pairs, int grid_x) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
   int r = 0;
   if (idx < P) r = __ldg(radii + idx);
-  uint32_t off = 0, depth_bits = 0;
+  uint32_t depth_bits = 0;
   int minx = 0, miny = 0, w = 0, n = 0;
   if (r > 0) {
-    off = (idx == 0) ? 0u : __ldg(offsets + idx - 1);
-    const float4* rec = records + (size_t)idx * REC_F4;
-    const float cx = __ldg(&rec[0].w), cy = __ldg(&rec[1].w);
-    depth_bits = __float_as_uint(__ldg(&rec[3].w));
-    const float rf = (float)r;
-    minx = min(grid_x, max(0, (int)__fmul_rn(__fsub_rn(cx, rf), 0.0625f)));
-    miny = min(grid_y, max(0, (int)__fmul_rn(__fsub_rn(cy, rf), 0.0625f)));
-    const int maxx = min(grid_x, max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(cx, rf), 16.0f), -1.0f), 0.0625f)));
-    const int maxy = min(grid_y, max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(cy, rf), 16.0f), -1.0f), 0.0625f)));
-    w = maxx - minx;
-    n = w * (maxy - miny);
+    // tile rect (getRect, auxiliary.h:67-77) and depth bits as left by the forward preprocess
+    const uint4 q = __ldg(rects + idx);
+    minx = (int)(q.x & 0xffffu); miny = (int)(q.x >> 16);
+    w = (int)(q.y & 0xffffu) - minx;
+    n = w * ((int)(q.y >> 16) - miny);
+    depth_bits = q.z;
   }
-  // small rects (the common case, <= 4 tiles) are written by the owning lane; large ones are
-  // spread over the warp.
   const int BIG = 16;
   if (n > 0 && n <= BIG) {
     for (int t = 0; t < n; t++) {
-      const int y = miny + t / w, x = minx + t % w;
-      keys[off + t] = ((uint64_t)(uint32_t)(y * grid_x + x) << 32) | depth_bits;
-      values[off + t] = (uint32_t)idx;
+      const uint32_t tile = (uint32_t)((miny + t / w) * grid_x + minx + t % w);
+      const uint32_t slot = atomicAdd(tile_cursor + tile * TILE_SUBS + ((uint32_t)idx & (TILE_SUBS - 1)), 1u);
+      pairs[slot] = make_uint2(depth_bits, (uint32_t)idx);
     }
   }
   unsigned big = __ballot_sync(0xffffffffu, n > BIG);
@@ -178,74 +125,228 @@ duplicate_kernel(int P, const float4* __restrict__ records, const uint32_t* __re
     const int bw = __shfl_sync(0xffffffffu, w, src);
     const int bminx = __shfl_sync(0xffffffffu, minx, src);
     const int bminy = __shfl_sync(0xffffffffu, miny, src);
-    const uint32_t boff = __shfl_sync(0xffffffffu, off, src);
     const uint32_t bdepth = __shfl_sync(0xffffffffu, depth_bits, src);
     const uint32_t bidx = (uint32_t)(idx - lane + src);
     for (int t = lane; t < bn; t += 32) {
-      const int y = bminy + t / bw, x = bminx + t % bw;
-      keys[boff + t] = ((uint64_t)(uint32_t)(y * grid_x + x) << 32) | bdepth;
-      values[boff + t] = bidx;
+      const uint32_t tile = (uint32_t)((bminy + t / bw) * grid_x + bminx + t % bw);
+      const uint32_t slot = atomicAdd(tile_cursor + tile * TILE_SUBS + (bidx & (TILE_SUBS - 1)), 1u);
+      pairs[slot] = make_uint2(bdepth, bidx);
     }
   }
 }
 
-void launch_duplicate_with_keys(int P, const float4* records, const uint32_t* offsets,
-                                const int* radii, uint64_t* keys, uint32_t* values, int grid_x,
-                                int grid_y, cudaStream_t stream) {
+void launch_scatter(int P, const uint4* rects, const int* radii, uint32_t* tile_cursor, uint2* pairs,
+                    int grid_x, cudaStream_t stream) {
   if (P <= 0) return;
-  duplicate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, records, offsets, radii, keys, values,
-                                                         grid_x, grid_y);
+  scatter_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, rects, radii, tile_cursor, pairs, grid_x);
 }
 
 // ---------------------------------------------------------------------------------------------
-// tile ranges (rasterizer_impl.cu:116-138): ranges[t] = [first, last+1) of tile t in the sorted
-// list; untouched tiles stay (0,0) (the memset of rasterizer_impl.cu:311 is issued by the launcher
-// on the same stream first).  Fused with it, because it streams the same sorted list: the per-
-// instance STRIP MASK -- bit s set iff the surfel's conservative contribution box (common.cuh,
-// CULL_RHO) meets rows [2s, 2s+1] of this tile -- which lets each compositing warp skip the
-// entries that cannot reach any of its 32 pixels without looking at the surfel.
+// 4. per-tile sort by depth bits: block-wide LSD radix sort (8-bit digits) of (depth, surfel)
+//    pairs.  Segments of up to TS_CAP_SMALL / TS_CAP_LARGE pairs are sorted in shared memory
+//    (two launches with different dynamic shared memory sizes so small tiles keep 3 CTAs per SM);
+//    longer ones ping-pong between their own slices of the pair buffer and of keys_sorted in
+//    global memory (same code, generic pointers).  Each launch covers all tiles; a CTA whose
+//    segment length is outside the launch's class returns at once.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-tile_ranges_kernel(size_t R, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
-                   const short4* __restrict__ bbox, uint2* __restrict__ ranges,
-                   uint8_t* __restrict__ strip_mask, int grid_x, int no_cull) {
-  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= R) return;
-  const uint32_t cur = (uint32_t)(__ldg(keys + idx) >> 32);
-  if (idx == 0) {
-    ranges[cur].x = 0;
-  } else {
-    const uint32_t prev = (uint32_t)(__ldg(keys + idx - 1) >> 32);
-    if (cur != prev) {
-      ranges[prev].y = (uint32_t)idx;
-      ranges[cur].x = (uint32_t)idx;
+constexpr uint32_t TS_CAP_SMALL = 4096;    // pairs per shared-memory buffer of the small class (2 x 32 KB + 32 KB histograms: 2 CTAs/SM)
+constexpr uint32_t TS_CAP_LARGE = 9216;    // large class (2 x 72 KB), 1024 threads
+constexpr int TS_SMALL_THREADS = 512, TS_SMALL_BITS = 9;   // <= 9-bit digits: 26 differing bits -> 3 passes
+constexpr int TS_LARGE_THREADS = 1024, TS_LARGE_BITS = 8;
+
+struct TileSortParams {
+  const uint2* ranges;
+  uint2* pairs;            // in: unsorted (depth bits, surfel) per tile segment; scratch afterwards
+  uint64_t* keys_sorted;   // out (and scratch of the global-memory class)
+  uint32_t* point_list;    // out
+  uint8_t* strip_mask;     // out
+  const short4* bbox;
+  int grid_x;
+  int no_cull;
+  uint32_t n_lo, n_hi;     // this launch handles segments with n_lo < n <= n_hi
+  uint32_t cap;            // pairs per shared-memory buffer (0: global-memory class)
+};
+
+// One stable LSD pass over `bits` bits at `shift`: A -> B.  Warp w owns the contiguous range
+// [w*chunk, (w+1)*chunk) of A; whist[w][d] first counts, then (after the scan over (digit, warp))
+// holds the next output slot of digit d for warp w.
+// lanes holding the same digit as this lane (match.any semantics, restricted to `valid` lanes), built
+// from `bits` ballots: fixed latency, whereas MATCH.ANY iterates over the distinct values in the warp
+// (typically 32 distinct digits here) and dominated the pass.
+__device__ __forceinline__ unsigned digit_peers(uint32_t d, bool valid, int bits) {
+  unsigned peers = __ballot_sync(0xffffffffu, valid);
+  for (int k = 0; k < bits; k++) {
+    const bool bit = (d >> k) & 1u;
+    const unsigned bal = __ballot_sync(0xffffffffu, valid && bit);
+    peers &= bit ? bal : ~bal;
+  }
+  return peers;
+}
+
+template <int THREADS, int MAXBITS>
+__device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* __restrict__ B, uint32_t n,
+                                           int shift, int bits, uint32_t (*whist)[1 << MAXBITS],
+                                           uint32_t* warp_tot, int t, int lane, int warp) {
+  constexpr int WARPS = THREADS / 32, MAXRADIX = 1 << MAXBITS;
+  const uint32_t radix = 1u << bits, dmask = radix - 1u;
+  const uint32_t chunk = ((n + THREADS - 1) / THREADS) * 32;
+  const uint32_t wbeg = min(warp * chunk, n), wend = min(wbeg + chunk, n);
+  for (int i = t; i < WARPS * MAXRADIX; i += THREADS) (&whist[0][0])[i] = 0u;
+  __syncthreads();
+  // sweep 1: per-warp digit histograms; lanes with equal digits are aggregated so that one lane per
+  // distinct digit touches shared memory (no shared-memory atomics: 2 cycles per lane)
+  for (uint32_t it = wbeg; it < wend; it += 32) {
+    const uint32_t i = it + lane;
+    const bool valid = i < wend;
+    const uint32_t d = valid ? ((A[i].x >> shift) & dmask) : 0u;
+    const unsigned peers = digit_peers(d, valid, bits);
+    if (valid && lane == __ffs(peers) - 1) whist[warp][d] += __popc(peers);
+    __syncwarp();
+  }
+  __syncthreads();
+  // exclusive scan over (digit, warp): each thread owns DPT consecutive digits
+  {
+    constexpr int DPT = (MAXRADIX + THREADS - 1) / THREADS;
+    uint32_t tot[DPT];
+    uint32_t mine = 0;
+#pragma unroll
+    for (int k = 0; k < DPT; k++) {
+      const uint32_t d = t * DPT + k;
+      uint32_t run = 0;
+      if (d < radix) {
+        for (int w = 0; w < WARPS; w++) { const uint32_t c = whist[w][d]; whist[w][d] = run; run += c; }
+      }
+      tot[k] = run;
+      mine += run;
+    }
+    uint32_t inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += v;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t base = inc - mine;
+    for (int w = 0; w < warp; w++) base += warp_tot[w];
+#pragma unroll
+    for (int k = 0; k < DPT; k++) {
+      const uint32_t d = t * DPT + k;
+      if (d < radix) {
+        for (int w = 0; w < WARPS; w++) whist[w][d] += base;
+      }
+      base += tot[k];
     }
   }
-  if (idx == R - 1) ranges[cur].y = (uint32_t)R;
+  __syncthreads();
+  // sweep 2: stable scatter
+  for (uint32_t it = wbeg; it < wend; it += 32) {
+    const uint32_t i = it + lane;
+    const bool valid = i < wend;
+    uint2 e = make_uint2(0u, 0u);
+    if (valid) e = A[i];
+    const uint32_t d = valid ? ((e.x >> shift) & dmask) : 0u;
+    const unsigned peers = digit_peers(d, valid, bits);
+    const int leader = valid ? __ffs(peers) - 1 : lane;
+    const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+    uint32_t old = 0;
+    if (valid && lane == leader) { old = whist[warp][d]; whist[warp][d] = old + __popc(peers); }
+    old = __shfl_sync(0xffffffffu, old, leader);
+    if (valid) B[old + rank] = e;
+    __syncwarp();
+  }
+  __syncthreads();
+}
 
-  uint32_t mask = 0xffu;
-  if (!no_cull) {
-    const short4 bx = __ldg(bbox + __ldg(point_list + idx));
-    const int tx = (int)(cur % (uint32_t)grid_x) * TILE_X, ty = (int)(cur / (uint32_t)grid_x) * TILE_Y;
-    mask = 0;
-    if (bx.x <= tx + TILE_X - 1 && bx.z >= tx) {
-      const int r0 = max((int)bx.y - ty, 0), r1 = min((int)bx.w - ty, TILE_Y - 1);
-      if (r0 <= r1) {
-        const int s0 = r0 / STRIP_ROWS, s1 = r1 / STRIP_ROWS;
-        mask = ((2u << s1) - 1u) & ~((1u << s0) - 1u);
+template <int THREADS, int MAXBITS>
+__global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams p) {
+  constexpr int WARPS = THREADS / 32;
+  extern __shared__ __align__(16) uint2 ts_dyn[];
+  __shared__ uint32_t whist[WARPS][1 << MAXBITS];
+  __shared__ uint32_t warp_tot[WARPS];
+  const uint32_t tile = blockIdx.x;
+  const uint2 range = __ldg(p.ranges + tile);
+  const uint32_t n = range.y - range.x;
+  if (n <= p.n_lo || n > p.n_hi) return;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const bool in_smem = p.cap != 0;
+  uint2* A = in_smem ? ts_dyn : p.pairs + range.x;
+  uint2* B = in_smem ? ts_dyn + p.cap : reinterpret_cast<uint2*>(p.keys_sorted + range.x);
+  if (in_smem) {
+    const uint2* src = p.pairs + range.x;
+    for (uint32_t i = t; i < n; i += THREADS) A[i] = __ldg(src + i);
+  }
+  __syncthreads();
+  // which depth bits differ inside this segment?  (view depths of one tile share sign and most exponent bits)
+  const uint32_t k0 = A[0].x;
+  uint32_t diff = 0;
+  for (uint32_t i = t; i < n; i += THREADS) diff |= A[i].x ^ k0;
+  diff = __reduce_or_sync(0xffffffffu, diff);
+  if (lane == 0) warp_tot[warp] = diff;
+  __syncthreads();
+  diff = 0;
+  for (int w = 0; w < WARPS; w++) diff |= warp_tot[w];
+  __syncthreads();
+  const int nbits = diff ? 32 - __clz(diff) : 0;
+  const int passes = (nbits + MAXBITS - 1) / MAXBITS;
+  const int bits = passes ? (nbits + passes - 1) / passes : 0;  // equal digit widths, <= MAXBITS
+  for (int shift = 0; shift < nbits; shift += bits) {
+    radix_pass<THREADS, MAXBITS>(A, B, n, shift, bits, whist, warp_tot, t, lane, warp);
+    uint2* tmp = A; A = B; B = tmp;
+  }
+  // equal depth bits: ascending surfel index (the reference's stable sort keeps emission order)
+  for (uint32_t i = t; i + 1 < n; i += THREADS) {
+    const uint32_t k = A[i].x;
+    if (A[i + 1].x == k && (i == 0 || A[i - 1].x != k)) {
+      uint32_t j = i + 1;
+      while (j + 1 < n && A[j + 1].x == k) j++;
+      for (uint32_t a = i + 1; a <= j; a++) {  // insertion sort of the run's surfel indices
+        const uint32_t v = A[a].y;
+        uint32_t b = a;
+        while (b > i && A[b - 1].y > v) { A[b].y = A[b - 1].y; b--; }
+        A[b].y = v;
       }
     }
   }
-  strip_mask[idx] = (uint8_t)mask;
+  __syncthreads();
+  const int tx = (int)(tile % (uint32_t)p.grid_x) * TILE_X, ty = (int)(tile / (uint32_t)p.grid_x) * TILE_Y;
+  for (uint32_t i = t; i < n; i += THREADS) {
+    const uint2 e = A[i];  // (in the global class A may alias keys_sorted[range.x + i]: read before write, same thread)
+    p.point_list[range.x + i] = e.y;
+    p.keys_sorted[range.x + i] = ((uint64_t)tile << 32) | e.x;
+    uint32_t mask = 0xffu;
+    if (!p.no_cull) {
+      const short4 bx = __ldg(p.bbox + e.y);
+      mask = 0;
+      if (bx.x <= tx + TILE_X - 1 && bx.z >= tx) {
+        const int r0 = max((int)bx.y - ty, 0), r1 = min((int)bx.w - ty, TILE_Y - 1);
+        if (r0 <= r1) mask = ((2u << (r1 / STRIP_ROWS)) - 1u) & ~((1u << (r0 / STRIP_ROWS)) - 1u);
+      }
+    }
+    p.strip_mask[range.x + i] = (uint8_t)mask;
+  }
 }
 
-void launch_tile_ranges(size_t R, const uint64_t* keys_sorted, const uint32_t* point_list,
-                        const short4* bbox, uint2* ranges, uint8_t* strip_mask, int grid_x,
-                        int num_tiles, int no_cull, cudaStream_t stream) {
-  cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream);
-  if (R == 0) return;
-  tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, stream>>>(R, keys_sorted, point_list, bbox, ranges,
-                                                                       strip_mask, grid_x, no_cull);
+void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, uint32_t* point_list,
+                      uint8_t* strip_mask, const short4* bbox, int grid_x, int num_tiles, int no_cull,
+                      cudaStream_t stream) {
+  auto small = tile_sort_kernel<TS_SMALL_THREADS, TS_SMALL_BITS>;
+  auto large = tile_sort_kernel<TS_LARGE_THREADS, TS_LARGE_BITS>;
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * TS_CAP_SMALL * sizeof(uint2)));
+    cudaFuncSetAttribute(large, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * TS_CAP_LARGE * sizeof(uint2)));
+    configured = true;
+  }
+  TileSortParams p{};
+  p.ranges = ranges; p.pairs = pairs; p.keys_sorted = keys_sorted; p.point_list = point_list;
+  p.strip_mask = strip_mask; p.bbox = bbox; p.grid_x = grid_x; p.no_cull = no_cull;
+  p.n_lo = 0; p.n_hi = TS_CAP_SMALL; p.cap = TS_CAP_SMALL;
+  small<<<num_tiles, TS_SMALL_THREADS, 2 * TS_CAP_SMALL * sizeof(uint2), stream>>>(p);
+  p.n_lo = TS_CAP_SMALL; p.n_hi = TS_CAP_LARGE; p.cap = TS_CAP_LARGE;
+  large<<<num_tiles, TS_LARGE_THREADS, 2 * TS_CAP_LARGE * sizeof(uint2), stream>>>(p);
+  p.n_lo = TS_CAP_LARGE; p.n_hi = 0xffffffffu; p.cap = 0;
+  large<<<num_tiles, TS_LARGE_THREADS, 0, stream>>>(p);
 }
 
 }  // namespace gsm

@@ -15,6 +15,8 @@ constexpr int TILE_PIX = TILE_X * TILE_Y;
 // A tile is composited by 8 independent warps, each owning a 16x2 pixel strip.
 constexpr int STRIP_ROWS = 2;
 constexpr int STRIPS_PER_TILE = TILE_Y / STRIP_ROWS;
+// Sub-cursors per tile for counting / appending instances (binning.cu), power of two.
+constexpr int TILE_SUBS = 8;
 
 // Compile-time constants of the reference (auxiliary.h:37-40).
 constexpr float NEAR_N = 0.2f;
@@ -60,10 +62,7 @@ __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a -
 struct GeometryLayout {
   size_t records;        // float4[P*5]
   size_t bbox;           // short4[P]  conservative integer pixel box of possible contribution
-  size_t tiles_touched;  // u32[P]
-  size_t offsets;        // u32[P]   inclusive scan of tiles_touched
-  size_t scan_temp;      // bytes for the scan
-  size_t scan_temp_bytes;
+  size_t rects;          // uint4[P]   (minx | miny<<16, maxx | maxy<<16, depth bits, 0): tile rect for the scatter
   size_t flags;          // u32[4]: [0] prefiltered-violation flag
   size_t total;
 };
@@ -73,19 +72,19 @@ struct ImageLayout {
   size_t final_T;    // f32[3*N]  (T, M1, M2)
   size_t n_contrib;  // u32[2*N]  (last contributor, median contributor)
   size_t ranges;     // uint2[Nt]
+  size_t tile_count;   // u32[Nt][TILE_SUBS]  instances per tile and sub-cursor (counted by the forward preprocess)
+  size_t tile_cursor;  // u32[Nt][TILE_SUBS]  append cursors of the scatter
+  size_t num_rendered; // u64      R
   size_t total;
 };
 ImageLayout image_layout(int width, int height);
 
 struct BinningLayout {
-  size_t point_list;       // u32[cap]   sorted values     (kept for backward)
+  size_t point_list;       // u32[cap]   depth-sorted surfel ids per tile   (kept for backward)
   size_t strip_mask;       // u8[cap]    per instance: which 16x2 strips of its tile it can touch (kept)
   size_t persistent;       // bytes from the start that must survive until backward
-  size_t keys_sorted;      // u64[cap]
-  size_t keys_unsorted;    // u64[cap]
-  size_t values_unsorted;  // u32[cap]
-  size_t sort_temp;
-  size_t sort_temp_bytes;
+  size_t keys_sorted;      // u64[cap]   (tile << 32 | depth bits), the reference's sorted keys
+  size_t pairs;            // uint2[cap] (depth bits, surfel) per tile segment, unsorted
   size_t total;
 };
 BinningLayout binning_layout(size_t capacity, int width, int height);
@@ -141,26 +140,21 @@ struct FwdPreprocessParams {
   int* radii;
   float4* records;
   short4* bbox;
-  uint32_t* tiles_touched;
+  uint4* rects;
+  uint32_t* tile_count;  // u32[Nt], zeroed by the caller: += 1 per (surfel, tile) instance
   uint32_t* flags;
 };
 void launch_preprocess_fwd(const FwdPreprocessParams& p, cudaStream_t stream);
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present,
                          cudaStream_t stream);
 
-size_t scan_temp_bytes(int P);
-cudaError_t launch_inclusive_scan(const uint32_t* in, uint32_t* out, int P, void* temp,
-                                  size_t temp_bytes, cudaStream_t stream);
-void launch_duplicate_with_keys(int P, const float4* records, const uint32_t* offsets,
-                                const int* radii, uint64_t* keys, uint32_t* values, int grid_x,
-                                int grid_y, cudaStream_t stream);
-size_t sort_temp_bytes(size_t n);
-cudaError_t launch_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in,
-                              uint32_t* vals_out, size_t n, int end_bit, void* temp,
-                              size_t temp_bytes, cudaStream_t stream);
-void launch_tile_ranges(size_t R, const uint64_t* keys_sorted, const uint32_t* point_list,
-                        const short4* bbox, uint2* ranges, uint8_t* strip_mask, int grid_x,
-                        int num_tiles, int no_cull, cudaStream_t stream);
+void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* ranges, int num_tiles,
+                      unsigned long long* total_out, cudaStream_t stream);
+void launch_scatter(int P, const uint4* rects, const int* radii, uint32_t* tile_cursor, uint2* pairs,
+                    int grid_x, cudaStream_t stream);
+void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, uint32_t* point_list,
+                      uint8_t* strip_mask, const short4* bbox, int grid_x, int num_tiles, int no_cull,
+                      cudaStream_t stream);
 
 struct FwdRenderParams {
   int W, H, grid_x, grid_y;

@@ -142,6 +142,7 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
   uint32_t tiles_out = 0;
   float Tu0 = 0, Tu1 = 0, Tu2 = 0, Tv0 = 0, Tv1 = 0, Tv2 = 0, Tw0 = 0, Tw1 = 0, Tw2 = 0;
   float nx = 0, ny = 0, nz = 0, cx = 0, cy = 0, opac = 0;
+  uint32_t rect_min = 0, rect_max = 0;
   short4 box = make_short4(-32768, -32768, 32767, 32767);
 
   // camera matrices are 16 floats each: uniform, served by the constant/L1 path
@@ -222,6 +223,12 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
     const int maxy = min(p.grid_y, max(0, (int)MUL(ADD(ADD(ADD(cy, rf), 16.0f), -1.0f), 0.0625f)));
     const uint32_t area = (uint32_t)((maxx - minx) * (maxy - miny));
     if (area == 0) break;
+    rect_min = (uint32_t)minx | ((uint32_t)miny << 16);
+    rect_max = (uint32_t)maxx | ((uint32_t)maxy << 16);
+    // per-tile instance counts (binning.cu step 1): one red.global.add per (surfel, tile) instance
+    for (int ty = miny; ty < maxy; ty++)
+      for (int tx = minx; tx < maxx; tx++)
+        atomicAdd(p.tile_count + (ty * p.grid_x + tx) * TILE_SUBS + (idx & (TILE_SUBS - 1)), 1u);
 
     // conservative contribution box (common.cuh, CULL_RHO); fp64 so that the cancellation in
     // centre^2 - <f,T^2> cannot shrink it
@@ -287,6 +294,7 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
   if (!valid) return;
   if (visible) {
     p.bbox[idx] = box;
+    p.rects[idx] = make_uint4(rect_min, rect_max, __float_as_uint(vz), 0u);
     float4* rec = p.records + (size_t)idx * REC_F4;
     rec[0] = make_float4(Tu0, Tu1, Tu2, cx);
     rec[1] = make_float4(Tv0, Tv1, Tv2, cy);
@@ -295,7 +303,6 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
     rec[4] = make_float4(rgb.x, rgb.y, rgb.z, __int_as_float(clamp_bits));
   }
   p.radii[idx] = radius_out;
-  p.tiles_touched[idx] = tiles_out;
 }
 
 void launch_preprocess_fwd(const FwdPreprocessParams& p, cudaStream_t stream) {

@@ -25,7 +25,10 @@ namespace gsm {
 // own -- scans the strip masks downwards from its deepest contributor, queues the entries that can
 // reach the strip, gathers their records into a private double-buffered stage, and reduces its 32
 // pixels' partial gradients with shuffles before one red.global.add per value.  No __syncthreads.
-constexpr int BWD_WARPS = 4;
+#ifndef GSM_BWD_WARPS
+#define GSM_BWD_WARPS 4
+#endif
+constexpr int BWD_WARPS = GSM_BWD_WARPS;
 constexpr int BWD_CHUNK = 32;
 constexpr int BWD_QUEUE = 128;
 
@@ -84,7 +87,10 @@ __device__ __forceinline__ void warp_reduce_scatter18(float (&v)[16], float& e0,
   e0 += __shfl_xor_sync(FULL, e0, 1);
 }
 
-__global__ void __launch_bounds__(BWD_WARPS * 32, 4) render_bwd_kernel(const BwdRenderParams p) {
+#ifndef GSM_BWD_MIN_CTAS
+#define GSM_BWD_MIN_CTAS 5
+#endif
+__global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_kernel(const BwdRenderParams p) {
   __shared__ __align__(16) BwdWarpSmem smem_all[BWD_WARPS];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   BwdWarpSmem& sm = smem_all[warp];

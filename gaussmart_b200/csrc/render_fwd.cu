@@ -28,7 +28,10 @@ namespace gsm {
 // no __syncthreads anywhere: a warp with a short (heavily culled or early-terminated) list retires
 // at once and the hardware block scheduler backfills, instead of waiting at a per-batch barrier
 // for the slowest strip of the tile.
-constexpr int FWD_WARPS = 4;
+#ifndef GSM_FWD_WARPS
+#define GSM_FWD_WARPS 4
+#endif
+constexpr int FWD_WARPS = GSM_FWD_WARPS;
 constexpr int FWD_CHUNK = 32;   // entries blended per stage
 constexpr int FWD_QUEUE = 128;  // position queue (power of two, >= FWD_CHUNK + 32)
 

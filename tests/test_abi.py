@@ -70,7 +70,8 @@ def test_image_and_binning_sizes():
     assert lib.gsm_image_ncontrib_offset(W, H) >= 12 * N
     assert lib.gsm_image_ranges_offset(W, H) >= 20 * N
     R = 10_000_000
-    assert lib.gsm_binning_bytes(R, W, H) >= 24 * R
+    assert lib.gsm_binning_bytes(R, W, H) >= 21 * R
+    assert 5 * R <= lib.gsm_binning_persistent_bytes(R) < lib.gsm_binning_bytes(R, W, H)
     assert lib.gsm_binning_sorted_keys_offset(R) >= 4 * R
     assert lib.gsm_binning_bytes(0, W, H) < (1 << 20)
 
@@ -90,4 +91,4 @@ def test_invalid_arguments_are_reported_without_touching_the_gpu():
 def test_stage_names():
     lib = _lib.load()
     names = [lib.gsm_stage_name(i).decode() for i in range(lib.gsm_stage_count())]
-    assert names[0] == "preprocess_fwd" and "render_bwd" in names and "sort" in names
+    assert names[0] == "preprocess_fwd" and "render_bwd" in names and "tile_sort" in names

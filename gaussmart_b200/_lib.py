@@ -25,6 +25,7 @@ EXPORTS = [
     "gsm_forward", "gsm_grad_workspace_bytes", "gsm_backward", "gsm_mark_visible",
     "gsm_knn_workspace_bytes", "gsm_knn_dist2",
     "gsm_stage_count", "gsm_stage_name", "gsm_stage_timing_enable", "gsm_stage_timing_read",
+    "gsm_sort_pairs32_temp_bytes", "gsm_sort_pairs32",
 ]
 
 
@@ -108,6 +109,11 @@ def load():
     lib.gsm_stage_timing_enable.argtypes = [c_int]
     lib.gsm_stage_timing_read.restype = c_int
     lib.gsm_stage_timing_read.argtypes = [POINTER(ctypes.c_double), POINTER(ctypes.c_longlong), c_int]
+    lib.gsm_sort_pairs32_temp_bytes.restype = c_size_t
+    lib.gsm_sort_pairs32_temp_bytes.argtypes = [c_size_t]
+    lib.gsm_sort_pairs32.restype = c_int
+    lib.gsm_sort_pairs32.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_void_p, c_size_t,
+                                     c_void_p]
     if lib.gsm_abi_version() != ABI_VERSION:
         raise ImportError(f"gaussmart_b200: ABI version mismatch ({lib.gsm_abi_version()} != {ABI_VERSION})")
     _lib = lib

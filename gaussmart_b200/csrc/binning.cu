@@ -318,10 +318,9 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
     if (!p.no_cull) {
       const short4 bx = __ldg(p.bbox + e.y);
       mask = 0;
-      if (bx.x <= tx + TILE_X - 1 && bx.z >= tx) {
-        const int r0 = max((int)bx.y - ty, 0), r1 = min((int)bx.w - ty, TILE_Y - 1);
-        if (r0 <= r1) mask = ((2u << (r1 / STRIP_ROWS)) - 1u) & ~((1u << (r0 / STRIP_ROWS)) - 1u);
-      }
+      const int c0 = max((int)bx.x - tx, 0), c1 = min((int)bx.z - tx, TILE_X - 1);
+      const int r0 = max((int)bx.y - ty, 0), r1 = min((int)bx.w - ty, TILE_Y - 1);
+      if (c0 <= c1 && r0 <= r1) mask = block_mask(c0, c1, r0, r1);
     }
     p.strip_mask[range.x + i] = (uint8_t)mask;
   }

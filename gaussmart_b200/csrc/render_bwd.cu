@@ -99,8 +99,8 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
   const uint32_t tile = strip_global / STRIPS_PER_TILE, strip = strip_global % STRIPS_PER_TILE;
   if (tile >= (uint32_t)(p.grid_x * p.grid_y)) return;
   const uint32_t tile_x = tile % (uint32_t)p.grid_x, tile_y = tile / (uint32_t)p.grid_x;
-  const uint32_t pixx = tile_x * TILE_X + (lane & 15);
-  const uint32_t pixy = tile_y * TILE_Y + strip * STRIP_ROWS + (lane >> 4);
+  const uint32_t pixx = tile_x * TILE_X + (uint32_t)block_px((int)strip, lane);
+  const uint32_t pixy = tile_y * TILE_Y + (uint32_t)block_py((int)strip, lane);
   const bool inside = pixx < (uint32_t)p.W && pixy < (uint32_t)p.H;
   const float pxf = (float)pixx, pyf = (float)pixy;
   const size_t N = (size_t)p.W * p.H;

@@ -169,6 +169,15 @@ size_t gsm_knn_workspace_bytes(int P);
 int gsm_knn_dist2(int P, const float* points /*[P,3]*/, float* mean_dist2 /*[P]*/,
                   void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- 32-bit key/value radix sort (stable, ascending on key bits [0, end_bit)): the hand-written
+ *      replacement of the cub::DeviceRadixSort::SortPairs call of the Morton ordering
+ *      (simple_knn.cu:213-214).  Exposed so that parity tests can hold it to a stable reference
+ *      sort directly; gsm_knn_dist2 uses it internally.  in/out buffers must not overlap. */
+size_t gsm_sort_pairs32_temp_bytes(size_t n);
+int gsm_sort_pairs32(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* values_in,
+                     uint32_t* values_out, size_t n, int end_bit, void* temp, size_t temp_bytes,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -83,6 +83,7 @@ GeometryLayout geometry_layout(int P) {
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 128); return o; };
   L.records = take(n * GSM_SURFEL_RECORD_BYTES);
   L.bbox = take(n * 8);
+  L.cull = take(n * 16);
   L.rects = take(n * 16);
   L.flags = take(16);
   L.total = off + 128;
@@ -205,7 +206,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     pp.means3D = a->means3D; pp.scales = a->scales; pp.rotations = a->rotations; pp.opacities = a->opacities;
     pp.shs = a->shs; pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;
     pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
-    pp.radii = a->radii; pp.records = records; pp.bbox = (short4*)(geom + G.bbox); pp.rects = (uint4*)(geom + G.rects); pp.tile_count = tile_count; pp.flags = flags;
+    pp.radii = a->radii; pp.records = records; pp.bbox = (short4*)(geom + G.bbox); pp.cull = (float4*)(geom + G.cull); pp.rects = (uint4*)(geom + G.rects); pp.tile_count = tile_count; pp.flags = flags;
     { StageMark m(GSM_STAGE_PREPROCESS_FWD, stream); launch_preprocess_fwd(pp, stream); }
     GSM_STAGE("forward preprocess");
     {
@@ -249,7 +250,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     {
       StageMark m(GSM_STAGE_SORT, stream);
       launch_tile_sort(ranges, pairs, (uint64_t*)(bin + B.keys_sorted), (uint32_t*)(bin + B.point_list),
-                       (uint8_t*)(bin + B.strip_mask), (const short4*)(geom + G.bbox), grid_x, num_tiles,
+                       (uint8_t*)(bin + B.strip_mask), (const short4*)(geom + G.bbox), (const float4*)(geom + G.cull), grid_x, num_tiles,
                        (a->debug & 2) ? 1 : 0, stream);
     }
     GSM_STAGE("tile sort");
@@ -261,6 +262,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     rp.point_list = bin ? (const uint32_t*)(bin + B.point_list) : nullptr;
     rp.records = records; rp.background = a->background;
     rp.strip_mask = bin ? (const uint8_t*)(bin + B.strip_mask) : nullptr;
+    rp.bbox = (const short4*)(geom + G.bbox); rp.no_cull = (a->debug & 2) ? 1 : 0;
     rp.final_T = (float*)(img + I.final_T); rp.n_contrib = (uint32_t*)(img + I.n_contrib);
     rp.out_color = a->out_color; rp.out_others = a->out_others;
     rp.stats = (unsigned long long*)a->work_counters;
@@ -302,6 +304,7 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   rp.records = (const float4*)(geom + G.records);
   const BinningLayout B = binning_layout(a->binning_capacity, W, H);
   rp.strip_mask = bin ? (const uint8_t*)(bin + B.strip_mask) : nullptr;
+  rp.bbox = (const short4*)(geom + G.bbox); rp.no_cull = (a->debug & 2) ? 1 : 0;
   rp.background = a->background;
   rp.final_T = (const float*)(img + I.final_T);
   rp.n_contrib = (const uint32_t*)(img + I.n_contrib);

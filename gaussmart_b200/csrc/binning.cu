@@ -161,6 +161,7 @@ struct TileSortParams {
   uint32_t* point_list;    // out
   uint8_t* strip_mask;     // out
   const short4* bbox;
+  const float4* cull;
   int grid_x;
   int no_cull;
   uint32_t n_lo, n_hi;     // this launch handles segments with n_lo < n <= n_hi
@@ -320,15 +321,28 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
       mask = 0;
       const int c0 = max((int)bx.x - tx, 0), c1 = min((int)bx.z - tx, TILE_X - 1);
       const int r0 = max((int)bx.y - ty, 0), r1 = min((int)bx.w - ty, TILE_Y - 1);
-      if (c0 <= c1 && r0 <= r1) mask = block_mask(c0, c1, r0, r1);
+      if (c0 <= c1 && r0 <= r1) {
+        mask = block_mask(c0, c1, r0, r1);
+        // keep only the blocks that meet the surfel's diagonal slabs (cull record: bounds of x+y and x-y over
+        // its contribution region, slack included): with the box this bounds the region by an octagon
+        const float4 dg = __ldg(p.cull + e.y);
+        uint32_t keep = 0;
+        for (uint32_t rest = mask; rest; rest &= rest - 1u) {
+          const int b = __ffs(rest) - 1;
+          const float x0 = (float)(tx + (b % BLOCKS_X) * BLOCK_W), y0 = (float)(ty + (b / BLOCKS_X) * BLOCK_H);
+          const float x1 = x0 + (float)(BLOCK_W - 1), y1 = y0 + (float)(BLOCK_H - 1);
+          if (x1 + y1 >= dg.x && x0 + y0 <= dg.y && x1 - y0 >= dg.z && x0 - y1 <= dg.w) keep |= 1u << b;
+        }
+        mask = keep;
+      }
     }
     p.strip_mask[range.x + i] = (uint8_t)mask;
   }
 }
 
 void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, uint32_t* point_list,
-                      uint8_t* strip_mask, const short4* bbox, int grid_x, int num_tiles, int no_cull,
-                      cudaStream_t stream) {
+                      uint8_t* strip_mask, const short4* bbox, const float4* cull, int grid_x, int num_tiles,
+                      int no_cull, cudaStream_t stream) {
   auto small = tile_sort_kernel<TS_SMALL_THREADS, TS_SMALL_BITS>;
   auto large = tile_sort_kernel<TS_LARGE_THREADS, TS_LARGE_BITS>;
   static bool configured = false;
@@ -339,7 +353,7 @@ void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, 
   }
   TileSortParams p{};
   p.ranges = ranges; p.pairs = pairs; p.keys_sorted = keys_sorted; p.point_list = point_list;
-  p.strip_mask = strip_mask; p.bbox = bbox; p.grid_x = grid_x; p.no_cull = no_cull;
+  p.strip_mask = strip_mask; p.bbox = bbox; p.cull = cull; p.grid_x = grid_x; p.no_cull = no_cull;
   p.n_lo = 0; p.n_hi = TS_CAP_SMALL; p.cap = TS_CAP_SMALL;
   small<<<num_tiles, TS_SMALL_THREADS, 2 * TS_CAP_SMALL * sizeof(uint2), stream>>>(p);
   p.n_lo = TS_CAP_SMALL; p.n_hi = TS_CAP_LARGE; p.cap = TS_CAP_LARGE;

@@ -68,6 +68,11 @@ constexpr int REC_F4 = 5;
 // of the camera plane get the unbounded box.  Compositing kernels use it only to SKIP work.
 constexpr float CULL_RHO = 11.5f;
 constexpr float CULL_SLACK_PX = 0.75f;
+// Diagonal slabs ("cull record", one float4 per surfel): (lo, hi) of x+y and (lo, hi) of x-y over the same
+// conservative contribution region as the box (the conic rho3d <= c^2 is an ellipse whose extent along a
+// direction n is sqrt(n^T S n); united with the low-pass disc; same stretch and slack as the box).  Box and
+// slabs bound the region by an octagon.  The tile sort drops from an instance's block mask the blocks that
+// miss a slab; like the box this only ever SKIPS work.  Unbounded slabs (+-inf) where the box is unbounded.
 
 // Gradient accumulation record (GSM_GRAD_RECORD_FLOATS = 20 floats, 80 B):
 //   [0..2] dTu  [3..5] dTv  [6..8] dTw  [9..10] dcentre  [11..13] drgb  [14..16] dnormal
@@ -81,6 +86,7 @@ __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a -
 struct GeometryLayout {
   size_t records;        // float4[P*5]
   size_t bbox;           // short4[P]  conservative integer pixel box of possible contribution
+  size_t cull;           // float4[P]  diagonal slabs of the contribution region ("cull record")
   size_t rects;          // uint4[P]   (minx | miny<<16, maxx | maxy<<16, depth bits, 0): tile rect for the scatter
   size_t flags;          // u32[4]: [0] prefiltered-violation flag
   size_t total;
@@ -159,6 +165,7 @@ struct FwdPreprocessParams {
   int* radii;
   float4* records;
   short4* bbox;
+  float4* cull;
   uint4* rects;
   uint32_t* tile_count;  // u32[Nt], zeroed by the caller: += 1 per (surfel, tile) instance
   uint32_t* flags;
@@ -172,7 +179,7 @@ void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* 
 void launch_scatter(int P, const uint4* rects, const int* radii, uint32_t* tile_cursor, uint2* pairs,
                     int grid_x, cudaStream_t stream);
 void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, uint32_t* point_list,
-                      uint8_t* strip_mask, const short4* bbox, int grid_x, int num_tiles, int no_cull,
+                      uint8_t* strip_mask, const short4* bbox, const float4* cull, int grid_x, int num_tiles, int no_cull,
                       cudaStream_t stream);
 
 struct FwdRenderParams {
@@ -181,6 +188,8 @@ struct FwdRenderParams {
   const uint32_t* point_list;
   const float4* records;
   const uint8_t* strip_mask;
+  const short4* bbox;         // per-surfel conservative contribution boxes
+  int no_cull;                // evaluate every (pixel, entry) pair (debug bit 1)
   const float* background;
   float* final_T;
   uint32_t* n_contrib;
@@ -196,6 +205,8 @@ struct BwdRenderParams {
   const uint32_t* point_list;
   const float4* records;
   const uint8_t* strip_mask;
+  const short4* bbox;
+  int no_cull;
   const float* background;
   const float* final_T;
   const uint32_t* n_contrib;

@@ -129,6 +129,10 @@ __device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict
   }
 }
 
+// upper bound of sqrt(x), x >= 0, through the fp32 unit (the fp64 square root is a long software sequence;
+// the extents it feeds only need to err upwards)
+__device__ __forceinline__ double sqrt_up(double x) { return (double)__fsqrt_ru(__double2float_ru(x)); }
+
 __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdPreprocessParams p) {
   extern __shared__ float sh_smem[];
   const int gidx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -144,6 +148,7 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
   float nx = 0, ny = 0, nz = 0, cx = 0, cy = 0, opac = 0;
   uint32_t rect_min = 0, rect_max = 0;
   short4 box = make_short4(-32768, -32768, 32767, 32767);
+  float4 diag = make_float4(-INFINITY, INFINITY, -INFINITY, INFINITY);  // unbounded diagonal slabs
 
   // camera matrices are 16 floats each: uniform, served by the constant/L1 path
   const float* __restrict__ vm = p.viewmatrix;
@@ -239,7 +244,7 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
     } else if (opac >= ALPHA_MIN) {  // (false for NaN: keep the unbounded box)
       // alpha >= 1/255  <=>  rho <= 2 ln(255 opacity); 3% + 0.2 margin on rho, capped at CULL_RHO (opacity <= 1)
       const double c2 = fmin((double)CULL_RHO * fmax(1.0, (double)opac * (double)opac),
-                             2.0 * log(255.0 * (double)opac) * 1.03 + 0.2);
+                             2.0 * (double)logf(255.0f * opac) * 1.03 + 0.2);  // logf: 1 ulp, inside the 0.2 margin
       const double w0 = Tw0, w1 = Tw1, w2 = Tw2;
       const double dd = c2 * (w0 * w0 + w1 * w1) - w2 * w2;
       if (dd < -1e-6 * w2 * w2 && w2 > 0.0) {  // the whole disc is in front of the camera plane
@@ -248,9 +253,9 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
         const double ccy = f0 * ((double)Tv0 * w0 + (double)Tv1 * w1) + f2 * (double)Tv2 * w2;
         const double ex2 = ccx * ccx - (f0 * ((double)Tu0 * Tu0 + (double)Tu1 * Tu1) + f2 * (double)Tu2 * Tu2);
         const double ey2 = ccy * ccy - (f0 * ((double)Tv0 * Tv0 + (double)Tv1 * Tv1) + f2 * (double)Tv2 * Tv2);
-        const double ex = sqrt(fmax(ex2, 0.0)) * 1.01 + (double)CULL_SLACK_PX;
-        const double ey = sqrt(fmax(ey2, 0.0)) * 1.01 + (double)CULL_SLACK_PX;
-        const double r2d = sqrt(0.5 * c2) + (double)CULL_SLACK_PX;  // low-pass disc around the reference centre
+        const double ex = sqrt_up(fmax(ex2, 0.0)) * 1.01 + (double)CULL_SLACK_PX;
+        const double ey = sqrt_up(fmax(ey2, 0.0)) * 1.01 + (double)CULL_SLACK_PX;
+        const double r2d = sqrt_up(0.5 * c2) + (double)CULL_SLACK_PX;  // low-pass disc around the reference centre
         const double x0 = fmin(ccx - ex, (double)cx - r2d), x1 = fmax(ccx + ex, (double)cx + r2d);
         const double y0 = fmin(ccy - ey, (double)cy - r2d), y1 = fmax(ccy + ey, (double)cy + r2d);
         if (x0 == x0 && x1 == x1 && y0 == y0 && y1 == y1) {  // not NaN
@@ -258,6 +263,19 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
           box.y = (short)fmax(-32768.0, fmin(32767.0, floor(y0)));
           box.z = (short)fmax(-32768.0, fmin(32767.0, ceil(x1)));
           box.w = (short)fmax(-32768.0, fmin(32767.0, ceil(y1)));
+          // diagonal slabs of the same region (common.cuh, "cull record"): the extent of the conic along
+          // (1,1) and (1,-1) is sqrt(S00 + S11 +- 2 S01) with S the conic's "covariance" (ex2, ey2 are its
+          // diagonal, sxy its off-diagonal term), stretched and slackened like the box and united with the disc
+          const double sxy = ccx * ccy - (f0 * ((double)Tu0 * Tv0 + (double)Tu1 * Tv1) + f2 * (double)Tu2 * Tv2);
+          const double s00 = fmax(ex2, 0.0), s11 = fmax(ey2, 0.0);
+          const double rt2 = 1.4142135623730951;
+          const double ep = sqrt_up(fmax(s00 + s11 + 2.0 * sxy, 0.0)) * 1.01 + rt2 * (double)CULL_SLACK_PX + 0.01;
+          const double em = sqrt_up(fmax(s00 + s11 - 2.0 * sxy, 0.0)) * 1.01 + rt2 * (double)CULL_SLACK_PX + 0.01;
+          const double dp = (double)cx + (double)cy, dm = (double)cx - (double)cy, dr = rt2 * r2d + 0.01;
+          const double plo = fmin(ccx + ccy - ep, dp - dr), phi = fmax(ccx + ccy + ep, dp + dr);
+          const double mlo = fmin(ccx - ccy - em, dm - dr), mhi = fmax(ccx - ccy + em, dm + dr);
+          if (plo == plo && phi == phi && mlo == mlo && mhi == mhi)
+            diag = make_float4(__double2float_rd(plo), __double2float_ru(phi), __double2float_rd(mlo), __double2float_ru(mhi));
         }
       }
     }
@@ -294,6 +312,7 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
   if (!valid) return;
   if (visible) {
     p.bbox[idx] = box;
+    p.cull[idx] = diag;
     p.rects[idx] = make_uint4(rect_min, rect_max, __float_as_uint(vz), 0u);
     float4* rec = p.records + (size_t)idx * REC_F4;
     rec[0] = make_float4(Tu0, Tu1, Tu2, cx);

@@ -4,13 +4,19 @@
 // replayed back to front, T is reconstructed by division (backward.cu:319) and the per-pair
 // gradients w.r.t. the homography rows Tu/Tv/Tw, the AABB centre, colour, normal and opacity are
 // produced.  Differences in HOW:
-//   * the replay starts at the tile's deepest contributor (max n_contrib over the tile, and per
-//     warp over the warp's 32 pixels) instead of the end of the list;
-//   * the 18 per-pair partial gradients are reduced across the warp with a recursive-halving
-//     shuffle network (21 shuffles) and leave the SM as ONE red.global.add per value per
-//     warp-surfel instead of one atomic per value per pixel-surfel (backward.cu:339-443);
-//   * they land in a compact 80-byte per-surfel gradient record that the backward preprocess
-//     expands, so only 80*P bytes are zero-filled per backward instead of 76 floats * P.
+//   * each warp owns one 8x4-pixel block of a tile and replays it on its own (no __syncthreads),
+//     starting at the block's deepest contributor instead of the end of the list;
+//   * the per-pixel SEQUENTIAL part of a pair (transmittance, running colour/depth/normal sums,
+//     dL/dalpha) runs in the pixel's lane as the entries go by, but the pair's GEOMETRIC part (the
+//     chain through the ray-splat intersection to Tu/Tv/Tw, ~2/3 of the arithmetic) is deferred:
+//     active pairs -- typically 4-5 of a block's 32 pixels per entry -- are pushed as 16-byte
+//     records into a small shared-memory ring, one entry per quarter-warp slot, and processed
+//     four entries at a time with every quarter-warp working on its own entry;
+//   * the 18 per-pair partial gradients are reduced inside the quarter-warp with a recursive-halving
+//     shuffle network (17 shuffles for 4 entries) and leave the SM as one red.global.add.v2.f32 per
+//     lane into a compact 80-byte per-surfel gradient record, instead of one atomic per value per
+//     pixel-surfel pair (backward.cu:339-443); the backward preprocess expands the record, so only
+//     80*P bytes are zero-filled per backward instead of 76 floats * P.
 #include "common.cuh"
 #include <cuda_pipeline.h>
 
@@ -32,59 +38,120 @@ constexpr int BWD_WARPS = GSM_BWD_WARPS;
 constexpr int BWD_CHUNK = 32;
 constexpr int BWD_QUEUE = 128;
 
+constexpr int BWD_RING = 8;  // quarter-warp slots of the deferred-pair ring (a push adds <= 4, a pass retires 4)
+
 struct BwdWarpSmem {
   float4 q[2][REC_F4][BWD_CHUNK];
   uint32_t id[2][BWD_CHUNK];
   uint32_t pos[2][BWD_CHUNK];  // 0-based list position k of the staged entry (the reference's `contributor`)
   uint32_t queue[BWD_QUEUE];
+  float4 pend[BWD_RING][8];    // deferred pairs: (G*dL_dalpha, dL_dz, alpha*T, bits: pixel | 3d-branch << 5)
+  uint32_t qinfo[BWD_RING];    // per slot: stage entry j | pairs in the slot << 8
+  float4 pixc[2][32];          // per pixel: (dL_dpixel.rgb, dL_dnormal.x), (dL_dnormal.yz, -, -)
 };
 
-// Recursive-halving reduce-scatter of 16 values over 32 lanes + 2 extra values.
-// On return lane L holds in v[0] the warp sum of slot (L>>1)&15 (both lanes of a pair hold it),
-// e0 holds the warp sum of extra slot (L>>4) (16 or 17).
-__device__ __forceinline__ void warp_reduce_scatter18(float (&v)[16], float& e0, float e1, int lane) {
+// red.global.add.v2.f32: two adjacent floats in one L2 reduction request (8-byte aligned)
+__device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
+}
+
+// Deferred geometric part of up to 4 entries at once: quarter-warp q works on ring slot head+q, lane i of
+// the quarter on the slot's i-th pair.  Recomputes the ray-splat intersection of the pair (MUFU
+// reciprocal: these values feed gradient terms only), forms the 18 partial gradients, reduces them
+// over the quarter's 8 lanes and adds them to the entry's gradient record.
+__device__ __forceinline__ void geometry_pass(BwdWarpSmem& sm, int s, int head, int nslots, int lane, int bx0, int by0,
+                                              float* __restrict__ grad_records) {
   const unsigned FULL = 0xffffffffu;
-  {
-    const bool up = lane & 16;
+  const int qtr = lane >> 3, i = lane & 7;
+  const int slot = (head + qtr) & (BWD_RING - 1);
+  const uint32_t qf = sm.qinfo[slot];
+  const int j = (int)(qf & 31u);
+  const bool slot_valid = qtr < nslots;
+  const bool valid = slot_valid && i < (int)(qf >> 8);
+  float v[16];
+  float e0 = 0.f, e1 = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; i++) {
-      const float send = up ? v[i] : v[i + 8];
-      const float keep = up ? v[i + 8] : v[i];
-      v[i] = keep + __shfl_xor_sync(FULL, send, 16);
+  for (int z = 0; z < 16; z++) v[z] = 0.f;
+  if (valid) {
+    const float4 pr = sm.pend[slot][i];
+    const uint32_t bits = __float_as_uint(pr.w);
+    const int pix = (int)(bits & 31u);
+    const float pxf = (float)(bx0 + pix % BLOCK_W), pyf = (float)(by0 + pix / BLOCK_W);
+    const float4 a = sm.q[s][0][j], b = sm.q[s][1][j], c = sm.q[s][2][j];
+    const float4 pc0 = sm.pixc[0][pix], pc1 = sm.pixc[1][pix];
+    const float dL_dz = pr.y, w = pr.z;
+    e1 = pr.x;
+    const float cw_e1 = c.w * e1;  // dL_dG * G
+    const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
+    const float lx = FMA(pyf, c.x, -b.x), ly = FMA(pyf, c.y, -b.y), lz = FMA(pyf, c.z, -b.z);
+    const float ppx = FMA(ky, lz, -MUL(kz, ly));
+    const float ppy = FMA(kz, lx, -MUL(kx, lz));
+    const float ppz = FMA(kx, ly, -MUL(ky, lx));
+    const float rpz = __fdividef(1.0f, ppz);
+    const float sx = ppx * rpz, sy = ppy * rpz;
+    v[11] = w * pc0.x; v[12] = w * pc0.y; v[13] = w * pc0.z;
+    v[14] = w * pc0.w; v[15] = w * pc1.x; e0 = w * pc1.y;
+    if (bits & 32u) {  // rho3d <= rho2d: gradient through the ray-splat intersection
+      const float dL_dsx = dL_dz * c.x - cw_e1 * sx;
+      const float dL_dsy = dL_dz * c.y - cw_e1 * sy;
+      const float dpx = dL_dsx * rpz, dpy = dL_dsy * rpz, dpz = -(dpx * sx + dpy * sy);
+      // dL_dk = l x dL_dp ; dL_dl = dL_dp x k
+      const float dkx = ly * dpz - lz * dpy, dky = lz * dpx - lx * dpz, dkz = lx * dpy - ly * dpx;
+      const float dlx = dpy * kz - dpz * ky, dly = dpz * kx - dpx * kz, dlz = dpx * ky - dpy * kx;
+      v[0] = -dkx; v[1] = -dky; v[2] = -dkz;
+      v[3] = -dlx; v[4] = -dly; v[5] = -dlz;
+      v[6] = pxf * dkx + pyf * dlx + dL_dz * sx;
+      v[7] = pxf * dky + pyf * dly + dL_dz * sy;
+      v[8] = pxf * dkz + pyf * dlz + dL_dz;
+    } else {  // low-pass branch: gradient to the AABB centre
+      const float dx = SUB(a.w, pxf), dy = SUB(b.w, pyf);
+      v[9] = cw_e1 * (-FILTER_INV_SQUARE * dx);
+      v[10] = cw_e1 * (-FILTER_INV_SQUARE * dy);
+      v[6] = sx * dL_dz;
+      v[7] = sy * dL_dz;
+      v[8] = dL_dz;
     }
-    const float send = up ? e0 : e1;
-    const float keep = up ? e1 : e0;
-    e0 = keep + __shfl_xor_sync(FULL, send, 16);
   }
-  {
-    const bool up = lane & 8;
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-      const float send = up ? v[i] : v[i + 4];
-      const float keep = up ? v[i + 4] : v[i];
-      v[i] = keep + __shfl_xor_sync(FULL, send, 8);
-    }
-    e0 += __shfl_xor_sync(FULL, e0, 8);
-  }
+  // recursive halving over the quarter's 8 lanes: lane i ends with the sums of slots 2i and 2i+1
   {
     const bool up = lane & 4;
 #pragma unroll
-    for (int i = 0; i < 2; i++) {
-      const float send = up ? v[i] : v[i + 2];
-      const float keep = up ? v[i + 2] : v[i];
-      v[i] = keep + __shfl_xor_sync(FULL, send, 4);
+    for (int z = 0; z < 8; z++) {
+      const float send = up ? v[z] : v[z + 8];
+      const float keep = up ? v[z + 8] : v[z];
+      v[z] = keep + __shfl_xor_sync(FULL, send, 4);
     }
-    e0 += __shfl_xor_sync(FULL, e0, 4);
+    const float send = up ? e0 : e1;
+    const float keep = up ? e1 : e0;
+    e0 = keep + __shfl_xor_sync(FULL, send, 4);  // lanes 0-3 of the quarter: slot 16, lanes 4-7: slot 17
   }
   {
     const bool up = lane & 2;
-    const float send = up ? v[0] : v[1];
-    const float keep = up ? v[1] : v[0];
-    v[0] = keep + __shfl_xor_sync(FULL, send, 2);
+#pragma unroll
+    for (int z = 0; z < 4; z++) {
+      const float send = up ? v[z] : v[z + 4];
+      const float keep = up ? v[z + 4] : v[z];
+      v[z] = keep + __shfl_xor_sync(FULL, send, 2);
+    }
     e0 += __shfl_xor_sync(FULL, e0, 2);
   }
-  v[0] += __shfl_xor_sync(FULL, v[0], 1);
-  e0 += __shfl_xor_sync(FULL, e0, 1);
+  {
+    const bool up = lane & 1;
+#pragma unroll
+    for (int z = 0; z < 2; z++) {
+      const float send = up ? v[z] : v[z + 2];
+      const float keep = up ? v[z + 2] : v[z];
+      v[z] = keep + __shfl_xor_sync(FULL, send, 1);
+    }
+    e0 += __shfl_xor_sync(FULL, e0, 1);
+  }
+  if (slot_valid) {
+    float* g = grad_records + (size_t)sm.id[s][j] * GREC;
+    red_add_v2(g + 2 * i, v[0], v[1]);
+    if (i == 0) atomicAdd(g + 16, e0);
+    else if (i == 4) atomicAdd(g + 17, e0);
+  }
+  __syncwarp();  // the slots may be refilled by the next push
 }
 
 #ifndef GSM_BWD_MIN_CTAS
@@ -130,6 +197,11 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
   float bg_dot_dpixel = 0.f;
 #pragma unroll
   for (int ch = 0; ch < 3; ch++) bg_dot_dpixel += __ldg(p.background + ch) * dL_dpixel[ch];
+
+  sm.pixc[0][lane] = make_float4(dL_dpixel[0], dL_dpixel[1], dL_dpixel[2], dL_dnormal2D[0]);
+  sm.pixc[1][lane] = make_float4(dL_dnormal2D[1], dL_dnormal2D[2], 0.f, 0.f);
+  const int bx0 = (int)pixx - (lane % BLOCK_W), by0 = (int)pixy - (lane / BLOCK_W);  // block origin
+  int ring_head = 0, ring_fill = 0;  // warp-uniform
 
   // deepest contributor of the warp: entries at or beyond it are behind every pixel of the strip
   const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
@@ -203,13 +275,11 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
       const float G = expf(power);
       const float alpha = fminf(MUL(c.w, G), ALPHA_MAX);
       active = active && !(alpha < ALPHA_MIN);
-      if (!__any_sync(0xffffffffu, active)) continue;
+      const unsigned am = __ballot_sync(0xffffffffu, active);
+      if (am == 0u) continue;
 
-      float v[16];
-      float e0 = 0.f, e1 = 0.f;
-#pragma unroll
-      for (int z = 0; z < 16; z++) v[z] = 0.f;
-
+      // ---- sequential part of the pair, in the pixel's lane ----
+      float e1 = 0.f, dL_dz = 0.f, w = 0.f;
       if (active) {
         const float4 nrm = sm.q[s][3][j], col = sm.q[s][4][j];
         const float normal[3] = {nrm.x, nrm.y, nrm.z};
@@ -219,16 +289,14 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
         // and use the 2-ulp MUFU reciprocal instead of the reference's 8 div.rn per pair.
         const float one_m_alpha = SUB(1.0f, alpha);
         T = __fdiv_rn(T, one_m_alpha);
-        const float w = alpha * T;
+        w = alpha * T;
         float dL_dalpha = 0.0f;
 #pragma unroll
         for (int ch = 0; ch < 3; ch++) {
           accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
           last_color[ch] = color[ch];
           dL_dalpha += (color[ch] - accum_rec[ch]) * dL_dpixel[ch];
-          v[11 + ch] = w * dL_dpixel[ch];
         }
-        float dL_dz = 0.0f;
         const float near_over_d = __fdiv_rn(NEAR_N, c_d);  // exact: m_d enters a cancelling sum below
         const float m_d = far_ratio * (1.0f - near_over_d);
         const float dmd_dd = (FAR_N / ((FAR_N - NEAR_N) * NEAR_N)) * near_over_d * near_over_d;
@@ -236,7 +304,7 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
         const float dL_dweight = (final_D2 + m_d * m_d * final_A - 2.0f * m_d * final_D) * dL_dreg;
         dL_dalpha += dL_dweight - last_dL_dT;
         last_dL_dT = dL_dweight * alpha + (1.0f - alpha) * last_dL_dT;
-        const float dL_dmd = 2.0f * (T * alpha) * (m_d * final_A - final_D) * dL_dreg;
+        const float dL_dmd = 2.0f * w * (m_d * final_A - final_D) * dL_dreg;
         dL_dz += dL_dmd * dmd_dd;
 
         accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
@@ -244,54 +312,41 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
         dL_dalpha += (c_d - accum_depth_rec) * dL_ddepth;
         accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
         dL_dalpha += (1.0f - accum_alpha_rec) * dL_daccum;
-        float dn[3];
 #pragma unroll
         for (int ch = 0; ch < 3; ch++) {
           accum_normal_rec[ch] = last_alpha * last_normal[ch] + (1.f - last_alpha) * accum_normal_rec[ch];
           last_normal[ch] = normal[ch];
           dL_dalpha += (normal[ch] - accum_normal_rec[ch]) * dL_dnormal2D[ch];
-          dn[ch] = alpha * T * dL_dnormal2D[ch];
         }
-        v[14] = dn[0]; v[15] = dn[1]; e0 = dn[2];
-
         dL_dalpha *= T;
         last_alpha = alpha;
         dL_dalpha += (-T_final * __fdividef(1.0f, one_m_alpha)) * bg_dot_dpixel;
-
-        const float dL_dG = c.w * dL_dalpha;
-        dL_dz += alpha * T * dL_ddepth;
-
-        if (rho3d <= rho2d) {
-          const float dL_dsx = dL_dG * -G * sx + dL_dz * c.x;
-          const float dL_dsy = dL_dG * -G * sy + dL_dz * c.y;
-          const float rpz = __fdividef(1.0f, ppz);
-          const float dsx_pz = dL_dsx * rpz, dsy_pz = dL_dsy * rpz;
-          const float dpx = dsx_pz, dpy = dsy_pz, dpz = -(dsx_pz * sx + dsy_pz * sy);
-          // dL_dk = l x dL_dp ; dL_dl = dL_dp x k
-          const float dkx = ly * dpz - lz * dpy, dky = lz * dpx - lx * dpz, dkz = lx * dpy - ly * dpx;
-          const float dlx = dpy * kz - dpz * ky, dly = dpz * kx - dpx * kz, dlz = dpx * ky - dpy * kx;
-          v[0] = -dkx; v[1] = -dky; v[2] = -dkz;
-          v[3] = -dlx; v[4] = -dly; v[5] = -dlz;
-          v[6] = pxf * dkx + pyf * dlx + dL_dz * sx;
-          v[7] = pxf * dky + pyf * dly + dL_dz * sy;
-          v[8] = pxf * dkz + pyf * dlz + dL_dz;
-        } else {
-          const float dG_ddelx = -G * FILTER_INV_SQUARE * dx;
-          const float dG_ddely = -G * FILTER_INV_SQUARE * dy;
-          v[9] = dL_dG * dG_ddelx;
-          v[10] = dL_dG * dG_ddely;
-          v[6] = sx * dL_dz;
-          v[7] = sy * dL_dz;
-          v[8] = dL_dz;
-        }
-        e1 = G * dL_dalpha;
+        dL_dz += w * dL_ddepth;
+        e1 = G * dL_dalpha;  // dL_dopacity of the pair; dL_dG * G = opacity * e1
       }
 
-      warp_reduce_scatter18(v, e0, e1, lane);
-      float* g = p.grad_records + (size_t)sm.id[s][j] * GREC;
-      if ((lane & 1) == 0) atomicAdd(g + (lane >> 1), v[0]);
-      else if (lane == 1) atomicAdd(g + 16, e0);
-      else if (lane == 17) atomicAdd(g + 17, e0);
+      // ---- push the active pairs: the entry takes ceil(c/8) quarter-warp slots of the ring ----
+      {
+        const int c = __popc(am), nq = (c + 7) >> 3;
+        const int rank = __popc(am & ((1u << lane) - 1u));
+        if (active)
+          sm.pend[(ring_head + ring_fill + (rank >> 3)) & (BWD_RING - 1)][rank & 7] =
+              make_float4(e1, dL_dz, w, __uint_as_float((uint32_t)lane | (rho3d <= rho2d ? 32u : 0u)));
+        if (lane < nq)
+          sm.qinfo[(ring_head + ring_fill + lane) & (BWD_RING - 1)] = (uint32_t)j | ((uint32_t)min(8, c - 8 * lane) << 8);
+        ring_fill += nq;
+        __syncwarp();
+      }
+      while (ring_fill >= 4) {
+        geometry_pass(sm, s, ring_head, 4, lane, bx0, by0, p.grad_records);
+        ring_head = (ring_head + 4) & (BWD_RING - 1);
+        ring_fill -= 4;
+      }
+    }
+    if (ring_fill > 0) {  // the staged records are recycled after this chunk: retire what is pending
+      geometry_pass(sm, s, ring_head, ring_fill, lane, bx0, by0, p.grad_records);
+      ring_head = 0;
+      ring_fill = 0;
     }
     __syncwarp();
     n_cur = n_next;

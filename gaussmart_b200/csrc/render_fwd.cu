@@ -1,8 +1,8 @@
 // Forward per-tile compositing (K4) for sm_100a.
 //
-// Restates cuda_rasterizer/forward.cu:256-448 (renderCUDA): one CTA per 16x16 tile, one thread
-// per pixel, depth-ordered alpha compositing of colour, depth, normal, distortion moments and
-// median depth.  Differences in HOW (not in WHAT):
+// Restates cuda_rasterizer/forward.cu:256-448 (renderCUDA): depth-ordered alpha compositing of
+// colour, depth, normal, distortion moments and median depth, one thread per pixel.
+// Differences in HOW (not in WHAT):
 //   * surfel data arrive as one packed 80-byte record (5 x 128-bit loads per staged surfel
 //     instead of 16 scalar loads from 4 arrays + 3 global loads per contributing pair);
 //   * batches are double-buffered in shared memory with cp.async so the gather of batch i+1
@@ -21,7 +21,7 @@ namespace gsm {
 #define SUB(a, b) __fsub_rn((a), (b))
 #define FMA(a, b, c) __fmaf_rn((a), (b), (c))
 
-// Warp-independent design: a CTA holds FWD_WARPS warps, each of which composites one 16x2 strip of
+// Warp-independent design: a CTA holds FWD_WARPS warps, each of which composites one 8x4-pixel block of
 // a tile ENTIRELY on its own -- it scans the tile's strip masks (1 byte per list entry, streamed),
 // compacts the entries that can reach its strip into a small position queue, gathers their packed
 // records into its private double-buffered shared-memory stage with cp.async, and blends.  There is

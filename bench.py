@@ -74,7 +74,7 @@ class ClockSampler:
             f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
             self.path = f.name
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=f,
+                                          "--format=csv,noheader,nounits", "-lms", "20"], stdout=f,
                                          stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -149,23 +149,30 @@ class OursArm:
         import gaussmart_b200 as gb
         from gaussmart_b200 import view_parallel as vp
         self.gb, self.vp, self.wl, self.device, self.world = gb, vp, wl, device, world
+        self.rank = int(os.environ.get("RANK", "0"))
         M = wl["params"]["shs"].shape[1]
-        self.bucket = vp.GradBucket(wl["P"], M, device, with_stats=True)
+        self.bucket = vp.GradBucket(wl["P"], M, device, with_stats=True) if world == 1 else None
+        # N > 1: factored exchange (all-reduce 40 B/surfel + all-gather dL/dRGB 12 B/surfel/view + local SH expand)
+        self.ex = vp.FactoredExchange(wl["P"], M, device, world, 1, with_stats=True) if world > 1 else None
         self.bg = torch.zeros(3, device=device)
         self.leaves = {k: v.clone().requires_grad_(True) for k, v in wl["params"].items()}
         self.means2D = torch.zeros_like(self.leaves["means3D"], requires_grad=True)
+        self.leaves_data = {k: v.detach() for k, v in self.leaves.items()}
 
     def value_step(self, view):
         wl = self.wl
         from gaussmart_b200.rasterizer import rasterize_into_bucket
-        color, radii, allmap, backward = rasterize_into_bucket(wl["params"], wl["cams_d"][view], self.bucket, False,
-                                                               bg=self.bg)
-        d2 = backward(wl["cot_d"][0], wl["cot_d"][1])
-        if self.world > 1:
-            self.bucket.stats.zero_()
-            self.bucket.max_radii.zero_()
-            self.vp.add_densification_stats(self.bucket, d2, radii)
-            self.vp.allreduce_bucket(self.bucket)
+        if self.world == 1:
+            color, radii, allmap, backward = rasterize_into_bucket(wl["params"], wl["cams_d"][view], self.bucket, False,
+                                                                   bg=self.bg)
+            backward(wl["cot_d"][0], wl["cot_d"][1])
+            return
+        # the step's global batch: rank r renders cams[r]; every rank knows all N cameras of the step
+        base = (view - self.rank) % N_VIEWS
+        cams = [wl["cams_d"][(base + r) % N_VIEWS] for r in range(self.world)]
+        self.vp.view_parallel_step_factored(
+            wl["params"], cams, self.ex, lambda v, c, a: wl["cot_d"],
+            raster_fn=lambda p_, c_, b_, a_, rgb_out=None: rasterize_into_bucket(p_, c_, b_, a_, bg=self.bg, rgb_out=rgb_out))
 
     def api_step(self, cam_d, gt):
         """Public API: GaussianRasterizationSettings / GaussianRasterizer + autograd (gr.py:37-97 shape)."""
@@ -181,10 +188,26 @@ class OursArm:
             rotations=L["rotations"])
         loss = loss_fn(color, allmap, gt)
         loss.backward()
-        if self.world > 1:
-            flat = torch.cat([L[k].grad.reshape(-1) for k in ("means3D", "shs", "opacities", "scales", "rotations")])
-            dist.all_reduce(flat)
         return loss
+
+    def api_step_view_parallel(self, cams_step, gt):
+        """N > 1: the public multi-GPU call, view_parallel_step_factored, with the loss of train.py's shape
+        differentiated w.r.t. the rendered maps inside cotangent_fn (same work as api_step per rank)."""
+        from gaussmart_b200.rasterizer import rasterize_into_bucket
+        box = {}
+
+        def cot(v, color, allmap):
+            c = color.detach().requires_grad_(True)
+            a = allmap.detach().requires_grad_(True)
+            loss = loss_fn(c, a, gt)
+            loss.backward()
+            box["loss"] = loss.detach()
+            return c.grad, a.grad
+
+        self.vp.view_parallel_step_factored(
+            self.leaves_data, cams_step, self.ex, cot,
+            raster_fn=lambda p_, c_, b_, a_, rgb_out=None: rasterize_into_bucket(p_, c_, b_, a_, bg=self.bg, rgb_out=rgb_out))
+        return box["loss"]
 
 
 class ReferenceArm:
@@ -283,7 +306,7 @@ def work_counts(wl, view, device):
                 E_bwd=int(ncontrib))
 
 
-def stage_model(wl, wc, deg):
+def stage_model(wl, wc, deg, world=1):
     """ALGORITHMIC bytes / flops per launch of every stage (restated in DESIGN.md)."""
     P, W, H = wl["P"], wl["W"], wl["H"]
     Npx, Nt = W * H, ((W + 15) // 16) * ((H + 15) // 16)
@@ -298,6 +321,9 @@ def stage_model(wl, wc, deg):
     m["grad_zero"] = ("hbm", 80 * P)
     m["render_bwd"] = ("fp32", 210 * C + 35 * (wc["E_bwd"] - C))
     m["preprocess_bwd"] = ("hbm", (147 + 12 * K) * Pv + (44 + 12 * K) * Pv + 4 * P)
+    if world > 1:  # factored exchange: K6 writes dL/dRGB instead of the SH rows; the expand reads N of them, writes the rows
+        m["preprocess_bwd"] = ("hbm", (147 + 12 * K) * Pv + 44 * Pv + 16 * P)
+        m["sh_grad_expand"] = ("hbm", (12 + 12 * world) * P + 12 * 16 * P)
     return m
 
 
@@ -422,7 +448,12 @@ def main():
             c = wl["cams"][v]
             cam_d = synthetic.Camera(c.image_width, c.image_height, c.FoVx, c.FoVy, c.tanfovx, c.tanfovy,
                                      mats_dev[0:16].view(4, 4), mats_dev[16:32].view(4, 4), mats_dev[32:35])
-            loss = arm.api_step(cam_d, gt_dev)
+            if world > 1 and args.impl == "ours":
+                base = (v - rank) % N_VIEWS
+                cams_step = [cam_d if r == rank else wl["cams_d"][(base + r) % N_VIEWS] for r in range(world)]
+                loss = arm.api_step_view_parallel(cams_step, gt_dev)
+            else:
+                loss = arm.api_step(cam_d, gt_dev)
             loss_host.copy_(loss.detach(), non_blocking=False)   # the per-iteration .item() of train.py:149
 
         ms_e2e = timed_loop(e2e_step, args.steps, max(3, args.warmup), world, rank)
@@ -447,6 +478,8 @@ def main():
                    "views_per_step": world, "parallelism": f"view-parallel x{world}" if world > 1 else "single GPU",
                    "l2": "inputs larger than L2 (surfel parameters %.2f GB >> 126 MB)" %
                          (wl["P"] * 58 * 4 / 1e9),
+                   "exchange": ("none (single GPU)" if world == 1 else
+                                "factored: all-reduce 40 B/surfel + all-gather dL/dRGB 12 B/surfel/view + local SH expand"),
                    "debug_P_override": args.P is not None},
         "clocks": clocks, "e2e": e2e,
     }
@@ -465,7 +498,7 @@ def main():
     # ---- roofline of every stage, dominant kernel first
     wcs = [work_counts(wl, v, device) for v in sorted({view_of(s) for s in range(args.steps)})][:N_VIEWS]
     wc = {k: sum(w[k] for w in wcs) / len(wcs) for k in wcs[0]}
-    model = stage_model(wl, wc, wl["deg"])
+    model = stage_model(wl, wc, wl["deg"], world)
     rows = []
     for name, (bound, work) in model.items():
         ms, calls = stages.get(name, (0.0, 0))
@@ -494,7 +527,7 @@ def main():
     line["stages"] = rows
     line["work"] = wc
     kernels_per_stage = {"preprocess_fwd": 1, "tile_scan": 1, "scatter": 1, "tile_sort": 3,
-                         "render_fwd": 1, "grad_zero": 0, "render_bwd": 1, "preprocess_bwd": 1}
+                         "render_fwd": 1, "grad_zero": 0, "render_bwd": 1, "preprocess_bwd": 1, "sh_grad_expand": 1}
     line["gpu_launches"] = int(sum(kernels_per_stage.get(n, 0) * c for n, (_, c) in stages.items()))
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(int(wc["E_bwd"]), wl["deg"])

@@ -17,7 +17,7 @@ GSM_ERR_BINNING_OVERFLOW = 10002
 GSM_ERR_WORKSPACE_TOO_SMALL = 10003
 GSM_SURFEL_RECORD_BYTES = 80
 GSM_GRAD_RECORD_FLOATS = 20
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 EXPORTS = [
     "gsm_last_error", "gsm_abi_version", "gsm_geometry_bytes", "gsm_image_bytes", "gsm_binning_bytes", "gsm_binning_persistent_bytes",
@@ -25,7 +25,7 @@ EXPORTS = [
     "gsm_forward", "gsm_grad_workspace_bytes", "gsm_backward", "gsm_mark_visible",
     "gsm_knn_workspace_bytes", "gsm_knn_dist2",
     "gsm_stage_count", "gsm_stage_name", "gsm_stage_timing_enable", "gsm_stage_timing_read",
-    "gsm_sort_pairs32_temp_bytes", "gsm_sort_pairs32",
+    "gsm_sort_pairs32_temp_bytes", "gsm_sort_pairs32", "gsm_sh_grad_expand",
 ]
 
 
@@ -58,6 +58,7 @@ class BackwardArgs(Structure):
         ("dL_dmeans2D", c_void_p), ("dL_dcolors", c_void_p), ("dL_dopacity", c_void_p),
         ("dL_dmeans3D", c_void_p), ("dL_dtransMat", c_void_p), ("dL_dsh", c_void_p),
         ("dL_dscales", c_void_p), ("dL_drotations", c_void_p), ("accumulate", c_int),
+        ("dL_drgb", c_void_p),
     ]
 
 
@@ -109,6 +110,8 @@ def load():
     lib.gsm_stage_timing_enable.argtypes = [c_int]
     lib.gsm_stage_timing_read.restype = c_int
     lib.gsm_stage_timing_read.argtypes = [POINTER(ctypes.c_double), POINTER(ctypes.c_longlong), c_int]
+    lib.gsm_sh_grad_expand.restype = c_int
+    lib.gsm_sh_grad_expand.argtypes = [c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]
     lib.gsm_sort_pairs32_temp_bytes.restype = c_size_t
     lib.gsm_sort_pairs32_temp_bytes.argtypes = [c_size_t]
     lib.gsm_sort_pairs32.restype = c_int

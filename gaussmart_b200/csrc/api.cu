@@ -27,7 +27,7 @@ int cuda_fail(cudaError_t e, const char* what) {
 // ---- optional per-stage device timing (gsm_stage_timing_*): cudaEvent pairs recorded on the
 // launching stream around every stage, resolved lazily when read.  Off by default.
 static const char* const kStageNames[GSM_NUM_STAGES] = {
-    "preprocess_fwd", "tile_scan", "scatter", "tile_sort", "unused", "render_fwd",
+    "preprocess_fwd", "tile_scan", "scatter", "tile_sort", "sh_grad_expand", "render_fwd",
     "grad_zero", "render_bwd", "preprocess_bwd", "knn"};
 
 struct StageTimer {
@@ -327,9 +327,23 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   pp.radii = a->radii; pp.records = rp.records; pp.grad_records = grad_records;
   pp.dL_dmeans2D = a->dL_dmeans2D; pp.dL_dcolors = a->dL_dcolors; pp.dL_dopacity = a->dL_dopacity;
   pp.dL_dmeans3D = a->dL_dmeans3D; pp.dL_dtransMat = a->dL_dtransMat; pp.dL_dsh = a->dL_dsh;
-  pp.dL_dscales = a->dL_dscales; pp.dL_drotations = a->dL_drotations;
+  pp.dL_dscales = a->dL_dscales; pp.dL_drotations = a->dL_drotations; pp.dL_drgb = a->dL_drgb;
   { StageMark m(GSM_STAGE_PREPROCESS_BWD, stream); launch_preprocess_bwd(pp, stream); }
   GSM_STAGE("backward preprocess");
+  return GSM_OK;
+}
+
+extern "C" int gsm_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,
+                                  const float* dL_drgb_all, float* dL_dsh, int accumulate, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0 || n_views < 0 || D < 0 || D > 3 || M < 0 || M > 16 || (D + 1) * (D + 1) > M) {
+    set_error("gsm_sh_grad_expand: bad sizes P=%d D=%d M=%d n_views=%d", P, D, M, n_views);
+    return GSM_ERR_INVALID_ARGUMENT;
+  }
+  if (P == 0) return GSM_OK;
+  StageMark m(GSM_STAGE_RANGES, stream);
+  launch_sh_grad_expand(P, D, M, n_views, means3D, campos_all, dL_drgb_all, dL_dsh, accumulate, stream);
+  GSM_CUDA(cudaGetLastError());
   return GSM_OK;
 }
 

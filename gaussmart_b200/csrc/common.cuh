@@ -239,7 +239,10 @@ struct BwdPreprocessParams {
   float* dL_dsh;
   float* dL_dscales;
   float* dL_drotations;
+  float* dL_drgb;  // optional [P,3]: factored mode, written INSTEAD of dL_dsh (see sh_grad_expand_kernel)
 };
 void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream);
+void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,
+                           const float* drgb_all, float* dL_dsh, int accumulate, cudaStream_t stream);
 
 }  // namespace gsm

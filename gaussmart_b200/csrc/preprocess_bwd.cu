@@ -23,6 +23,33 @@ __device__ __forceinline__ void store3(float* dst, f3 v, bool acc = false) {
   else { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; }
 }
 
+// SH basis coefficients of sh_backward (dL_dsh[k] = coef[k] * dL_dRGB), same expressions, for the
+// normalised direction (x, y, z); coefficients beyond degree D are zero.
+__device__ __forceinline__ void sh_coefficients(int D, float x, float y, float z, float (&coef)[16]) {
+#pragma unroll
+  for (int k = 0; k < 16; k++) coef[k] = 0.f;
+  const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
+  coef[0] = C0;
+  if (D > 0) {
+    coef[1] = -C1 * y; coef[2] = C1 * z; coef[3] = -C1 * x;
+    if (D > 1) {
+      const float C20 = 1.0925484305920792f, C21 = -1.0925484305920792f, C22 = 0.31539156525252005f,
+                  C23 = -1.0925484305920792f, C24 = 0.5462742152960396f;
+      const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+      coef[4] = C20 * xy; coef[5] = C21 * yz; coef[6] = C22 * (2.f * zz - xx - yy);
+      coef[7] = C23 * xz; coef[8] = C24 * (xx - yy);
+      if (D > 2) {
+        const float C30 = -0.5900435899266435f, C31 = 2.890611442640554f, C32 = -0.4570457994644658f,
+                    C33 = 0.3731763325901154f, C34 = -0.4570457994644658f, C35 = 1.445305721320277f,
+                    C36 = -0.5900435899266435f;
+        coef[9] = C30 * y * (3.f * xx - yy); coef[10] = C31 * xy * z; coef[11] = C32 * y * (4.f * zz - xx - yy);
+        coef[12] = C33 * z * (2.f * zz - 3.f * xx - 3.f * yy); coef[13] = C34 * x * (4.f * zz - xx - yy);
+        coef[14] = C35 * z * (xx - yy); coef[15] = C36 * x * (xx - 3.f * yy);
+      }
+    }
+  }
+}
+
 // SH backward (backward.cu:20-139), in place on a shared-memory row: on entry `row` holds this
 // surfel's SH coefficients (3M floats), on exit dL_dsh (zeros beyond the active degree).  Every
 // coefficient is read before its slot is overwritten.
@@ -34,26 +61,17 @@ __device__ void sh_backward(int D, int M, float* row, f3 dir_orig, f3 dL_dRGB, f
   const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
   f3 dx = mk(0, 0, 0), dy = mk(0, 0, 0), dz = mk(0, 0, 0);
 #define SH(k) mk(sh[3 * (k)], sh[3 * (k) + 1], sh[3 * (k) + 2])
-  store3(dL_dsh + 0, C0 * dL_dRGB);
   int written = 1;
   if (D > 0) {
     dx = (-C1) * SH(3);
     dy = (-C1) * SH(1);
     dz = C1 * SH(2);
-    store3(dL_dsh + 3, (-C1 * y) * dL_dRGB);
-    store3(dL_dsh + 6, (C1 * z) * dL_dRGB);
-    store3(dL_dsh + 9, (-C1 * x) * dL_dRGB);
     written = 4;
     if (D > 1) {
       const float C20 = 1.0925484305920792f, C21 = -1.0925484305920792f, C22 = 0.31539156525252005f,
                   C23 = -1.0925484305920792f, C24 = 0.5462742152960396f;
       const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
       const f3 s4 = SH(4), s5 = SH(5), s6 = SH(6), s7 = SH(7), s8 = SH(8);
-      store3(dL_dsh + 12, (C20 * xy) * dL_dRGB);
-      store3(dL_dsh + 15, (C21 * yz) * dL_dRGB);
-      store3(dL_dsh + 18, (C22 * (2.f * zz - xx - yy)) * dL_dRGB);
-      store3(dL_dsh + 21, (C23 * xz) * dL_dRGB);
-      store3(dL_dsh + 24, (C24 * (xx - yy)) * dL_dRGB);
       dx = dx + (C20 * y) * s4 + (C22 * 2.f * -x) * s6 + (C23 * z) * s7 + (C24 * 2.f * x) * s8;
       dy = dy + (C20 * x) * s4 + (C21 * z) * s5 + (C22 * 2.f * -y) * s6 + (C24 * 2.f * -y) * s8;
       dz = dz + (C21 * y) * s5 + (C22 * 2.f * 2.f * z) * s6 + (C23 * x) * s7;
@@ -63,13 +81,6 @@ __device__ void sh_backward(int D, int M, float* row, f3 dir_orig, f3 dL_dRGB, f
                     C33 = 0.3731763325901154f, C34 = -0.4570457994644658f, C35 = 1.445305721320277f,
                     C36 = -0.5900435899266435f;
         const f3 s9 = SH(9), s10 = SH(10), s11 = SH(11), s12 = SH(12), s13 = SH(13), s14 = SH(14), s15 = SH(15);
-        store3(dL_dsh + 27, (C30 * y * (3.f * xx - yy)) * dL_dRGB);
-        store3(dL_dsh + 30, (C31 * xy * z) * dL_dRGB);
-        store3(dL_dsh + 33, (C32 * y * (4.f * zz - xx - yy)) * dL_dRGB);
-        store3(dL_dsh + 36, (C33 * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB);
-        store3(dL_dsh + 39, (C34 * x * (4.f * zz - xx - yy)) * dL_dRGB);
-        store3(dL_dsh + 42, (C35 * z * (xx - yy)) * dL_dRGB);
-        store3(dL_dsh + 45, (C36 * x * (xx - 3.f * yy)) * dL_dRGB);
         dx = dx + ((C30 * 3.f * 2.f * xy) * s9 + (C31 * yz) * s10 + (C32 * -2.f * xy) * s11 +
                    (C33 * -3.f * 2.f * xz) * s12 + (C34 * (-3.f * xx + 4.f * zz - yy)) * s13 +
                    (C35 * 2.f * xz) * s14 + (C36 * 3.f * (xx - yy)) * s15);
@@ -83,6 +94,14 @@ __device__ void sh_backward(int D, int M, float* row, f3 dir_orig, f3 dL_dRGB, f
     }
   }
 #undef SH
+  // every coefficient above has been read: the row now becomes dL_dsh = coef (x) dL_dRGB (zeros beyond degree D)
+  {
+    float coef[16];
+    sh_coefficients(D, x, y, z, coef);
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+      if (k < written) store3(dL_dsh + 3 * k, coef[k] * dL_dRGB);
+  }
   for (int k = written * 3; k < M * 3; k++) dL_dsh[k] = 0.0f;
 
   const f3 dL_ddir = mk(dot(dx, dL_dRGB), dot(dy, dL_dRGB), dot(dz, dL_dRGB));
@@ -171,7 +190,10 @@ __global__ void __launch_bounds__(PBWD_THREADS) preprocess_bwd_kernel(const BwdP
   const int rows = min(32, p.P - warp_first);
   float* wsm = sh_smem + (size_t)warp * 32 * (3 * p.M + 1);
   float* my_row = wsm + lane * (3 * p.M + 1);
-  const bool has_sh = p.shs != nullptr && p.dL_dsh != nullptr;
+  // factored mode (view-parallel): dL_dRGB is written instead of the 3M-float dL_dsh row, which the
+  // receiver rebuilds as basis(dir) (x) dL_dRGB (sh_grad_expand_kernel); the SH term of dL_dmean3D stays here
+  const bool factored = p.dL_drgb != nullptr;
+  const bool has_sh = p.shs != nullptr && (p.dL_dsh != nullptr || factored);
   if (has_sh) {
     sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, p.M, rows, vis_mask, lane);
     __syncwarp();
@@ -179,7 +201,7 @@ __global__ void __launch_bounds__(PBWD_THREADS) preprocess_bwd_kernel(const BwdP
 
   f3 dmean3D = mk(0, 0, 0);
   float dmean2D_x = 0.f, dmean2D_y = 0.f, dopacity = 0.f;
-  f3 dcolor = mk(0, 0, 0);
+  f3 dcolor = mk(0, 0, 0), drgb_masked = mk(0, 0, 0);
   float dscale_x = 0.f, dscale_y = 0.f;
   float4 drot = make_float4(0, 0, 0, 0);
   float dT[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -316,6 +338,7 @@ __global__ void __launch_bounds__(PBWD_THREADS) preprocess_bwd_kernel(const BwdP
       f3 add;
       sh_backward(p.D, p.M, my_row, dir_orig, dRGB, add);
       dmean3D = dmean3D + add;
+      drgb_masked = dRGB;
     }
 
     // densification heuristic (backward.cu:632-635); in the precomputed-T case the reference reads
@@ -326,7 +349,9 @@ __global__ void __launch_bounds__(PBWD_THREADS) preprocess_bwd_kernel(const BwdP
     dmean2D_y = a5 * depth * 0.5f * float(p.H);
   }
 
-  if (has_sh) {
+  if (has_sh && factored) {
+    if (valid) store3(p.dL_drgb + 3 * i, drgb_masked);  // per view: never accumulated
+  } else if (has_sh) {
     __syncwarp();
     sh_rows_store(wsm, p.dL_dsh + (size_t)warp_first * p.M * 3, p.M, rows, vis_mask, acc, lane);
   } else if (p.dL_dsh != nullptr && valid && !acc) {
@@ -364,6 +389,76 @@ __global__ void __launch_bounds__(PBWD_THREADS) preprocess_bwd_kernel(const BwdP
   if (p.dL_dscales) { p.dL_dscales[2 * i] = dscale_x; p.dL_dscales[2 * i + 1] = dscale_y; }
   if (p.dL_drotations) reinterpret_cast<float4*>(p.dL_drotations)[i] = drot;
 }
+
+// View-parallel exchange, receiving side: dL_dsh[p] (=|+=) sum over views v of basis(dir_v(p)) (x) dL_dRGB_v[p].
+// dL_dsh of ONE view is a rank-1 product of a view-dependent basis (a function of the surfel position and
+// the view's camera centre, both known on every rank) and 3 floats, so ranks exchange the 3 floats
+// (12 B/surfel/view) instead of the 12M-byte row (192 B at M = 16).  One thread per surfel; the rows
+// leave through shared memory as coalesced 128-bit stores (sh_rows_store).
+__global__ void __launch_bounds__(PBWD_THREADS)
+sh_grad_expand_kernel(int P, int D, int M, int n_views, const float* __restrict__ means3D,
+                      const float* __restrict__ campos_all, const float* __restrict__ drgb_all,
+                      float* __restrict__ dL_dsh, int accumulate) {
+  extern __shared__ float sh_smem[];
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int warp_first = idx - lane;
+  if (warp_first >= P) return;
+  const bool valid = idx < P;
+  const size_t i = (size_t)(valid ? idx : P - 1);
+  const int rows = min(32, P - warp_first);
+  float* wsm = sh_smem + (size_t)warp * 32 * (3 * M + 1);
+  float* my_row = wsm + lane * (3 * M + 1);
+  const f3 pos = mk(__ldg(means3D + 3 * i), __ldg(means3D + 3 * i + 1), __ldg(means3D + 3 * i + 2));
+  const int K = min(M, (D + 1) * (D + 1));
+  float acc[48];
+#pragma unroll
+  for (int k = 0; k < 48; k++) acc[k] = 0.f;
+  bool any = false;
+  for (int v = 0; v < n_views; v++) {
+    const float* g = drgb_all + ((size_t)v * P + i) * 3;
+    const f3 d = mk(__ldg(g), __ldg(g + 1), __ldg(g + 2));
+    if (!valid || (d.x == 0.f && d.y == 0.f && d.z == 0.f)) continue;  // culled in this view (or no gradient)
+    any = true;
+    const f3 dir = mk(pos.x - __ldg(campos_all + 3 * v), pos.y - __ldg(campos_all + 3 * v + 1),
+                      pos.z - __ldg(campos_all + 3 * v + 2));
+    const float len = __fsqrt_rn(__fmaf_rn(dir.z, dir.z, __fmaf_rn(dir.x, dir.x, __fmul_rn(dir.y, dir.y))));
+    float coef[16];
+    sh_coefficients(D, __fdiv_rn(dir.x, len), __fdiv_rn(dir.y, len), __fdiv_rn(dir.z, len), coef);
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      acc[3 * k] += coef[k] * d.x; acc[3 * k + 1] += coef[k] * d.y; acc[3 * k + 2] += coef[k] * d.z;
+    }
+  }
+  const unsigned vis_mask = __ballot_sync(0xffffffffu, any);
+  if (any) {
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      if (k < M) {
+        const bool on = k < K;
+        my_row[3 * k] = on ? acc[3 * k] : 0.f; my_row[3 * k + 1] = on ? acc[3 * k + 1] : 0.f;
+        my_row[3 * k + 2] = on ? acc[3 * k + 2] : 0.f;
+      }
+    }
+    for (int k = 16; k < M; k++) { my_row[3 * k] = 0.f; my_row[3 * k + 1] = 0.f; my_row[3 * k + 2] = 0.f; }
+  }
+  __syncwarp();
+  sh_rows_store(wsm, dL_dsh + (size_t)warp_first * M * 3, M, rows, vis_mask, accumulate != 0, lane);
+}
+
+void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,
+                           const float* drgb_all, float* dL_dsh, int accumulate, cudaStream_t stream) {
+  if (P <= 0 || M <= 0) return;
+  const size_t smem = (size_t)(PBWD_THREADS / 32) * 32 * (3 * M + 1) * sizeof(float);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    cudaFuncSetAttribute(sh_grad_expand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    configured = smem;
+  }
+  sh_grad_expand_kernel<<<(P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(
+      P, D, M, n_views, means3D, campos_all, drgb_all, dL_dsh, accumulate);
+}
+
 
 void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream) {
   if (p.P <= 0) return;

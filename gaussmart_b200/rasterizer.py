@@ -129,11 +129,14 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
 
 def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp, viewmatrix,
                    projmatrix, tanfovx, tanfovy, grad_out_color, grad_depth, sh, sh_degree, campos, geomBuffer,
-                   num_rendered, binningBuffer, imgBuffer, debug, out=None, accumulate=False, binning_capacity=None):
+                   num_rendered, binningBuffer, imgBuffer, debug, out=None, accumulate=False, binning_capacity=None,
+                   rgb_out=None):
     """Equivalent of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:136-233).
 
     `out` (optional) maps means3D / shs / opacities / scales / rotations to preallocated tensors the
-    kernel writes into (or adds to, with `accumulate`) -- the view-parallel gradient bucket."""
+    kernel writes into (or adds to, with `accumulate`) -- the view-parallel gradient bucket.
+    `rgb_out` (optional, [P,3]) selects the factored SH gradient: the kernel writes dL/dRGB there and no
+    dL_dsh rows (gsm_backward_args.dL_drgb); `sh_grad_expand` rebuilds them."""
     lib = _lib.load()
     P = means3D.shape[0]
     H, W = grad_out_color.shape[1], grad_out_color.shape[2]
@@ -162,7 +165,10 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
         dL_dcolors = _out("colors_precomp", (P, 3)) if colors_precomp.numel() != 0 else None
         dL_dopacity = _out("opacities", (P, 1))
         dL_dtransMat = _out("cov3D_precomp", (P, 9)) if cov3Ds_precomp.numel() != 0 else None
-        dL_dsh = _out("shs", (P, M, 3)) if M != 0 else None
+        if rgb_out is not None and (M == 0 or tuple(rgb_out.shape) != (P, 3) or rgb_out.dtype != torch.float32
+                                    or not rgb_out.is_contiguous() or rgb_out.device != dev):
+            raise RuntimeError("rgb_out must be a contiguous float32 [P,3] tensor on the surfels' device (and shs given)")
+        dL_dsh = _out("shs", (P, M, 3)) if (M != 0 and rgb_out is None) else None
         dL_dscales = _out("scales", (P, 2)) if scales.numel() != 0 else None
         dL_drotations = _out("rotations", (P, 4)) if rotations.numel() != 0 else None
         if P != 0:
@@ -185,6 +191,7 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
             a.dL_dmeans3D, a.dL_dtransMat, a.dL_dsh = _ptr(dL_dmeans3D), _ptr(dL_dtransMat), _ptr(dL_dsh)
             a.dL_dscales, a.dL_drotations = _ptr(dL_dscales), _ptr(dL_drotations)
             a.accumulate = int(bool(accumulate))
+            a.dL_drgb = _ptr(rgb_out)
             stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
             _lib.check(lib.gsm_backward(ctypes.byref(a), stream), "backward")
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dtransMat, dL_dsh, dL_dscales, dL_drotations
@@ -271,7 +278,27 @@ class _RasterizeGaussians(torch.autograd.Function):
         return grads
 
 
-def rasterize_into_bucket(params, camera, bucket, accumulate, bg=None, scale_modifier=1.0):
+def sh_grad_expand(means3D, campos_all, rgb_all, dL_dsh, sh_degree, accumulate=False):
+    """dL_dsh[P,M,3] (= or +=) sum over views v of basis(normalize(means3D - campos_all[v])) (x) rgb_all[v]
+    (gsm_sh_grad_expand): the receiving side of the factored view-parallel exchange."""
+    lib = _lib.load()
+    P, M = dL_dsh.shape[0], dL_dsh.shape[1]
+    n_views = rgb_all.shape[0]
+    dev = dL_dsh.device
+    for name, t, shape in (("means3D", means3D, (P, 3)), ("campos_all", campos_all, (n_views, 3)),
+                           ("rgb_all", rgb_all, (n_views, P, 3)), ("dL_dsh", dL_dsh, (P, M, 3))):
+        _check_cuda(name, t)
+        if tuple(t.shape) != shape or t.dtype != torch.float32 or not t.is_contiguous():
+            raise RuntimeError(f"{name} must be contiguous float32 {shape}")
+    with torch.cuda.device(dev):
+        stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        _lib.check(lib.gsm_sh_grad_expand(P, int(sh_degree), M, n_views, _ptr(means3D), _ptr(campos_all), _ptr(rgb_all),
+                                          _ptr(dL_dsh), int(bool(accumulate)), stream), "sh_grad_expand")
+    return dL_dsh
+
+
+def rasterize_into_bucket(params, camera, bucket, accumulate, bg=None, scale_modifier=1.0, rgb_out=None,
+                          sh_degree=None):
     """Forward + (deferred) backward of one view with the surfel gradients written by the backward
     preprocess kernel straight into `bucket.views` (gaussmart_b200.view_parallel.GradBucket) -- no
     autograd, no pack kernel before the collective.
@@ -286,7 +313,8 @@ def rasterize_into_bucket(params, camera, bucket, accumulate, bg=None, scale_mod
     if bg is None:
         bg = torch.zeros(3, dtype=torch.float32, device=dev)
     sh = params["shs"]
-    sh_degree = int(round(sh.shape[1] ** 0.5)) - 1
+    if sh_degree is None:  # active degree (gaussian_model.py:oneupSHdegree); default: all allocated coefficients
+        sh_degree = int(round(sh.shape[1] ** 0.5)) - 1
     H, W = int(camera.image_height), int(camera.image_width)
     with torch.no_grad():
         R, color, allmap, radii, geom, binning, image = _forward_impl(
@@ -301,7 +329,7 @@ def rasterize_into_bucket(params, camera, bucket, accumulate, bg=None, scale_mod
                                camera.world_view_transform.contiguous(), camera.full_proj_transform.contiguous(),
                                camera.tanfovx, camera.tanfovy, dL_dcolor, dL_dallmap, sh.contiguous(), sh_degree,
                                camera.camera_center.contiguous(), geom, R, binning, image, False,
-                               out=bucket.views, accumulate=accumulate)
+                               out=bucket.views, accumulate=accumulate, rgb_out=rgb_out)
         return g[0]
 
     return color, radii, allmap, backward

@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 2
+#define GSM_ABI_VERSION 3
 
 #define GSM_OK 0
 #define GSM_ERR_INVALID_ARGUMENT 10001
@@ -123,7 +123,7 @@ typedef struct gsm_backward_args {
   int width, height;
   float tan_fovx, tan_fovy;
   float scale_modifier;
-  int debug;
+  int debug;            /* bits as gsm_forward_args.debug */
   const float* background;
   const float* means3D;
   const float* shs;
@@ -153,10 +153,22 @@ typedef struct gsm_backward_args {
   int accumulate;       /* 0: outputs are overwritten (reference semantics: fresh zero tensors,
                            rasterize_points.cu:187-195).  1: every output except dL_dmeans2D is
                            ADDED to (view-parallel accumulation over a rank's local views) */
+  float* dL_drgb;       /* optional [P,3] (NULL: reference behaviour).  Factored SH gradient for the view-parallel
+                           exchange: when given (with shs), the clamp-masked dL/dRGB of every surfel (zeros for
+                           culled ones) is written here INSTEAD of the [P,M,3] dL_dsh rows (dL_dsh may be NULL);
+                           gsm_sh_grad_expand rebuilds dL_dsh from it on any rank.  Never accumulated. */
 } gsm_backward_args;
 
 size_t gsm_grad_workspace_bytes(int P);
 int gsm_backward(const gsm_backward_args* args, void* stream);
+
+/* ---- view-parallel exchange, receiving side (new: the reference is single-GPU).  dL_dsh of one view is the
+ *      rank-1 product basis(normalize(mean - campos_view)) (x) dL_dRGB (backward.cu:20-139), so ranks exchange
+ *      dL_dRGB (12 B/surfel/view) instead of the 12M-byte row.  dL_dsh[p] (= or +=, `accumulate`) the sum over
+ *      the n_views views of basis (x) dL_drgb_all[v][p]; D = active SH degree, M = allocated coefficients. */
+int gsm_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D /*[P,3]*/,
+                       const float* campos_all /*[n_views,3]*/, const float* dL_drgb_all /*[n_views,P,3]*/,
+                       float* dL_dsh /*[P,M,3]*/, int accumulate, void* stream);
 
 /* ---- markVisible: replaces CudaRasterizer::Rasterizer::markVisible (rasterizer.h:24-31,
  *      rasterizer_impl.cu:141-153; rasterize_points.cu:235-254).  present is uint8[P]. */

@@ -309,3 +309,75 @@ def test_bucket_path_matches_autograd_and_accumulates(P):
         assert torch.isfinite(bucket.views[k]).all()
         viol, _ = grad_violations(bucket.views[k].cpu(), want.cpu(), rel=1e-4, floor=1e-6)
         assert viol <= 2, (k, viol)
+
+
+@pytest.mark.parametrize("P,deg", [(5000, 3), (4999 + 32 * 7, 1)])
+def test_factored_sh_gradient_matches_dense_path(P, deg):
+    """View-parallel factored exchange on one rank: K6 writes dL/dRGB instead of dL_dsh (gsm_backward_args.dL_drgb),
+    gsm_sh_grad_expand rebuilds basis(dir_view) (x) dL/dRGB summed over 3 views (one slot left empty).  Must equal
+    the dense path (K6 writing dL_dsh rows, accumulated over the same views) up to the atomics' summation-order noise."""
+    from gaussmart_b200 import view_parallel as vp
+    W, H = 160, 120
+    M = (deg + 1) ** 2 if deg == 3 else 16   # deg 1 with 16 allocated coefficients: rows beyond K must be zero
+    scene = synthetic.make_scene(P, W, 3 if M == 16 else deg, 92)
+    scene = scene._replace(scales=scene.scales * 2.0)
+    cams = [synthetic.make_camera(W, H, th) for th in (0.0, 0.7, -0.5)]
+    cams_d = [synthetic.Camera(*[x.cuda() if isinstance(x, torch.Tensor) else x for x in c]) for c in cams]
+    cot = synthetic.make_cotangents(W, H, 17)
+    full = scene.shs.cuda()
+    params = dict(means3D=scene.means3D.cuda(), shs=full, opacities=scene.opacities.cuda(),
+                  scales=scene.scales.cuda(), rotations=scene.rotations.cuda())
+
+    class _P(dict):
+        pass
+
+    def raster(params_, cam, bucket, acc, rgb_out=None):
+        # active degree `deg` on M allocated coefficients, as gaussian_model.py's oneupSHdegree schedule does
+        from gaussmart_b200.rasterizer import _forward_impl, _backward_impl
+        e = torch.empty(0, device="cuda")
+        bg = torch.zeros(3, device="cuda")
+        R, color, allmap, radii, geom, binning, image = _forward_impl(
+            bg, params_["means3D"], e, params_["opacities"], params_["scales"], params_["rotations"], 1.0, e,
+            cam.world_view_transform, cam.full_proj_transform, cam.tanfovx, cam.tanfovy, H, W, params_["shs"], deg,
+            cam.camera_center, False, False)
+
+        def backward(dc, da):
+            g = _backward_impl(bg, params_["means3D"], radii, e, params_["scales"], params_["rotations"], 1.0, e,
+                               cam.world_view_transform.contiguous(), cam.full_proj_transform.contiguous(), cam.tanfovx,
+                               cam.tanfovy, dc, da, params_["shs"], deg, cam.camera_center.contiguous(), geom, R, binning,
+                               image, False, out=bucket.views, accumulate=acc, rgb_out=rgb_out)
+            return g[0]
+        return color, radii, allmap, backward
+
+    for n_views in (1, 3):
+        dense = vp.GradBucket(P, M, "cuda")
+        dense.flat.fill_(float("nan"))
+        vp.view_parallel_step(params, cams_d[:n_views], dense, lambda v, c, a: (cot[0].cuda(), cot[1].cuda()),
+                              raster_fn=lambda p_, c_, b_, a_: raster(p_, c_, b_, a_), rank=0, world_size=1, reduce=False)
+        ex = vp.FactoredExchange(P, M, "cuda", 1, max_local_views=4)   # 4 slots, at most 3 used
+        ex.flat.fill_(float("nan"))
+        ex.rgb_send.fill_(float("nan"))
+        ex.dL_dsh.fill_(float("nan"))
+        from gaussmart_b200.rasterizer import sh_grad_expand
+        vp.view_parallel_step_factored(params, cams_d[:n_views], ex, lambda v, c, a: (cot[0].cuda(), cot[1].cuda()),
+                                       raster_fn=raster, expand_fn=sh_grad_expand, rank=0, world_size=1, sh_degree=deg)
+        g = ex.gradients()
+        # (two separate backward runs: the gradient records are sums of unordered fp32 atomics, so equality is
+        # up to that noise, as between two runs of the reference)
+        for k in ("means3D", "opacities", "scales", "rotations"):
+            viol, _ = grad_violations(g[k].cpu(), dense.views[k].cpu(), rel=1e-4, floor=1e-6)
+            assert viol <= 2, (k, viol)
+        assert torch.isfinite(g["shs"]).all()
+        K = (deg + 1) ** 2
+        assert (g["shs"][:, K:] == 0).all() and (dense.views["shs"][:, K:] == 0).all()
+        assert g["shs"].abs().max() > 0
+        viol, _ = grad_violations(g["shs"].cpu(), dense.views["shs"].cpu(), rel=1e-4, floor=1e-6)
+        assert viol <= 2, viol
+        rel_fro = ((g["shs"] - dense.views["shs"]).double().norm() / dense.views["shs"].double().norm()).item()
+        assert rel_fro < 1e-5, rel_fro
+        # the expansion itself is exact: rebuilt from THIS run's dL/dRGB, a row is coefficient * dL/dRGB bit for bit
+        if n_views == 1:
+            dc0 = ex.rgb_recv[0, 0] * 0.28209479177387814
+            assert torch.equal(g["shs"][:, 0], dc0)
+        assert torch.allclose(ex.stats[0], dense.stats[0], rtol=1e-4, atol=1e-7) and torch.equal(ex.stats[1], dense.stats[1])
+        assert torch.equal(ex.max_radii, dense.max_radii)

@@ -172,7 +172,9 @@ class OursArm:
         cams = [wl["cams_d"][(base + r) % N_VIEWS] for r in range(self.world)]
         self.vp.view_parallel_step_factored(
             wl["params"], cams, self.ex, lambda v, c, a: wl["cot_d"],
-            raster_fn=lambda p_, c_, b_, a_, rgb_out=None: rasterize_into_bucket(p_, c_, b_, a_, bg=self.bg, rgb_out=rgb_out))
+            raster_fn=lambda p_, c_, b_, a_, rgb_out=None: rasterize_into_bucket(p_, c_, b_, a_, bg=self.bg, rgb_out=rgb_out,
+                                                                                fused_stats=True),
+            fused_stats=True)
 
     def api_step(self, cam_d, gt):
         """Public API: GaussianRasterizationSettings / GaussianRasterizer + autograd (gr.py:37-97 shape)."""
@@ -206,7 +208,9 @@ class OursArm:
 
         self.vp.view_parallel_step_factored(
             self.leaves_data, cams_step, self.ex, cot,
-            raster_fn=lambda p_, c_, b_, a_, rgb_out=None: rasterize_into_bucket(p_, c_, b_, a_, bg=self.bg, rgb_out=rgb_out))
+            raster_fn=lambda p_, c_, b_, a_, rgb_out=None: rasterize_into_bucket(p_, c_, b_, a_, bg=self.bg, rgb_out=rgb_out,
+                                                                                fused_stats=True),
+            fused_stats=True)
         return box["loss"]
 
 

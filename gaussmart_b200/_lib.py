@@ -59,6 +59,7 @@ class BackwardArgs(Structure):
         ("dL_dmeans3D", c_void_p), ("dL_dtransMat", c_void_p), ("dL_dsh", c_void_p),
         ("dL_dscales", c_void_p), ("dL_drotations", c_void_p), ("accumulate", c_int),
         ("dL_drgb", c_void_p),
+        ("densify_grad_norm", c_void_p), ("densify_visible", c_void_p), ("max_radii", c_void_p),
     ]
 
 

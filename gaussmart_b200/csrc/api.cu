@@ -328,6 +328,7 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   pp.dL_dmeans2D = a->dL_dmeans2D; pp.dL_dcolors = a->dL_dcolors; pp.dL_dopacity = a->dL_dopacity;
   pp.dL_dmeans3D = a->dL_dmeans3D; pp.dL_dtransMat = a->dL_dtransMat; pp.dL_dsh = a->dL_dsh;
   pp.dL_dscales = a->dL_dscales; pp.dL_drotations = a->dL_drotations; pp.dL_drgb = a->dL_drgb;
+  pp.stat_norm = a->densify_grad_norm; pp.stat_vis = a->densify_visible; pp.max_radii = a->max_radii;
   { StageMark m(GSM_STAGE_PREPROCESS_BWD, stream); launch_preprocess_bwd(pp, stream); }
   GSM_STAGE("backward preprocess");
   return GSM_OK;

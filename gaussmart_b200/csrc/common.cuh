@@ -240,6 +240,9 @@ struct BwdPreprocessParams {
   float* dL_dscales;
   float* dL_drotations;
   float* dL_drgb;  // optional [P,3]: factored mode, written INSTEAD of dL_dsh (see sh_grad_expand_kernel)
+  float* stat_norm;  // optional [P]: += ||dL_dmeans2D.xy|| of visible surfels
+  float* stat_vis;   // optional [P]: += 1 for visible surfels
+  int* max_radii;    // optional [P]: max= radii
 };
 void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream);
 void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,

@@ -361,6 +361,11 @@ __global__ void __launch_bounds__(PBWD_THREADS) preprocess_bwd_kernel(const BwdP
   if (!valid) return;
   // the view-space gradient is per view (gm.py:551-553 takes its norm per view): never accumulated
   p.dL_dmeans2D[3 * i] = dmean2D_x; p.dL_dmeans2D[3 * i + 1] = dmean2D_y; p.dL_dmeans2D[3 * i + 2] = 0.f;
+  if (visible) {  // densification statistics of the view (gaussian_model.py:551-553), fused
+    if (p.stat_norm) p.stat_norm[i] += sqrtf(dmean2D_x * dmean2D_x + dmean2D_y * dmean2D_y);
+    if (p.stat_vis) p.stat_vis[i] += 1.0f;
+    if (p.max_radii) p.max_radii[i] = max(p.max_radii[i], __ldg(p.radii + idx));
+  }
   if (acc) {
     if (!visible) return;  // adds nothing
     p.dL_dopacity[i] += dopacity;

@@ -130,11 +130,12 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
 def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp, viewmatrix,
                    projmatrix, tanfovx, tanfovy, grad_out_color, grad_depth, sh, sh_degree, campos, geomBuffer,
                    num_rendered, binningBuffer, imgBuffer, debug, out=None, accumulate=False, binning_capacity=None,
-                   rgb_out=None):
+                   rgb_out=None, stats=None):
     """Equivalent of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:136-233).
 
     `out` (optional) maps means3D / shs / opacities / scales / rotations to preallocated tensors the
     kernel writes into (or adds to, with `accumulate`) -- the view-parallel gradient bucket.
+    `stats` (optional) = (grad_norm[P], visible[P], max_radii[P]): densification statistics accumulated by the kernel.
     `rgb_out` (optional, [P,3]) selects the factored SH gradient: the kernel writes dL/dRGB there and no
     dL_dsh rows (gsm_backward_args.dL_drgb); `sh_grad_expand` rebuilds them."""
     lib = _lib.load()
@@ -192,6 +193,12 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
             a.dL_dscales, a.dL_drotations = _ptr(dL_dscales), _ptr(dL_drotations)
             a.accumulate = int(bool(accumulate))
             a.dL_drgb = _ptr(rgb_out)
+            if stats is not None:  # (grad_norm[P] f32, visible[P] f32, max_radii[P] i32): fused densification statistics
+                gn, vis, mr = stats
+                for t, dt in ((gn, torch.float32), (vis, torch.float32), (mr, torch.int32)):
+                    if tuple(t.shape) != (P,) or t.dtype != dt or not t.is_contiguous() or t.device != dev:
+                        raise RuntimeError("stats must be contiguous [P] tensors (float32, float32, int32) on the surfels' device")
+                a.densify_grad_norm, a.densify_visible, a.max_radii = _ptr(gn), _ptr(vis), _ptr(mr)
             stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
             _lib.check(lib.gsm_backward(ctypes.byref(a), stream), "backward")
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dtransMat, dL_dsh, dL_dscales, dL_drotations
@@ -298,7 +305,7 @@ def sh_grad_expand(means3D, campos_all, rgb_all, dL_dsh, sh_degree, accumulate=F
 
 
 def rasterize_into_bucket(params, camera, bucket, accumulate, bg=None, scale_modifier=1.0, rgb_out=None,
-                          sh_degree=None):
+                          sh_degree=None, fused_stats=False):
     """Forward + (deferred) backward of one view with the surfel gradients written by the backward
     preprocess kernel straight into `bucket.views` (gaussmart_b200.view_parallel.GradBucket) -- no
     autograd, no pack kernel before the collective.
@@ -329,7 +336,8 @@ def rasterize_into_bucket(params, camera, bucket, accumulate, bg=None, scale_mod
                                camera.world_view_transform.contiguous(), camera.full_proj_transform.contiguous(),
                                camera.tanfovx, camera.tanfovy, dL_dcolor, dL_dallmap, sh.contiguous(), sh_degree,
                                camera.camera_center.contiguous(), geom, R, binning, image, False,
-                               out=bucket.views, accumulate=accumulate, rgb_out=rgb_out)
+                               out=bucket.views, accumulate=accumulate, rgb_out=rgb_out,
+                               stats=(bucket.stats[0], bucket.stats[1], bucket.max_radii) if fused_stats else None)
         return g[0]
 
     return color, radii, allmap, backward

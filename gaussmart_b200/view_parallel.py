@@ -150,18 +150,20 @@ class FactoredExchange:
     def __init__(self, P: int, M: int, device, world_size: int, max_local_views: int = 1, with_stats: bool = True):
         self.P, self.M, self.world_size, self.max_local_views = P, M, world_size, max_local_views
         sizes = [(name, (P,) + shape, P * shape[0]) for name, shape in SMALL_SEGMENTS]
-        n = sum((cnt + 31) // 32 * 32 for _, _, cnt in sizes)
+        P_pad = (P + 31) // 32 * 32
+        n = sum((cnt + 31) // 32 * 32 for _, _, cnt in sizes) + (2 * P_pad if with_stats else 0)
         self.flat = torch.zeros(n, dtype=torch.float32, device=device)   # the all-reduced part
         self.views: Dict[str, torch.Tensor] = {}
         off = 0
         for name, shape, cnt in sizes:
             self.views[name] = self.flat[off:off + cnt].view(shape)
             off += (cnt + 31) // 32 * 32
+        self._stats_off = off  # the densification statistics ride in the same all-reduce (both are sums)
         self.rgb_send = torch.zeros(max_local_views, P, 3, dtype=torch.float32, device=device)
         self.rgb_recv = torch.zeros(world_size, max_local_views, P, 3, dtype=torch.float32, device=device)
         self.campos = torch.zeros(world_size * max_local_views, 3, dtype=torch.float32, device=device)
         self.dL_dsh = torch.zeros(P, M, 3, dtype=torch.float32, device=device)  # rebuilt locally, identical on all ranks
-        self.stats = torch.zeros(2, P, dtype=torch.float32, device=device) if with_stats else None
+        self.stats = self.flat[off:off + 2 * P_pad].view(2, P_pad)[:, :P] if with_stats else None
         self.max_radii = torch.zeros(P, dtype=torch.int32, device=device) if with_stats else None
 
     def wire_bytes(self) -> int:
@@ -183,22 +185,24 @@ def exchange_factored(ex: FactoredExchange, group=None):
         dist.all_gather_into_tensor(ex.rgb_recv.view(-1), ex.rgb_send.view(-1), group=group)
     else:
         dist.all_gather(list(ex.rgb_recv.unbind(0)), ex.rgb_send, group=group)
-    dist.all_reduce(ex.flat, op=dist.ReduceOp.SUM, group=group)
-    if ex.stats is not None:
-        dist.all_reduce(ex.stats, op=dist.ReduceOp.SUM, group=group)
+    dist.all_reduce(ex.flat, op=dist.ReduceOp.SUM, group=group)   # gradients + (grad-norm, visibility) statistics
+    if ex.max_radii is not None:
         dist.all_reduce(ex.max_radii, op=dist.ReduceOp.MAX, group=group)
 
 
 def view_parallel_step_factored(params: Dict[str, torch.Tensor], cameras: Sequence, ex: FactoredExchange,
                                 cotangent_fn: Callable, raster_fn: Optional[Callable] = None,
                                 expand_fn: Optional[Callable] = None, group=None, rank: Optional[int] = None,
-                                world_size: Optional[int] = None, sh_degree: Optional[int] = None) -> List[ViewResult]:
+                                world_size: Optional[int] = None, sh_degree: Optional[int] = None,
+                                fused_stats: bool = False) -> List[ViewResult]:
     """view_parallel_step with the factored exchange.  After the call ex.gradients() holds, on every rank, the
     gradient of all five parameter tensors summed over ALL views of `cameras`.
 
     raster_fn : (params, camera, ex, accumulate, rgb_out=) -> (color, radii, allmap, backward) -- writes the small
                 segments into ex.views and dL_dRGB of the view into rgb_out
     expand_fn : (means3D, campos_all[V,3], rgb_all[V,P,3], dL_dsh[P,M,3], sh_degree) -> None
+    fused_stats : raster_fn's backward accumulates the densification statistics itself (the CUDA rasterizer does,
+                with fused_stats=True: gsm_backward_args.densify_*); otherwise they are added here with torch ops
     sh_degree : ACTIVE SH degree the views were rasterised with (default: the degree the M allocated coefficients hold)
     """
     if rank is None:
@@ -222,13 +226,13 @@ def view_parallel_step_factored(params: Dict[str, torch.Tensor], cameras: Sequen
     if not mine:
         ex.flat.zero_()
     if ex.stats is not None:
-        ex.stats.zero_()
+        ex.flat[ex._stats_off:].zero_()
         ex.max_radii.zero_()
     for j, v in enumerate(mine):
         color, radii, allmap, backward = raster_fn(params, cameras[v], ex, j > 0, rgb_out=ex.rgb_send[j])
         dc, da = cotangent_fn(v, color, allmap)
         dL_dmeans2D = backward(dc, da)
-        if ex.stats is not None:
+        if ex.stats is not None and not fused_stats:
             add_densification_stats(ex, dL_dmeans2D, radii)
         results.append(ViewResult(color, radii, allmap))
     if len(mine) < ex.max_local_views:

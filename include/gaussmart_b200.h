@@ -157,6 +157,12 @@ typedef struct gsm_backward_args {
                            exchange: when given (with shs), the clamp-masked dL/dRGB of every surfel (zeros for
                            culled ones) is written here INSTEAD of the [P,M,3] dL_dsh rows (dL_dsh may be NULL);
                            gsm_sh_grad_expand rebuilds dL_dsh from it on any rank.  Never accumulated. */
+  /* optional densification statistics of this view, fused into the backward preprocess (train.py:199-203,
+     gaussian_model.py:551-553), all [P], all NULL for reference behaviour: for every visible surfel
+     densify_grad_norm += ||dL_dmeans2D.xy||, densify_visible += 1, max_radii = max(max_radii, radii) */
+  float* densify_grad_norm;
+  float* densify_visible;
+  int* max_radii;
 } gsm_backward_args;
 
 size_t gsm_grad_workspace_bytes(int P);

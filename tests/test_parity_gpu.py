@@ -345,7 +345,8 @@ def test_factored_sh_gradient_matches_dense_path(P, deg):
             g = _backward_impl(bg, params_["means3D"], radii, e, params_["scales"], params_["rotations"], 1.0, e,
                                cam.world_view_transform.contiguous(), cam.full_proj_transform.contiguous(), cam.tanfovx,
                                cam.tanfovy, dc, da, params_["shs"], deg, cam.camera_center.contiguous(), geom, R, binning,
-                               image, False, out=bucket.views, accumulate=acc, rgb_out=rgb_out)
+                               image, False, out=bucket.views, accumulate=acc, rgb_out=rgb_out,
+                               stats=(bucket.stats[0], bucket.stats[1], bucket.max_radii) if rgb_out is not None else None)
             return g[0]
         return color, radii, allmap, backward
 
@@ -360,7 +361,8 @@ def test_factored_sh_gradient_matches_dense_path(P, deg):
         ex.dL_dsh.fill_(float("nan"))
         from gaussmart_b200.rasterizer import sh_grad_expand
         vp.view_parallel_step_factored(params, cams_d[:n_views], ex, lambda v, c, a: (cot[0].cuda(), cot[1].cuda()),
-                                       raster_fn=raster, expand_fn=sh_grad_expand, rank=0, world_size=1, sh_degree=deg)
+                                       raster_fn=raster, expand_fn=sh_grad_expand, rank=0, world_size=1, sh_degree=deg,
+                                       fused_stats=True)  # statistics accumulated by K6, dense path: torch ops
         g = ex.gradients()
         # (two separate backward runs: the gradient records are sums of unordered fp32 atomics, so equality is
         # up to that noise, as between two runs of the reference)

@@ -84,6 +84,7 @@ GeometryLayout geometry_layout(int P) {
   L.records = take(n * GSM_SURFEL_RECORD_BYTES);
   L.bbox = take(n * 8);
   L.cull = take(n * 16);
+  L.clamp = take(n);
   L.rects = take(n * 16);
   L.flags = take(16);
   L.total = off + 128;
@@ -206,7 +207,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     pp.means3D = a->means3D; pp.scales = a->scales; pp.rotations = a->rotations; pp.opacities = a->opacities;
     pp.shs = a->shs; pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;
     pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
-    pp.radii = a->radii; pp.records = records; pp.bbox = (short4*)(geom + G.bbox); pp.cull = (float4*)(geom + G.cull); pp.rects = (uint4*)(geom + G.rects); pp.tile_count = tile_count; pp.flags = flags;
+    pp.radii = a->radii; pp.records = records; pp.bbox = (short4*)(geom + G.bbox); pp.cull = (float4*)(geom + G.cull); pp.clamp = (uint8_t*)(geom + G.clamp); pp.rects = (uint4*)(geom + G.rects); pp.tile_count = tile_count; pp.flags = flags;
     { StageMark m(GSM_STAGE_PREPROCESS_FWD, stream); launch_preprocess_fwd(pp, stream); }
     GSM_STAGE("forward preprocess");
     {
@@ -324,7 +325,7 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   pp.means3D = a->means3D; pp.scales = a->scales; pp.rotations = a->rotations; pp.shs = a->shs;
   pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;
   pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
-  pp.radii = a->radii; pp.records = rp.records; pp.grad_records = grad_records;
+  pp.radii = a->radii; pp.records = rp.records; pp.clamp = (const uint8_t*)(geom + G.clamp); pp.grad_records = grad_records;
   pp.dL_dmeans2D = a->dL_dmeans2D; pp.dL_dcolors = a->dL_dcolors; pp.dL_dopacity = a->dL_dopacity;
   pp.dL_dmeans3D = a->dL_dmeans3D; pp.dL_dtransMat = a->dL_dtransMat; pp.dL_dsh = a->dL_dsh;
   pp.dL_dscales = a->dL_dscales; pp.dL_drotations = a->dL_drotations; pp.dL_drgb = a->dL_drgb;

@@ -87,6 +87,7 @@ struct GeometryLayout {
   size_t records;        // float4[P*5]
   size_t bbox;           // short4[P]  conservative integer pixel box of possible contribution
   size_t cull;           // float4[P]  diagonal slabs of the contribution region ("cull record")
+  size_t clamp;          // u8[P]      bit c set when colour channel c was clamped at 0 (read by the backward preprocess)
   size_t rects;          // uint4[P]   (minx | miny<<16, maxx | maxy<<16, depth bits, 0): tile rect for the scatter
   size_t flags;          // u32[4]: [0] prefiltered-violation flag
   size_t total;
@@ -166,6 +167,7 @@ struct FwdPreprocessParams {
   float4* records;
   short4* bbox;
   float4* cull;
+  uint8_t* clamp;
   uint4* rects;
   uint32_t* tile_count;  // u32[Nt], zeroed by the caller: += 1 per (surfel, tile) instance
   uint32_t* flags;
@@ -230,6 +232,7 @@ struct BwdPreprocessParams {
   const float* campos;
   const int* radii;
   const float4* records;
+  const uint8_t* clamp;
   const float* grad_records;
   float* dL_dmeans2D;
   float* dL_dcolors;

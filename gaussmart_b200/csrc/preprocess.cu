@@ -111,19 +111,20 @@ constexpr int PFWD_THREADS = 128;
 __device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict__ g, int M, int rows,
                                              unsigned vis_mask, int lane) {
   const int rl = 3 * M, rs = rl + 1, total = rows * rl;
+  const unsigned rmagic = 0xffffffffu / (unsigned)rl + 1u;  // idx / rl == umulhi(idx, rmagic) for idx < 2^16 (one division per thread instead of one per element)
   if (rows == 32 && (reinterpret_cast<size_t>(g) & 15) == 0) {
     const float4* g4 = reinterpret_cast<const float4*>(g);
     for (int f = lane; f < total / 4; f += 32) {
-      const int e0 = 4 * f, r0 = e0 / rl, r3 = (e0 + 3) / rl;
+      const int e0 = 4 * f, r0 = (int)__umulhi((unsigned)e0, rmagic), r3 = (int)__umulhi((unsigned)(e0 + 3), rmagic);
       if (!((vis_mask >> r0) & 1u) && !((vis_mask >> r3) & 1u)) continue;
       const float4 v = __ldg(g4 + f);
       const float vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-      for (int e = 0; e < 4; e++) { const int i = e0 + e, r = i / rl; wsm[r * rs + (i - r * rl)] = vv[e]; }
+      for (int e = 0; e < 4; e++) { const int i = e0 + e, r = (int)__umulhi((unsigned)i, rmagic); wsm[r * rs + (i - r * rl)] = vv[e]; }
     }
   } else {
     for (int i = lane; i < total; i += 32) {
-      const int r = i / rl;
+      const int r = (int)__umulhi((unsigned)i, rmagic);
       if ((vis_mask >> r) & 1u) wsm[r * rs + (i - r * rl)] = __ldg(g + i);
     }
   }
@@ -157,6 +158,15 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
   const float px = __ldg(p.means3D + 3 * (size_t)idx + 0);
   const float py = __ldg(p.means3D + 3 * (size_t)idx + 1);
   const float pz = __ldg(p.means3D + 3 * (size_t)idx + 2);
+  // issued before the cull test so that they are in flight together with the position (28 B that a culled
+  // surfel would not have needed, against one dependent round trip to HBM less for the visible ones)
+  float2 sc_in = make_float2(0.f, 0.f);
+  float4 q_in = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.transMat_precomp == nullptr) {
+    sc_in = __ldg(reinterpret_cast<const float2*>(p.scales) + idx);
+    q_in = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+  }
+  const float opac_in = __ldg(p.opacities + idx);
 
   // p_view = [p 1] * V   (auxiliary.h:79-87), association: m12 + fma(z,m8, fma(x,m0, y*m4))
   const float vx = ADD(vm[12], FMA(pz, vm[8], FMA(px, vm[0], MUL(py, vm[4]))));
@@ -171,8 +181,8 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
     }
 
     if (p.transMat_precomp == nullptr) {
-      const float2 sc = __ldg(reinterpret_cast<const float2*>(p.scales) + idx);
-      const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+      const float2 sc = sc_in;
+      const float4 q = q_in;
       float3 L0, L1, L2;
       build_L(q, MUL(p.scale_modifier, sc.x), MUL(p.scale_modifier, sc.y), L0, L1, L2);
       // A = M^T * world2ndc, rows (L0,0), (L1,0), (p,1); columns c = 0..3 of projmatrix
@@ -237,7 +247,7 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
 
     // conservative contribution box (common.cuh, CULL_RHO); fp64 so that the cancellation in
     // centre^2 - <f,T^2> cannot shrink it
-    opac = __ldg(p.opacities + idx);
+    opac = opac_in;
     if (opac < ALPHA_MIN) {
       // alpha = opacity * exp(power) with power <= 0 never reaches 1/255 (forward.cu:385-392): empty box
       box = make_short4(32767, 32767, -32768, -32768);
@@ -312,6 +322,7 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
   if (!valid) return;
   if (visible) {
     p.bbox[idx] = box;
+    p.clamp[idx] = (uint8_t)clamp_bits;
     p.cull[idx] = diag;
     p.rects[idx] = make_uint4(rect_min, rect_max, __float_as_uint(vz), 0u);
     float4* rec = p.records + (size_t)idx * REC_F4;

@@ -123,19 +123,20 @@ constexpr int PBWD_THREADS = 128;
 __device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict__ g, int M, int rows,
                                              unsigned vis_mask, int lane) {
   const int rl = 3 * M, rs = rl + 1, total = rows * rl;
+  const unsigned rmagic = 0xffffffffu / (unsigned)rl + 1u;  // idx / rl == umulhi(idx, rmagic) for idx < 2^16 (one division per thread instead of one per element)
   if (rows == 32 && (reinterpret_cast<size_t>(g) & 15) == 0) {
     const float4* g4 = reinterpret_cast<const float4*>(g);
     for (int f = lane; f < total / 4; f += 32) {
-      const int e0 = 4 * f, r0 = e0 / rl, r3 = (e0 + 3) / rl;
+      const int e0 = 4 * f, r0 = (int)__umulhi((unsigned)e0, rmagic), r3 = (int)__umulhi((unsigned)(e0 + 3), rmagic);
       if (!((vis_mask >> r0) & 1u) && !((vis_mask >> r3) & 1u)) continue;
       const float4 v = __ldg(g4 + f);
       const float vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-      for (int e = 0; e < 4; e++) { const int idx = e0 + e, r = idx / rl; wsm[r * rs + (idx - r * rl)] = vv[e]; }
+      for (int e = 0; e < 4; e++) { const int idx = e0 + e, r = (int)__umulhi((unsigned)idx, rmagic); wsm[r * rs + (idx - r * rl)] = vv[e]; }
     }
   } else {
     for (int idx = lane; idx < total; idx += 32) {
-      const int r = idx / rl;
+      const int r = (int)__umulhi((unsigned)idx, rmagic);
       if ((vis_mask >> r) & 1u) wsm[r * rs + (idx - r * rl)] = __ldg(g + idx);
     }
   }
@@ -144,6 +145,7 @@ __device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict
 __device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restrict__ g, int M, int rows,
                                               unsigned vis_mask, bool acc, int lane) {
   const int rl = 3 * M, rs = rl + 1, total = rows * rl;
+  const unsigned rmagic = 0xffffffffu / (unsigned)rl + 1u;  // idx / rl == umulhi(idx, rmagic) for idx < 2^16 (one division per thread instead of one per element)
   if (rows == 32 && (reinterpret_cast<size_t>(g) & 15) == 0) {
     float4* g4 = reinterpret_cast<float4*>(g);
     for (int f = lane; f < total / 4; f += 32) {
@@ -152,7 +154,7 @@ __device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restric
       bool any = false;
 #pragma unroll
       for (int e = 0; e < 4; e++) {
-        const int idx = e0 + e, r = idx / rl;
+        const int idx = e0 + e, r = (int)__umulhi((unsigned)idx, rmagic);
         const bool vis = (vis_mask >> r) & 1u;
         vv[e] = vis ? wsm[r * rs + (idx - r * rl)] : 0.0f;
         any |= vis;
@@ -167,7 +169,7 @@ __device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restric
     }
   } else {
     for (int idx = lane; idx < total; idx += 32) {
-      const int r = idx / rl;
+      const int r = (int)__umulhi((unsigned)idx, rmagic);
       const bool vis = (vis_mask >> r) & 1u;
       const float v = vis ? wsm[r * rs + (idx - r * rl)] : 0.0f;
       if (acc) { if (vis) g[idx] += v; }
@@ -176,7 +178,10 @@ __device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restric
   }
 }
 
-__global__ void __launch_bounds__(PBWD_THREADS) preprocess_bwd_kernel(const BwdPreprocessParams p) {
+#ifndef GSM_PBWD_MIN_CTAS
+#define GSM_PBWD_MIN_CTAS 6
+#endif
+__global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bwd_kernel(const BwdPreprocessParams p) {
   extern __shared__ float sh_smem[];
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -224,8 +229,11 @@ __global__ void __launch_bounds__(PBWD_THREADS) preprocess_bwd_kernel(const BwdP
     const float* vm = p.viewmatrix;
     const float* pm = p.projmatrix;
     const f3 pos = mk(__ldg(p.means3D + 3 * i), __ldg(p.means3D + 3 * i + 1), __ldg(p.means3D + 3 * i + 2));
-    const float4* rec = p.records + i * REC_F4;
-    const float depth = __ldg(&rec[2].z);  // transMats[idx*9+8] of the forward
+    // transMats[idx*9+8] of the forward (Tw.z): it depends on the position and the projection matrix only, so it
+    // is recomputed in the forward's association (preprocess.cu) instead of gathered from the 80-byte record
+    const float depth = p.scales == nullptr
+                            ? __ldg(p.transMat_precomp + 9 * i + 8)
+                            : __fadd_rn(pm[15], __fmaf_rn(pos.z, pm[11], __fmaf_rn(pos.x, pm[3], __fmul_rn(pos.y, pm[7]))));
 
     const bool precomp = (p.scales == nullptr);
     f3 T0, T1, T2;            // rows Tu, Tv, Tw
@@ -329,7 +337,7 @@ __global__ void __launch_bounds__(PBWD_THREADS) preprocess_bwd_kernel(const BwdP
     }
 
     if (has_sh) {
-      const int clamp_bits = __float_as_int(__ldg(&rec[4].w));
+      const int clamp_bits = (int)__ldg(p.clamp + i);
       f3 dRGB = dcolor;
       if (clamp_bits & 1) dRGB.x = 0.f;
       if (clamp_bits & 2) dRGB.y = 0.f;

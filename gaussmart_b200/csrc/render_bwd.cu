@@ -35,8 +35,12 @@ namespace gsm {
 #define GSM_BWD_WARPS 4
 #endif
 constexpr int BWD_WARPS = GSM_BWD_WARPS;
-constexpr int BWD_CHUNK = 32;
-constexpr int BWD_QUEUE = 128;
+#ifndef GSM_BWD_CHUNK
+#define GSM_BWD_CHUNK 32
+#endif
+constexpr int BWD_CHUNK = GSM_BWD_CHUNK;  // entries per stage (<= 32)
+constexpr int BWD_QUEUE = 64;             // position queue (power of two, >= BWD_CHUNK + 32)
+static_assert(BWD_CHUNK <= 32 && BWD_CHUNK + 32 <= BWD_QUEUE, "queue too small");
 
 constexpr int BWD_RING = 8;  // quarter-warp slots of the deferred-pair ring (a push adds <= 4, a pass retires 4)
 
@@ -155,7 +159,7 @@ __device__ __forceinline__ void geometry_pass(BwdWarpSmem& sm, int s, int head, 
 }
 
 #ifndef GSM_BWD_MIN_CTAS
-#define GSM_BWD_MIN_CTAS 5
+#define GSM_BWD_MIN_CTAS 6
 #endif
 __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_kernel(const BwdRenderParams p) {
   __shared__ __align__(16) BwdWarpSmem smem_all[BWD_WARPS];

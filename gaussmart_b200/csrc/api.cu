@@ -262,7 +262,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     rp.ranges = ranges;
     rp.point_list = bin ? (const uint32_t*)(bin + B.point_list) : nullptr;
     rp.records = records; rp.background = a->background;
-    rp.strip_mask = bin ? (const uint8_t*)(bin + B.strip_mask) : nullptr;
+    rp.strip_mask = bin ? (uint8_t*)(bin + B.strip_mask) : nullptr;
     rp.bbox = (const short4*)(geom + G.bbox); rp.no_cull = (a->debug & 2) ? 1 : 0;
     rp.final_T = (float*)(img + I.final_T); rp.n_contrib = (uint32_t*)(img + I.n_contrib);
     rp.out_color = a->out_color; rp.out_others = a->out_others;

@@ -189,7 +189,7 @@ struct FwdRenderParams {
   const uint2* ranges;
   const uint32_t* point_list;
   const float4* records;
-  const uint8_t* strip_mask;
+  uint8_t* strip_mask;        // read, and refined: bits of (block, entry) pairs without a blended pixel are cleared
   const short4* bbox;         // per-surfel conservative contribution boxes
   int no_cull;                // evaluate every (pixel, entry) pair (debug bit 1)
   const float* background;

@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--P", type=int, default=None, help="override the surfel count (debug only; flagged in config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-knn", action="store_true")
     return ap.parse_args()
 
 
@@ -373,6 +374,31 @@ def cpu_baseline(full_entries_per_iter, deg):
                 sample_seconds=dt)
 
 
+def knn_leg(wl, impl, reps=3):
+    """distCUDA2 (the scale initialiser of the path, run once per training: C4 "incl. distCUDA2 init") on the
+    workload's 5 M points: one warm-up + `reps` timed calls, CUDA events; reported beside the iteration metric."""
+    pts = wl["params"]["means3D"].contiguous()
+    if impl == "reference":
+        import ref_loader
+        fn = ref_loader.load_knn().distCUDA2
+    else:
+        import gaussmart_b200 as gb
+        fn = gb.distCUDA2
+    fn(pts)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        out = fn(pts)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    P = pts.shape[0]
+    return {"ms": ms, "points": P, "points_per_s": P / (ms * 1e-3), "calls": reps,
+            "compulsory_gbs": 16.0 * P / (ms * 1e-3) / 1e9,   # 12 B in + 4 B out per point (SURVEY.md 8d)
+            "checksum": float(out.double().sum().item())}
+
+
 # ------------------------------------------------------------------------------------------------
 def main():
     args = parse()
@@ -496,6 +522,11 @@ def main():
                                           "it runs: on the same B200"}
         if e2e is None:
             line["e2e"] = {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+        if not args.no_knn:
+            try:
+                line["knn"] = knn_leg(wl, "reference", reps=1)
+            except Exception as ex:  # pragma: no cover
+                line["knn"] = {"error": repr(ex)[:200]}
         print(json.dumps(line))
         return 0
 
@@ -533,6 +564,8 @@ def main():
     kernels_per_stage = {"preprocess_fwd": 1, "tile_scan": 1, "scatter": 1, "tile_sort": 3,
                          "render_fwd": 1, "grad_zero": 0, "render_bwd": 1, "preprocess_bwd": 1, "sh_grad_expand": 1}
     line["gpu_launches"] = int(sum(kernels_per_stage.get(n, 0) * c for n, (_, c) in stages.items()))
+    if world == 1 and not args.no_knn:
+        line["knn"] = knn_leg(wl, "ours")
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(int(wc["E_bwd"]), wl["deg"])
     print(json.dumps(line))

@@ -114,6 +114,7 @@ BinningLayout binning_layout(size_t capacity, int width, int height) {
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 128); return o; };
   L.point_list = take(capacity * 4);
   L.strip_mask = take(capacity + 4);
+  L.pix_mask = take(capacity * 4 * STRIPS_PER_TILE);
   L.persistent = off;
   L.keys_sorted = take(capacity * 8);
   L.pairs = take(capacity * 8);
@@ -263,6 +264,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     rp.point_list = bin ? (const uint32_t*)(bin + B.point_list) : nullptr;
     rp.records = records; rp.background = a->background;
     rp.strip_mask = bin ? (uint8_t*)(bin + B.strip_mask) : nullptr;
+    rp.pix_mask = bin ? (uint32_t*)(bin + B.pix_mask) : nullptr; rp.pix_plane = a->binning_capacity;
     rp.bbox = (const short4*)(geom + G.bbox); rp.no_cull = (a->debug & 2) ? 1 : 0;
     rp.final_T = (float*)(img + I.final_T); rp.n_contrib = (uint32_t*)(img + I.n_contrib);
     rp.out_color = a->out_color; rp.out_others = a->out_others;
@@ -305,6 +307,7 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   rp.records = (const float4*)(geom + G.records);
   const BinningLayout B = binning_layout(a->binning_capacity, W, H);
   rp.strip_mask = bin ? (const uint8_t*)(bin + B.strip_mask) : nullptr;
+  rp.pix_mask = bin ? (const uint32_t*)(bin + B.pix_mask) : nullptr; rp.pix_plane = a->binning_capacity;
   rp.bbox = (const short4*)(geom + G.bbox); rp.no_cull = (a->debug & 2) ? 1 : 0;
   rp.background = a->background;
   rp.final_T = (const float*)(img + I.final_T);

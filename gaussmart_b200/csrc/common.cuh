@@ -108,6 +108,8 @@ ImageLayout image_layout(int width, int height);
 struct BinningLayout {
   size_t point_list;       // u32[cap]   depth-sorted surfel ids per tile   (kept for backward)
   size_t strip_mask;       // u8[cap]    per instance: which 32-pixel blocks of its tile it can touch (kept)
+  size_t pix_mask;         // u32[8][cap] per block plane and instance: the pixels of the block that blended the entry
+                           //            (written by the forward compositing, kept)
   size_t persistent;       // bytes from the start that must survive until backward
   size_t keys_sorted;      // u64[cap]   (tile << 32 | depth bits), the reference's sorted keys
   size_t pairs;            // uint2[cap] (depth bits, surfel) per tile segment, unsorted
@@ -190,6 +192,8 @@ struct FwdRenderParams {
   const uint32_t* point_list;
   const float4* records;
   uint8_t* strip_mask;        // read, and refined: bits of (block, entry) pairs without a blended pixel are cleared
+  uint32_t* pix_mask;         // out: [8][pix_plane] pixels of block b that blended list entry i, at [b * pix_plane + i]
+  size_t pix_plane;
   const short4* bbox;         // per-surfel conservative contribution boxes
   int no_cull;                // evaluate every (pixel, entry) pair (debug bit 1)
   const float* background;
@@ -207,6 +211,8 @@ struct BwdRenderParams {
   const uint32_t* point_list;
   const float4* records;
   const uint8_t* strip_mask;
+  const uint32_t* pix_mask;   // as left by the forward compositing
+  size_t pix_plane;
   const short4* bbox;
   int no_cull;
   const float* background;

@@ -42,16 +42,22 @@ constexpr int BWD_CHUNK = GSM_BWD_CHUNK;  // entries per stage (<= 32)
 constexpr int BWD_QUEUE = 64;             // position queue (power of two, >= BWD_CHUNK + 32)
 static_assert(BWD_CHUNK <= 32 && BWD_CHUNK + 32 <= BWD_QUEUE, "queue too small");
 
-constexpr int BWD_RING = 8;  // quarter-warp slots of the deferred-pair ring (a push adds <= 4, a pass retires 4)
+#ifndef GSM_BWD_SLOTS
+#define GSM_BWD_SLOTS 16
+#endif
+constexpr int BWD_SLOTS = GSM_BWD_SLOTS;  // quarter-warp slots of deferred pairs per batch of entries (>= 4: one entry takes <= 4)
+static_assert(BWD_SLOTS >= 4 && BWD_SLOTS % 4 == 0, "a batch must hold at least one entry");
 
 struct BwdWarpSmem {
   float4 q[2][REC_F4][BWD_CHUNK];
   uint32_t id[2][BWD_CHUNK];
-  uint32_t pos[2][BWD_CHUNK];  // 0-based list position k of the staged entry (the reference's `contributor`)
+  uint32_t pos[2][BWD_CHUNK];    // 0-based list position k of the staged entry (the reference's `contributor`)
+  uint32_t pmask[2][BWD_CHUNK];  // pixels of this block that blended the entry (from the forward pass)
   uint32_t queue[BWD_QUEUE];
-  float4 pend[BWD_RING][8];    // deferred pairs: (G*dL_dalpha, dL_dz, alpha*T, bits: pixel | 3d-branch << 5)
-  uint32_t qinfo[BWD_RING];    // per slot: stage entry j | pairs in the slot << 8
-  float4 pixc[2][32];          // per pixel: (dL_dpixel.rgb, dL_dnormal.x), (dL_dnormal.yz, -, -)
+  float4 pend[BWD_SLOTS][8];     // deferred pairs: (G*dL_dalpha, dL_dz, alpha*T, bits: pixel | 3d-branch << 5)
+  uint32_t qinfo[BWD_SLOTS];     // per slot: stage entry j | pairs in the slot << 8
+  uint32_t sbase[BWD_CHUNK];     // first slot of entry j (chunk-wide numbering)
+  float4 pixc[2][32];            // per pixel: (dL_dpixel.rgb, dL_dnormal.x), (dL_dnormal.yz, -, -)
 };
 
 // red.global.add.v2.f32: two adjacent floats in one L2 reduction request (8-byte aligned)
@@ -59,15 +65,15 @@ __device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
 }
 
-// Deferred geometric part of up to 4 entries at once: quarter-warp q works on ring slot head+q, lane i of
+// Deferred geometric part of up to 4 entries at once: quarter-warp q works on slot first+q (< nslots valid), lane i of
 // the quarter on the slot's i-th pair.  Recomputes the ray-splat intersection of the pair (MUFU
 // reciprocal: these values feed gradient terms only), forms the 18 partial gradients, reduces them
 // over the quarter's 8 lanes and adds them to the entry's gradient record.
-__device__ __forceinline__ void geometry_pass(BwdWarpSmem& sm, int s, int head, int nslots, int lane, int bx0, int by0,
+__device__ __forceinline__ void geometry_pass(BwdWarpSmem& sm, int s, int first, int nslots, int lane, int bx0, int by0,
                                               float* __restrict__ grad_records) {
   const unsigned FULL = 0xffffffffu;
   const int qtr = lane >> 3, i = lane & 7;
-  const int slot = (head + qtr) & (BWD_RING - 1);
+  const int slot = min(first + qtr, BWD_SLOTS - 1);
   const uint32_t qf = sm.qinfo[slot];
   const int j = (int)(qf & 31u);
   const bool slot_valid = qtr < nslots;
@@ -155,7 +161,6 @@ __device__ __forceinline__ void geometry_pass(BwdWarpSmem& sm, int s, int head, 
     if (i == 0) atomicAdd(g + 16, e0);
     else if (i == 4) atomicAdd(g + 17, e0);
   }
-  __syncwarp();  // the slots may be refilled by the next push
 }
 
 #ifndef GSM_BWD_MIN_CTAS
@@ -205,9 +210,7 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
   sm.pixc[0][lane] = make_float4(dL_dpixel[0], dL_dpixel[1], dL_dpixel[2], dL_dnormal2D[0]);
   sm.pixc[1][lane] = make_float4(dL_dnormal2D[1], dL_dnormal2D[2], 0.f, 0.f);
   const int bx0 = (int)pixx - (lane % BLOCK_W), by0 = (int)pixy - (lane / BLOCK_W);  // block origin
-  int ring_head = 0, ring_fill = 0;  // warp-uniform
-
-  // deepest contributor of the warp: entries at or beyond it are behind every pixel of the strip
+  // deepest contributor of the warp: entries at or beyond it are behind every pixel of the block
   const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
 
   float T = T_final;
@@ -216,6 +219,8 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
   float accum_depth_rec = 0.f, accum_alpha_rec = 0.f, accum_normal_rec[3] = {0.f, 0.f, 0.f};
   float last_dL_dT = 0.f;
   const float far_ratio = __uint_as_float(GSM_FAR_RATIO_BITS);
+  const unsigned FULL = 0xffffffffu;
+  const uint32_t* __restrict__ pix_plane = p.pix_mask + (size_t)strip * p.pix_plane;
 
   // ---- scan / queue / stage machinery (warp-uniform state); list offsets run DOWN from warp_last-1 ----
   int scan = warp_last - 1;  // next 0-based list offset to scan (descending); < 0 => exhausted
@@ -224,7 +229,7 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
     while (qcount < BWD_CHUNK && scan >= 0) {
       const int o = scan - lane;
       const bool hit = o >= 0 && (__ldg(p.strip_mask + range.x + o) & strip_bit);
-      const unsigned m = __ballot_sync(0xffffffffu, hit);
+      const unsigned m = __ballot_sync(FULL, hit);
       if (hit) sm.queue[(qhead + qcount + __popc(m & ((1u << lane) - 1u))) & (BWD_QUEUE - 1)] = (uint32_t)o;
       qcount += __popc(m);
       scan -= 32;
@@ -238,6 +243,7 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
       sm.pos[s][lane] = o;
       const uint32_t id = __ldg(p.point_list + range.x + o);
       sm.id[s][lane] = id;
+      sm.pmask[s][lane] = __ldg(pix_plane + range.x + o);
       const float4* src = p.records + (size_t)id * REC_F4;
 #pragma unroll
       for (int f = 0; f < REC_F4; f++) __pipeline_memcpy_async(&sm.q[s][f][lane], src + f, sizeof(float4));
@@ -256,35 +262,60 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
     const int n_next = issue(s ^ 1);
     __pipeline_wait_prior(1);
     __syncwarp();
-    for (int j = 0; j < n_cur; j++) {
-      const int k = (int)sm.pos[s][j];  // == the reference's `contributor` after its decrement
-      bool active = k < last_contributor;
-      const float4 a = sm.q[s][0][j], b = sm.q[s][1][j], c = sm.q[s][2][j];
-      const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
-      const float lx = FMA(pyf, c.x, -b.x), ly = FMA(pyf, c.y, -b.y), lz = FMA(pyf, c.z, -b.z);
-      const float ppx = FMA(ky, lz, -MUL(kz, ly));
-      const float ppy = FMA(kz, lx, -MUL(kx, lz));
-      const float ppz = FMA(kx, ly, -MUL(ky, lx));
-      active = active && (ppz != 0.0f);
-      const float sx = __fdiv_rn(ppx, ppz), sy = __fdiv_rn(ppy, ppz);
-      const float rho3d = FMA(sx, sx, MUL(sy, sy));
-      const float dx = SUB(a.w, pxf), dy = SUB(b.w, pyf);
-      const float r2 = FMA(dy, dy, MUL(dx, dx));
-      const float rho2d = ADD(r2, r2);
-      const float rho = fminf(rho3d, rho2d);
-      const float c_d = ADD(c.z, FMA(c.x, sx, MUL(c.y, sy)));
-      active = active && !(c_d < NEAR_N);
-      const float power = MUL(rho, -0.5f);
-      active = active && !(power > 0.0f);
-      const float G = expf(power);
-      const float alpha = fminf(MUL(c.w, G), ALPHA_MAX);
-      active = active && !(alpha < ALPHA_MIN);
-      const unsigned am = __ballot_sync(0xffffffffu, active);
-      if (am == 0u) continue;
 
-      // ---- sequential part of the pair, in the pixel's lane ----
-      float e1 = 0.f, dL_dz = 0.f, w = 0.f;
-      if (active) {
+    // ---- the chunk's pixel masks: lane j holds entry j's, every lane collects the entries of ITS pixel ----
+    const uint32_t emask = lane < n_cur ? sm.pmask[s][lane] : 0u;   // pixels that blended entry `lane`
+    uint32_t mine = 0;                                              // entries of the chunk that my pixel blended
+    for (int j = 0; j < n_cur; j++) mine |= ((sm.pmask[s][j] >> lane) & 1u) << j;
+    // slots: entry j takes ceil(popc/8) quarter-warp slots; exclusive prefix over the entries
+    const int cnt = __popc(emask), nq = (cnt + 7) >> 3;
+    int incl = nq;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(FULL, incl, o);
+      if (lane >= o) incl += v;
+    }
+    const int excl = incl - nq;
+    if (lane < n_cur) sm.sbase[lane] = (uint32_t)excl;
+    __syncwarp();
+
+    // ---- batches of consecutive entries whose slots fit the pending buffer ----
+    int jb = 0;
+    while (jb < n_cur) {
+      const int base = __shfl_sync(FULL, excl, jb);
+      const unsigned fits = __ballot_sync(FULL, lane >= jb && lane < n_cur && incl - base <= BWD_SLOTS);
+      // entries jb .. je-1 (contiguous run of `fits` from jb; at least one, an entry takes <= 4 slots)
+      const unsigned run = ~(fits >> jb);
+      const int je = jb + (run ? __ffs(run) - 1 : 32 - jb);
+      const int nslots = __shfl_sync(FULL, incl, je - 1) - base;
+      if (lane >= jb && lane < je) {
+        for (int t = 0; t < nq; t++) sm.qinfo[excl - base + t] = (uint32_t)lane | ((uint32_t)min(8, cnt - 8 * t) << 8);
+      }
+
+      // ---- sequential part: every lane walks its own pixel's entries of the batch, back to front ----
+      uint32_t todo = mine & (je >= 32 ? FULL : ((1u << je) - 1u)) & ~((1u << jb) - 1u);
+      while (todo) {
+        const int j = __ffs(todo) - 1;
+        todo &= todo - 1u;
+        const int k = (int)sm.pos[s][j];  // == the reference's `contributor` after its decrement
+        const float4 a = sm.q[s][0][j], b = sm.q[s][1][j], c = sm.q[s][2][j];
+        const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
+        const float lx = FMA(pyf, c.x, -b.x), ly = FMA(pyf, c.y, -b.y), lz = FMA(pyf, c.z, -b.z);
+        const float ppx = FMA(ky, lz, -MUL(kz, ly));
+        const float ppy = FMA(kz, lx, -MUL(kx, lz));
+        const float ppz = FMA(kx, ly, -MUL(ky, lx));
+        const float sx = __fdiv_rn(ppx, ppz), sy = __fdiv_rn(ppy, ppz);
+        const float rho3d = FMA(sx, sx, MUL(sy, sy));
+        const float dx = SUB(a.w, pxf), dy = SUB(b.w, pyf);
+        const float r2 = FMA(dy, dy, MUL(dx, dx));
+        const float rho2d = ADD(r2, r2);
+        const float rho = fminf(rho3d, rho2d);
+        const float c_d = ADD(c.z, FMA(c.x, sx, MUL(c.y, sy)));
+        const float power = MUL(rho, -0.5f);
+        const float G = expf(power);
+        const float alpha = fminf(MUL(c.w, G), ALPHA_MAX);
+        // (the forward blended this pair, so every test of backward.cu:283-316 passes: same expressions, same bits)
+
         const float4 nrm = sm.q[s][3][j], col = sm.q[s][4][j];
         const float normal[3] = {nrm.x, nrm.y, nrm.z};
         const float color[3] = {col.x, col.y, col.z};
@@ -293,8 +324,8 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
         // and use the 2-ulp MUFU reciprocal instead of the reference's 8 div.rn per pair.
         const float one_m_alpha = SUB(1.0f, alpha);
         T = __fdiv_rn(T, one_m_alpha);
-        w = alpha * T;
-        float dL_dalpha = 0.0f;
+        const float w = alpha * T;
+        float dL_dalpha = 0.0f, dL_dz = 0.0f;
 #pragma unroll
         for (int ch = 0; ch < 3; ch++) {
           accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
@@ -326,31 +357,20 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
         last_alpha = alpha;
         dL_dalpha += (-T_final * __fdividef(1.0f, one_m_alpha)) * bg_dot_dpixel;
         dL_dz += w * dL_ddepth;
-        e1 = G * dL_dalpha;  // dL_dopacity of the pair; dL_dG * G = opacity * e1
-      }
+        const float e1 = G * dL_dalpha;  // dL_dopacity of the pair; dL_dG * G = opacity * e1
 
-      // ---- push the active pairs: the entry takes ceil(c/8) quarter-warp slots of the ring ----
-      {
-        const int c = __popc(am), nq = (c + 7) >> 3;
-        const int rank = __popc(am & ((1u << lane) - 1u));
-        if (active)
-          sm.pend[(ring_head + ring_fill + (rank >> 3)) & (BWD_RING - 1)][rank & 7] =
-              make_float4(e1, dL_dz, w, __uint_as_float((uint32_t)lane | (rho3d <= rho2d ? 32u : 0u)));
-        if (lane < nq)
-          sm.qinfo[(ring_head + ring_fill + lane) & (BWD_RING - 1)] = (uint32_t)j | ((uint32_t)min(8, c - 8 * lane) << 8);
-        ring_fill += nq;
-        __syncwarp();
+        // my place among the entry's pairs: slot of the entry + rank of my pixel in its mask
+        const uint32_t em = sm.pmask[s][j];
+        const int rank = __popc(em & ((1u << lane) - 1u));
+        const int slot = (int)sm.sbase[j] - base + (rank >> 3);
+        sm.pend[slot][rank & 7] =
+            make_float4(e1, dL_dz, w, __uint_as_float((uint32_t)lane | (rho3d <= rho2d ? 32u : 0u)));
       }
-      while (ring_fill >= 4) {
-        geometry_pass(sm, s, ring_head, 4, lane, bx0, by0, p.grad_records);
-        ring_head = (ring_head + 4) & (BWD_RING - 1);
-        ring_fill -= 4;
-      }
-    }
-    if (ring_fill > 0) {  // the staged records are recycled after this chunk: retire what is pending
-      geometry_pass(sm, s, ring_head, ring_fill, lane, bx0, by0, p.grad_records);
-      ring_head = 0;
-      ring_fill = 0;
+      __syncwarp();
+      for (int first = 0; first < nslots; first += 4)
+        geometry_pass(sm, s, first, min(4, nslots - first), lane, bx0, by0, p.grad_records);
+      __syncwarp();  // the slots are refilled by the next batch
+      jb = je;
     }
     __syncwarp();
     n_cur = n_next;

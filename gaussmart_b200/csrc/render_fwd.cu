@@ -162,16 +162,25 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
       hit_entries |= 1u << j;
       if (STATS) n_contributing++;
     }
-    // Refine the block masks for the backward pass: an entry that no pixel of this block blended is a no-op
-    // there too (its activity test is this kernel's contribution test, bit for bit, and pixels that stopped
-    // earlier are excluded by their last contributor), so this block's bit of the entry's mask is cleared and
-    // the backward never queues it -- 57 % of the queued (block, entry) pairs at C4.  Only this warp reads
-    // this bit, and it is past these entries.
+    // Hand the backward pass what this pass found out.  The backward's activity test of a pair is this kernel's
+    // contribution test, bit for bit (pixels that stopped earlier are excluded by their last contributor), so
+    //  * an entry that no pixel of this block blended is a no-op there too: this block's bit of the entry's mask
+    //    is cleared and the backward never queues it (57 % of the queued (block, entry) pairs at C4);
+    //  * for the others the 32-bit set of blending pixels is stored (pix_mask[block][entry]): the backward walks,
+    //    per pixel, exactly its own contributors.
+    // Only this warp reads this bit / writes this word, and it is past these entries.
     {
       const uint32_t any_hit = __reduce_or_sync(0xffffffffu, hit_entries);
-      if (lane < n_cur && !((any_hit >> lane) & 1u)) {
+      uint32_t my_mask = 0;  // lane j: the pixels that blended entry j (32x32 bit transpose, hit entries only)
+      for (uint32_t rest = any_hit; rest; rest &= rest - 1u) {
+        const int j = __ffs(rest) - 1;
+        const uint32_t b = __ballot_sync(0xffffffffu, (hit_entries >> j) & 1u);
+        if (lane == j) my_mask = b;
+      }
+      if (lane < n_cur) {
         const size_t at = (size_t)range.x + qpos[lane] - 1u;
-        atomicAnd(reinterpret_cast<unsigned int*>(p.strip_mask + (at & ~(size_t)3)), ~(strip_bit << (8u * (unsigned)(at & 3))));
+        if (my_mask) p.pix_mask[(size_t)strip * p.pix_plane + at] = my_mask;
+        else atomicAnd(reinterpret_cast<unsigned int*>(p.strip_mask + (at & ~(size_t)3)), ~(strip_bit << (8u * (unsigned)(at & 3))));
       }
     }
     if (all_done) break;

@@ -233,11 +233,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.raster_settings = raster_settings
         ctx.num_rendered = num_rendered
         ctx.opacity_shape = opacities.shape
-        # only the depth-sorted surfel list (first 4*R bytes) of the binning workspace is needed by
-        # backward; keep a compact copy so the transient sort scratch returns to the allocator now
+        # backward needs the persistent prefix of the binning workspace (surfel list, block masks, per-entry pixel
+        # masks: 37 of its 53 bytes per instance); the buffer is kept whole rather than copied
         ctx.binning_capacity = binningBuffer.gsm_capacity
-        keep = _lib.load().gsm_binning_persistent_bytes(ctx.binning_capacity)
-        point_list = binningBuffer[:keep].clone() if num_rendered > 0 else binningBuffer[:0]
+        point_list = binningBuffer
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
                               point_list, imgBuffer)
         ctx.mark_non_differentiable(radii)

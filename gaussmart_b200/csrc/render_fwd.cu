@@ -39,6 +39,7 @@ struct FwdWarpSmem {
   float4 q[2][REC_F4][FWD_CHUNK];  // [stage][field][entry]  5 KB
   uint32_t pos[2][FWD_CHUNK];      // 1-based position of the staged entry in the tile list
   uint32_t queue[FWD_QUEUE];
+  uint32_t hit[FWD_CHUNK];         // per staged entry: the pixels of the block that blended it
 };
 
 template <bool STATS>
@@ -115,7 +116,8 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
     const float4* __restrict__ q4 = sm.q[s][4];
     const uint32_t* __restrict__ qpos = sm.pos[s];
     bool all_done = false;
-    uint32_t hit_entries = 0;  // bit j: this pixel blended entry j of the chunk
+    sm.hit[lane] = 0u;
+    __syncwarp();
     for (int j = 0; j < n_cur; j++) {
       if (__all_sync(0xffffffffu, done)) { all_done = true; break; }
       if (done) continue;
@@ -159,7 +161,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
       C0 = FMA(w, col.x, C0); C1 = FMA(w, col.y, C1); C2 = FMA(w, col.z, C2);
       T = test_T;
       last_contributor = contributor;
-      hit_entries |= 1u << j;
+      atomicOr(&sm.hit[j], 1u << lane);
       if (STATS) n_contributing++;
     }
     // Hand the backward pass what this pass found out.  The backward's activity test of a pair is this kernel's
@@ -170,13 +172,8 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
     //    per pixel, exactly its own contributors.
     // Only this warp reads this bit / writes this word, and it is past these entries.
     {
-      const uint32_t any_hit = __reduce_or_sync(0xffffffffu, hit_entries);
-      uint32_t my_mask = 0;  // lane j: the pixels that blended entry j (32x32 bit transpose, hit entries only)
-      for (uint32_t rest = any_hit; rest; rest &= rest - 1u) {
-        const int j = __ffs(rest) - 1;
-        const uint32_t b = __ballot_sync(0xffffffffu, (hit_entries >> j) & 1u);
-        if (lane == j) my_mask = b;
-      }
+      __syncwarp();
+      const uint32_t my_mask = sm.hit[lane];  // lane j: the pixels that blended entry j
       if (lane < n_cur) {
         const size_t at = (size_t)range.x + qpos[lane] - 1u;
         if (my_mask) p.pix_mask[(size_t)strip * p.pix_plane + at] = my_mask;

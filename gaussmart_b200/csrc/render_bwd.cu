@@ -43,10 +43,12 @@ constexpr int BWD_QUEUE = 64;             // position queue (power of two, >= BW
 static_assert(BWD_CHUNK <= 32 && BWD_CHUNK + 32 <= BWD_QUEUE, "queue too small");
 
 #ifndef GSM_BWD_SLOTS
-#define GSM_BWD_SLOTS 16
+#define GSM_BWD_SLOTS 32
 #endif
-constexpr int BWD_SLOTS = GSM_BWD_SLOTS;  // quarter-warp slots of deferred pairs per batch of entries (>= 4: one entry takes <= 4)
-static_assert(BWD_SLOTS >= 4 && BWD_SLOTS % 4 == 0, "a batch must hold at least one entry");
+constexpr int SLOT_W = 4;                      // lanes (pairs) per slot: an entry takes ceil(pairs / 4) slots
+constexpr int SLOTS_PER_PASS = 32 / SLOT_W;    // 8 entries-slots retired per warp pass
+constexpr int BWD_SLOTS = GSM_BWD_SLOTS;       // slots of deferred pairs per batch of entries (one entry takes <= 8)
+static_assert(BWD_SLOTS >= 32 / SLOT_W && BWD_SLOTS % SLOTS_PER_PASS == 0, "a batch must hold at least one entry");
 
 struct BwdWarpSmem {
   float4 q[2][REC_F4][BWD_CHUNK];
@@ -54,7 +56,7 @@ struct BwdWarpSmem {
   uint32_t pos[2][BWD_CHUNK];    // 0-based list position k of the staged entry (the reference's `contributor`)
   uint32_t pmask[2][BWD_CHUNK];  // pixels of this block that blended the entry (from the forward pass)
   uint32_t queue[BWD_QUEUE];
-  float4 pend[BWD_SLOTS][8];     // deferred pairs: (G*dL_dalpha, dL_dz, alpha*T, bits: pixel | 3d-branch << 5)
+  float4 pend[BWD_SLOTS][SLOT_W];  // deferred pairs: (G*dL_dalpha, dL_dz, alpha*T, bits: pixel | 3d-branch << 5)
   uint32_t qinfo[BWD_SLOTS];     // per slot: stage entry j | pairs in the slot << 8
   uint32_t sbase[BWD_CHUNK];     // first slot of entry j (chunk-wide numbering)
   float4 pixc[2][32];            // per pixel: (dL_dpixel.rgb, dL_dnormal.x), (dL_dnormal.yz, -, -)
@@ -64,15 +66,19 @@ struct BwdWarpSmem {
 __device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
 }
+// red.global.add.v4.f32: four adjacent floats (16-byte aligned)
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 
-// Deferred geometric part of up to 4 entries at once: quarter-warp q works on slot first+q (< nslots valid), lane i of
-// the quarter on the slot's i-th pair.  Recomputes the ray-splat intersection of the pair (MUFU
+// Deferred geometric part of up to 8 entries at once: lanes 4q..4q+3 work on slot first+q (< nslots valid), lane i of
+// the four on the slot's i-th pair.  Recomputes the ray-splat intersection of the pair (MUFU
 // reciprocal: these values feed gradient terms only), forms the 18 partial gradients, reduces them
-// over the quarter's 8 lanes and adds them to the entry's gradient record.
+// over the slot's 4 lanes and adds them to the entry's gradient record (one red.global.add.v4.f32 per lane).
 __device__ __forceinline__ void geometry_pass(BwdWarpSmem& sm, int s, int first, int nslots, int lane, int bx0, int by0,
                                               float* __restrict__ grad_records) {
   const unsigned FULL = 0xffffffffu;
-  const int qtr = lane >> 3, i = lane & 7;
+  const int qtr = lane / SLOT_W, i = lane % SLOT_W;
   const int slot = min(first + qtr, BWD_SLOTS - 1);
   const uint32_t qf = sm.qinfo[slot];
   const int j = (int)(qf & 31u);
@@ -122,44 +128,34 @@ __device__ __forceinline__ void geometry_pass(BwdWarpSmem& sm, int s, int first,
       v[8] = dL_dz;
     }
   }
-  // recursive halving over the quarter's 8 lanes: lane i ends with the sums of slots 2i and 2i+1
+  // recursive halving over the slot's 4 lanes: lane i ends with the sums of values 4i .. 4i+3
   {
-    const bool up = lane & 4;
+    const bool up = lane & 2;
 #pragma unroll
     for (int z = 0; z < 8; z++) {
       const float send = up ? v[z] : v[z + 8];
       const float keep = up ? v[z + 8] : v[z];
-      v[z] = keep + __shfl_xor_sync(FULL, send, 4);
+      v[z] = keep + __shfl_xor_sync(FULL, send, 2);
     }
     const float send = up ? e0 : e1;
     const float keep = up ? e1 : e0;
-    e0 = keep + __shfl_xor_sync(FULL, send, 4);  // lanes 0-3 of the quarter: slot 16, lanes 4-7: slot 17
-  }
-  {
-    const bool up = lane & 2;
-#pragma unroll
-    for (int z = 0; z < 4; z++) {
-      const float send = up ? v[z] : v[z + 4];
-      const float keep = up ? v[z + 4] : v[z];
-      v[z] = keep + __shfl_xor_sync(FULL, send, 2);
-    }
-    e0 += __shfl_xor_sync(FULL, e0, 2);
+    e0 = keep + __shfl_xor_sync(FULL, send, 2);  // lanes 0-1 of the slot: value 16, lanes 2-3: value 17
   }
   {
     const bool up = lane & 1;
 #pragma unroll
-    for (int z = 0; z < 2; z++) {
-      const float send = up ? v[z] : v[z + 2];
-      const float keep = up ? v[z + 2] : v[z];
+    for (int z = 0; z < 4; z++) {
+      const float send = up ? v[z] : v[z + 4];
+      const float keep = up ? v[z + 4] : v[z];
       v[z] = keep + __shfl_xor_sync(FULL, send, 1);
     }
     e0 += __shfl_xor_sync(FULL, e0, 1);
   }
+  const float e17 = __shfl_down_sync(FULL, e0, 2);  // lane 0 of the slot fetches value 17 from lane 2
   if (slot_valid) {
     float* g = grad_records + (size_t)sm.id[s][j] * GREC;
-    red_add_v2(g + 2 * i, v[0], v[1]);
-    if (i == 0) atomicAdd(g + 16, e0);
-    else if (i == 4) atomicAdd(g + 17, e0);
+    red_add_v4(g + 4 * i, v[0], v[1], v[2], v[3]);
+    if (i == 0) red_add_v2(g + 16, e0, e17);
   }
 }
 
@@ -268,7 +264,7 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
     uint32_t mine = 0;                                              // entries of the chunk that my pixel blended
     for (int j = 0; j < n_cur; j++) mine |= ((sm.pmask[s][j] >> lane) & 1u) << j;
     // slots: entry j takes ceil(popc/8) quarter-warp slots; exclusive prefix over the entries
-    const int cnt = __popc(emask), nq = (cnt + 7) >> 3;
+    const int cnt = __popc(emask), nq = (cnt + SLOT_W - 1) / SLOT_W;
     int incl = nq;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -289,7 +285,7 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
       const int je = jb + (run ? __ffs(run) - 1 : 32 - jb);
       const int nslots = __shfl_sync(FULL, incl, je - 1) - base;
       if (lane >= jb && lane < je) {
-        for (int t = 0; t < nq; t++) sm.qinfo[excl - base + t] = (uint32_t)lane | ((uint32_t)min(8, cnt - 8 * t) << 8);
+        for (int t = 0; t < nq; t++) sm.qinfo[excl - base + t] = (uint32_t)lane | ((uint32_t)min(SLOT_W, cnt - SLOT_W * t) << 8);
       }
 
       // ---- sequential part: every lane walks its own pixel's entries of the batch, back to front ----
@@ -362,13 +358,13 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
         // my place among the entry's pairs: slot of the entry + rank of my pixel in its mask
         const uint32_t em = sm.pmask[s][j];
         const int rank = __popc(em & ((1u << lane) - 1u));
-        const int slot = (int)sm.sbase[j] - base + (rank >> 3);
-        sm.pend[slot][rank & 7] =
+        const int slot = (int)sm.sbase[j] - base + rank / SLOT_W;
+        sm.pend[slot][rank % SLOT_W] =
             make_float4(e1, dL_dz, w, __uint_as_float((uint32_t)lane | (rho3d <= rho2d ? 32u : 0u)));
       }
       __syncwarp();
-      for (int first = 0; first < nslots; first += 4)
-        geometry_pass(sm, s, first, min(4, nslots - first), lane, bx0, by0, p.grad_records);
+      for (int first = 0; first < nslots; first += SLOTS_PER_PASS)
+        geometry_pass(sm, s, first, min(SLOTS_PER_PASS, nslots - first), lane, bx0, by0, p.grad_records);
       __syncwarp();  // the slots are refilled by the next batch
       jb = je;
     }

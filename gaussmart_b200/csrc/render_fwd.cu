@@ -40,6 +40,7 @@ struct FwdWarpSmem {
   uint32_t pos[2][FWD_CHUNK];      // 1-based position of the staged entry in the tile list
   uint32_t queue[FWD_QUEUE];
   uint32_t hit[FWD_CHUNK];         // per staged entry: the pixels of the block that blended it
+  float cut[FWD_CHUNK];            // per staged entry: upper bound of rho for alpha >= 1/255 (pre-test below)
 };
 
 template <bool STATS>
@@ -117,6 +118,9 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
     const uint32_t* __restrict__ qpos = sm.pos[s];
     bool all_done = false;
     sm.hit[lane] = 0u;
+    // alpha = min(0.99, o exp(-rho/2)) >= 1/255 needs rho <= 2 ln(255 o); 0.1 % + 1e-3 covers every rounding of
+    // the exact evaluation below (expf, the products, the two divisions: a few ulp).  Negative for o < 1/255.
+    if (lane < n_cur) sm.cut[lane] = p.no_cull ? 3.0e38f : FMA(2.0f * __logf(255.0f * q2[lane].w), 1.001f, 1.0e-3f);
     __syncwarp();
     for (int j = 0; j < n_cur; j++) {
       if (__all_sync(0xffffffffu, done)) { all_done = true; break; }
@@ -131,12 +135,20 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
       const float ppx = FMA(ky, lz, -MUL(kz, ly));
       const float ppy = FMA(kz, lx, -MUL(kx, lz));
       const float ppz = FMA(kx, ly, -MUL(ky, lx));
-      if (ppz == 0.0f) continue;
-      const float sx = __fdiv_rn(ppx, ppz), sy = __fdiv_rn(ppy, ppz);
-      const float rho3d = FMA(sx, sx, MUL(sy, sy));
       const float dx = SUB(a.w, pxf), dy = SUB(b.w, pyf);
       const float r2 = FMA(dy, dy, MUL(dx, dx));
       const float rho2d = ADD(r2, r2);
+      {
+        // pre-test before the two IEEE divisions and the exponential: can this pixel reach alpha >= 1/255 at all?
+        // rho3d = (ppx^2 + ppy^2) / ppz^2, compared without dividing (NaNs pass).  More than half of the queued
+        // entries fail it for every pixel of the block (their box meets the block, their footprint does not), and
+        // then the warp skips the rest of the iteration.
+        const float cut = sm.cut[j];
+        if ((ppx * ppx + ppy * ppy) > cut * (ppz * ppz) && rho2d > cut) continue;
+      }
+      if (ppz == 0.0f) continue;
+      const float sx = __fdiv_rn(ppx, ppz), sy = __fdiv_rn(ppy, ppz);
+      const float rho3d = FMA(sx, sx, MUL(sy, sy));
       const float rho = fminf(rho3d, rho2d);
       const float depth = ADD(c.z, FMA(c.x, sx, MUL(c.y, sy)));
       if (depth < NEAR_N) continue;

@@ -445,13 +445,15 @@ def main():
 
     # ---- value: device-resident
     sampler = ClockSampler(local_rank)
-    # warm-up outside the sampler, then reset the stage timers so they cover the timed region only
-    for s in range(args.warmup):
+    # nvidia-smi takes ~0.2 s to start sampling and the timed region is only ~0.1 s at the default 20 steps: the
+    # sampler runs from before the warm-up (the same load) to the end of the timed region
+    sampler.start()
+    time.sleep(0.3)
+    for s in range(max(args.warmup, 3)):
         arm.value_step(view_of(s))
     barrier(world)
     if args.impl == "ours":
-        _lib.stage_timing_read(reset=True)
-    sampler.start()
+        _lib.stage_timing_read(reset=True)   # the stage timers cover the timed region only
     ms_total = timed_loop(lambda s: arm.value_step(view_of(s)), args.steps, 0, world, rank)
     clocks = sampler.stop()
     stages = _lib.stage_timing_read(reset=True) if args.impl == "ours" else {}

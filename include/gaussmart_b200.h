@@ -59,9 +59,11 @@ size_t gsm_geometry_bytes(int P);
  * Replaces ImageState::fromChunk (rasterizer_impl.cu:172-179). */
 size_t gsm_image_bytes(int width, int height);
 /* binning workspace for `capacity` (surfel,tile) instances.  Its first
- * gsm_binning_persistent_bytes(capacity) bytes (the depth-sorted surfel list u32[capacity] and the
- * per-instance strip masks u8[capacity]) must survive until backward -- a copy of that prefix is as
- * good as the original; the rest (keys, sort scratch) is transient.
+ * gsm_binning_persistent_bytes(capacity) bytes must survive until backward -- a copy of that prefix is as good
+ * as the original: the depth-sorted surfel list u32[capacity], the per-instance block masks u8[capacity]
+ * (written by the tile sort, REFINED by the forward compositing: bits of (block, entry) pairs without a blended
+ * pixel are cleared) and the per-entry pixel sets u32[8][capacity] (which pixels of block b blended list entry i,
+ * written by the forward compositing; gsm_backward walks them).  The rest (keys, sort scratch) is transient.
  * Replaces BinningState::fromChunk (rasterizer_impl.cu:181-194). */
 size_t gsm_binning_bytes(size_t capacity, int width, int height);
 size_t gsm_binning_persistent_bytes(size_t capacity);

@@ -114,13 +114,33 @@ __device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict
   const unsigned rmagic = 0xffffffffu / (unsigned)rl + 1u;  // idx / rl == umulhi(idx, rmagic) for idx < 2^16 (one division per thread instead of one per element)
   if (rows == 32 && (reinterpret_cast<size_t>(g) & 15) == 0) {
     const float4* g4 = reinterpret_cast<const float4*>(g);
-    for (int f = lane; f < total / 4; f += 32) {
-      const int e0 = 4 * f, r0 = (int)__umulhi((unsigned)e0, rmagic), r3 = (int)__umulhi((unsigned)(e0 + 3), rmagic);
-      if (!((vis_mask >> r0) & 1u) && !((vis_mask >> r3) & 1u)) continue;
-      const float4 v = __ldg(g4 + f);
-      const float vv[4] = {v.x, v.y, v.z, v.w};
+    // batches of 4 independent 128-bit loads per lane are issued before any of them is consumed: the row stream is
+    // 54 % of the kernel's read bytes and one load per loop iteration left the lanes waiting on HBM one at a time
+#ifndef GSM_ROW_LOADS
+#define GSM_ROW_LOADS 4
+#endif
+    constexpr int LOADS_IN_FLIGHT = GSM_ROW_LOADS;
+    for (int f0 = lane; f0 < total / 4; f0 += 32 * LOADS_IN_FLIGHT) {
+      float4 v[LOADS_IN_FLIGHT];
+      bool take[LOADS_IN_FLIGHT];
 #pragma unroll
-      for (int e = 0; e < 4; e++) { const int i = e0 + e, r = (int)__umulhi((unsigned)i, rmagic); wsm[r * rs + (i - r * rl)] = vv[e]; }
+      for (int u = 0; u < LOADS_IN_FLIGHT; u++) {
+        const int f = f0 + 32 * u, e0 = 4 * f;
+        const int r0 = (int)__umulhi((unsigned)e0, rmagic), r3 = (int)__umulhi((unsigned)(e0 + 3), rmagic);
+        take[u] = f < total / 4 && (((vis_mask >> r0) & 1u) || ((vis_mask >> r3) & 1u));
+        v[u] = take[u] ? __ldg(g4 + f) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < LOADS_IN_FLIGHT; u++) {
+        if (!take[u]) continue;
+        const int e0 = 4 * (f0 + 32 * u);
+        const float vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          const int i = e0 + e, r = (int)__umulhi((unsigned)i, rmagic);
+          wsm[r * rs + (i - r * rl)] = vv[e];
+        }
+      }
     }
   } else {
     for (int i = lane; i < total; i += 32) {

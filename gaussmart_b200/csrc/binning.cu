@@ -111,10 +111,21 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ r
   }
   const int BIG = 16;
   if (n > 0 && n <= BIG) {
-    for (int t = 0; t < n; t++) {
-      const uint32_t tile = (uint32_t)((miny + t / w) * grid_x + minx + t % w);
-      const uint32_t slot = atomicAdd(tile_cursor + tile * TILE_SUBS + ((uint32_t)idx & (TILE_SUBS - 1)), 1u);
-      pairs[slot] = make_uint2(depth_bits, (uint32_t)idx);
+    // the cursor atomics return a value: four are issued before the first result is consumed, instead of one
+    // L2 round trip per instance in sequence
+    for (int t0 = 0; t0 < n; t0 += 4) {
+      uint32_t slot[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int t = t0 + u;
+        if (t < n) {
+          const uint32_t tile = (uint32_t)((miny + t / w) * grid_x + minx + t % w);
+          slot[u] = atomicAdd(tile_cursor + tile * TILE_SUBS + ((uint32_t)idx & (TILE_SUBS - 1)), 1u);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (t0 + u < n) pairs[slot[u]] = make_uint2(depth_bits, (uint32_t)idx);
     }
   }
   unsigned big = __ballot_sync(0xffffffffu, n > BIG);

@@ -219,6 +219,14 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
   // receiver rebuilds as basis(dir) (x) dL_dRGB (sh_grad_expand_kernel); the SH term of dL_dmean3D stays here
   const bool factored = p.dL_drgb != nullptr;
   const bool has_sh = p.shs != nullptr && (p.dL_dsh != nullptr || factored);
+  // the thread's own operands are requested BEFORE the cooperative row staging, so both streams are in flight together
+  float4 g0 = make_float4(0, 0, 0, 0), g1 = g0, g2 = g0, g3 = g0, g4 = g0;
+  f3 pos = mk(0, 0, 0);
+  if (visible) {
+    const float4* g = reinterpret_cast<const float4*>(p.grad_records + i * GREC);
+    g0 = __ldg(g + 0); g1 = __ldg(g + 1); g2 = __ldg(g + 2); g3 = __ldg(g + 3); g4 = __ldg(g + 4);
+    pos = mk(__ldg(p.means3D + 3 * i), __ldg(p.means3D + 3 * i + 1), __ldg(p.means3D + 3 * i + 2));
+  }
   if (has_sh) {
     sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, p.M, rows, vis_mask, lane);
     __syncwarp();
@@ -232,12 +240,6 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
   float dT[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
 
   if (visible) {
-    const float* g = p.grad_records + i * GREC;
-    const float4 g0 = __ldg(reinterpret_cast<const float4*>(g) + 0);
-    const float4 g1 = __ldg(reinterpret_cast<const float4*>(g) + 1);
-    const float4 g2 = __ldg(reinterpret_cast<const float4*>(g) + 2);
-    const float4 g3 = __ldg(reinterpret_cast<const float4*>(g) + 3);
-    const float4 g4 = __ldg(reinterpret_cast<const float4*>(g) + 4);
     dT[0] = g0.x; dT[1] = g0.y; dT[2] = g0.z; dT[3] = g0.w; dT[4] = g1.x; dT[5] = g1.y;
     dT[6] = g1.z; dT[7] = g1.w; dT[8] = g2.x;
     const float gcx = g2.y, gcy = g2.z;
@@ -248,7 +250,6 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
 
     const float* vm = p.viewmatrix;
     const float* pm = p.projmatrix;
-    const f3 pos = mk(__ldg(p.means3D + 3 * i), __ldg(p.means3D + 3 * i + 1), __ldg(p.means3D + 3 * i + 2));
     // transMats[idx*9+8] of the forward (Tw.z): it depends on the position and the projection matrix only, so it
     // is recomputed in the forward's association (preprocess.cu) instead of gathered from the 80-byte record
     const float depth = p.scales == nullptr

@@ -176,18 +176,28 @@ class FactoredExchange:
         return g
 
 
-def exchange_factored(ex: FactoredExchange, group=None):
-    """The exchange step of the factored path: one all-gather (dL_dRGB) + one all-reduce (the rest)."""
+def exchange_factored(ex: FactoredExchange, group=None, after_gather: Optional[Callable] = None):
+    """The exchange step of the factored path: one all-gather (dL_dRGB) + one all-reduce (the rest, statistics
+    included) + the max of the radii.  `after_gather()` (the local SH expand) is launched as soon as the gathered
+    dL_dRGB is visible to the compute stream, so that it runs WHILE the all-reduce is still on the wire: the
+    collectives are issued asynchronously and only waited for where their result is needed."""
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         ex.rgb_recv[0].copy_(ex.rgb_send)
+        if after_gather is not None:
+            after_gather()
         return
     if dist.get_backend(group) == "nccl":
-        dist.all_gather_into_tensor(ex.rgb_recv.view(-1), ex.rgb_send.view(-1), group=group)
+        wg = dist.all_gather_into_tensor(ex.rgb_recv.view(-1), ex.rgb_send.view(-1), group=group, async_op=True)
     else:
-        dist.all_gather(list(ex.rgb_recv.unbind(0)), ex.rgb_send, group=group)
-    dist.all_reduce(ex.flat, op=dist.ReduceOp.SUM, group=group)   # gradients + (grad-norm, visibility) statistics
-    if ex.max_radii is not None:
-        dist.all_reduce(ex.max_radii, op=dist.ReduceOp.MAX, group=group)
+        wg = dist.all_gather(list(ex.rgb_recv.unbind(0)), ex.rgb_send, group=group, async_op=True)
+    wr = dist.all_reduce(ex.flat, op=dist.ReduceOp.SUM, group=group, async_op=True)   # gradients + statistics sums
+    wm = dist.all_reduce(ex.max_radii, op=dist.ReduceOp.MAX, group=group, async_op=True) if ex.max_radii is not None else None
+    wg.wait()
+    if after_gather is not None:
+        after_gather()
+    wr.wait()
+    if wm is not None:
+        wm.wait()
 
 
 def view_parallel_step_factored(params: Dict[str, torch.Tensor], cameras: Sequence, ex: FactoredExchange,
@@ -237,7 +247,6 @@ def view_parallel_step_factored(params: Dict[str, torch.Tensor], cameras: Sequen
         results.append(ViewResult(color, radii, allmap))
     if len(mine) < ex.max_local_views:
         ex.rgb_send[len(mine):].zero_()  # unused slots contribute nothing
-    exchange_factored(ex, group)
     # camera centre of slot (r, j) = view r + j*N; empty slots keep zeros (their dL_dRGB is zero)
     slots = ex.campos.view(world_size, ex.max_local_views, 3)
     for v in range(n_views):  # device-side copies of 12 bytes: no host synchronisation
@@ -246,5 +255,6 @@ def view_parallel_step_factored(params: Dict[str, torch.Tensor], cameras: Sequen
             slots[v % world_size, v // world_size].copy_(c, non_blocking=True)
     if sh_degree is None:
         sh_degree = int(round(params["shs"].shape[1] ** 0.5)) - 1
-    expand_fn(params["means3D"], ex.campos, ex.rgb_recv.view(-1, ex.P, 3), ex.dL_dsh, sh_degree)
+    exchange_factored(ex, group, after_gather=lambda: expand_fn(params["means3D"], ex.campos,
+                                                                ex.rgb_recv.view(-1, ex.P, 3), ex.dL_dsh, sh_degree))
     return results

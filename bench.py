@@ -134,10 +134,15 @@ def make_workload(args, device):
                 cot=cot, cot_d=cot_d)
 
 
-def loss_fn(color, allmap, gt):
-    """L1 photometric term + small terms on every allmap channel so that every backward branch is live
-    (train.py:113-143 shape: L1, normal and distortion regularisers)."""
-    return ((color - gt).abs().mean() + 0.05 * allmap[2:5].abs().mean() + 100.0 * allmap[6].mean() +
+LAMBDA_DSSIM = 0.2  # arguments/__init__.py:86 (OptimizationParams.lambda_dssim)
+
+
+def loss_fn(color, allmap, gt, photometric):
+    """train.py:113-143 shape: (1 - lambda) L1 + lambda (1 - SSIM) on the colour (train.py:113-114; `photometric`
+    is each arm's own implementation of it: the reference's torch ops for the reference arm, the fused
+    gsm_photometric_loss for ours) + small terms on every allmap channel so that every backward branch is
+    live (normal and distortion regularisers)."""
+    return (photometric(color, gt, LAMBDA_DSSIM) + 0.05 * allmap[2:5].abs().mean() + 100.0 * allmap[6].mean() +
             0.01 * (allmap[0].mean() + allmap[1].mean() + allmap[5].mean()))
 
 
@@ -149,7 +154,9 @@ class OursArm:
     def __init__(self, wl, device, world):
         import gaussmart_b200 as gb
         from gaussmart_b200 import view_parallel as vp
+        from gaussmart_b200.loss import photometric_loss
         self.gb, self.vp, self.wl, self.device, self.world = gb, vp, wl, device, world
+        self.photometric = photometric_loss
         self.rank = int(os.environ.get("RANK", "0"))
         M = wl["params"]["shs"].shape[1]
         self.bucket = vp.GradBucket(wl["P"], M, device, with_stats=True) if world == 1 else None
@@ -189,7 +196,7 @@ class OursArm:
         color, radii, allmap = gb.GaussianRasterizer(S)(
             means3D=L["means3D"], means2D=self.means2D, opacities=L["opacities"], shs=L["shs"], scales=L["scales"],
             rotations=L["rotations"])
-        loss = loss_fn(color, allmap, gt)
+        loss = loss_fn(color, allmap, gt, self.photometric)
         loss.backward()
         return loss
 
@@ -202,7 +209,7 @@ class OursArm:
         def cot(v, color, allmap):
             c = color.detach().requires_grad_(True)
             a = allmap.detach().requires_grad_(True)
-            loss = loss_fn(c, a, gt)
+            loss = loss_fn(c, a, gt, self.photometric)
             loss.backward()
             box["loss"] = loss.detach()
             return c.grad, a.grad
@@ -222,6 +229,9 @@ class ReferenceArm:
     def __init__(self, wl, device, world):
         import ref_loader
         self.ref = ref_loader.load_dsr()
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import loss_oracle  # the reference's own torch loss (utils/loss_utils.py restated; pinned by tests/golden/loss_ref_*)
+        self.photometric = loss_oracle.photometric_loss
         self.wl, self.device, self.world = wl, device, 1
         self.bg = torch.zeros(3, device=device)
         self.leaves = {k: v.clone().requires_grad_(True) for k, v in wl["params"].items()}
@@ -245,7 +255,7 @@ class ReferenceArm:
 
     def api_step(self, cam_d, gt):
         color, radii, allmap = self._render(cam_d)
-        loss = loss_fn(color, allmap, gt)
+        loss = loss_fn(color, allmap, gt, self.photometric)
         loss.backward()
         return loss
 
@@ -399,6 +409,35 @@ def knn_leg(wl, impl, reps=3):
             "checksum": float(out.double().sum().item())}
 
 
+def loss_leg(wl, photometric, reps=20):
+    """The photometric loss of the iteration (train.py:113-114), value + gradient w.r.t. the image, at the
+    workload's resolution: each arm's own implementation (fused gsm_photometric_loss / the reference's torch ops),
+    CUDA events; reported beside the iteration metric.  compulsory bytes: read image + gt,
+    write the gradient = 12 B per pixel-channel."""
+    g = torch.Generator(device="cpu").manual_seed(99)
+    gt = torch.rand(3, wl["H"], wl["W"], generator=g).cuda()
+    img = (gt + 0.05 * torch.randn(3, wl["H"], wl["W"], generator=g).cuda()).clamp(0, 1)
+
+    def once():
+        x = img.detach().requires_grad_(True)
+        loss = photometric(x, gt, LAMBDA_DSSIM)
+        loss.backward()
+        return loss, x.grad
+    for _ in range(3):
+        once()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        loss, grad = once()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    n = img.numel()
+    return {"ms": ms, "pixels": wl["H"] * wl["W"], "calls": reps, "compulsory_gbs": 12.0 * n / (ms * 1e-3) / 1e9,
+            "loss": float(loss.detach()), "grad_checksum": float(grad.double().abs().sum())}
+
+
 # ------------------------------------------------------------------------------------------------
 def main():
     args = parse()
@@ -529,6 +568,8 @@ def main():
                 line["knn"] = knn_leg(wl, "reference", reps=1)
             except Exception as ex:  # pragma: no cover
                 line["knn"] = {"error": repr(ex)[:200]}
+            if hasattr(arm, "photometric"):
+                line["loss"] = loss_leg(wl, arm.photometric)
         print(json.dumps(line))
         return 0
 
@@ -568,6 +609,7 @@ def main():
     line["gpu_launches"] = int(sum(kernels_per_stage.get(n, 0) * c for n, (_, c) in stages.items()))
     if world == 1 and not args.no_knn:
         line["knn"] = knn_leg(wl, "ours")
+        line["loss"] = loss_leg(wl, arm.photometric)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(int(wc["E_bwd"]), wl["deg"])
     print(json.dumps(line))

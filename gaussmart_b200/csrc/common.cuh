@@ -137,7 +137,8 @@ int cuda_fail(cudaError_t e, const char* what);
 // ---- optional per-stage timing (api.cu) --------------------------------------------------
 enum {
   GSM_STAGE_PREPROCESS_FWD = 0, GSM_STAGE_SCAN, GSM_STAGE_DUPLICATE, GSM_STAGE_SORT, GSM_STAGE_RANGES,
-  GSM_STAGE_RENDER_FWD, GSM_STAGE_GRAD_ZERO, GSM_STAGE_RENDER_BWD, GSM_STAGE_PREPROCESS_BWD, GSM_STAGE_KNN
+  GSM_STAGE_RENDER_FWD, GSM_STAGE_GRAD_ZERO, GSM_STAGE_RENDER_BWD, GSM_STAGE_PREPROCESS_BWD, GSM_STAGE_KNN,
+  GSM_STAGE_LOSS
 };
 class StageMark {  // RAII: records a cudaEvent pair around a stage when timing is enabled
  public:

@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 3
+#define GSM_ABI_VERSION 4
 
 #define GSM_OK 0
 #define GSM_ERR_INVALID_ARGUMENT 10001
@@ -44,7 +44,7 @@ int gsm_abi_version(void);
  * cudaEvent pair on the launching stream.  gsm_stage_timing_read synchronises the outstanding
  * events and returns, per stage, the summed device milliseconds and the number of launches.
  * The reference has no equivalent (its only hook is debug's sync-after-stage, auxiliary.h:296-303). */
-#define GSM_NUM_STAGES 10
+#define GSM_NUM_STAGES 11
 int gsm_stage_count(void);
 const char* gsm_stage_name(int stage);
 int gsm_stage_timing_enable(int on); /* returns the previous setting */
@@ -177,6 +177,18 @@ int gsm_backward(const gsm_backward_args* args, void* stream);
 int gsm_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D /*[P,3]*/,
                        const float* campos_all /*[n_views,3]*/, const float* dL_drgb_all /*[n_views,P,3]*/,
                        float* dL_dsh /*[P,M,3]*/, int accumulate, void* stream);
+
+/* ---- photometric loss of the training iteration (the rasterizer's caller).  Replaces, fused,
+ *      utils/loss_utils.py:16-17 (l1_loss) + :32-62 (ssim, _ssim: 11x11 Gaussian window, sigma 1.5, zero padding,
+ *      C1 = 0.01^2, C2 = 0.03^2, mean) as combined at train.py:113-114 AND their autograd backward:
+ *        loss = (1 - lambda_dssim) * mean|image - gt| + lambda_dssim * (1 - ssim(image, gt))
+ *      image, gt: [C,H,W] fp32 on the device.  loss_out (device, may be NULL): [3] = loss, l1, ssim.
+ *      dL_dimage [C,H,W] = grad_scale * dloss/dimage (overwritten).  workspace: caller-owned scratch of
+ *      gsm_photometric_loss_workspace_bytes(C,H,W) bytes. */
+size_t gsm_photometric_loss_workspace_bytes(int C, int H, int W);
+int gsm_photometric_loss(const float* image, const float* gt, int C, int H, int W, float lambda_dssim,
+                         float grad_scale, float* loss_out, float* dL_dimage, void* workspace,
+                         size_t workspace_bytes, void* stream);
 
 /* ---- markVisible: replaces CudaRasterizer::Rasterizer::markVisible (rasterizer.h:24-31,
  *      rasterizer_impl.cu:141-153; rasterize_points.cu:235-254).  present is uint8[P]. */

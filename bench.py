@@ -54,6 +54,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-knn", action="store_true")
+    ap.add_argument("--no-render", action="store_true", help="skip the render-FPS leg (forward only, workload size and 4K)")
     return ap.parse_args()
 
 
@@ -200,6 +201,16 @@ class OursArm:
         loss.backward()
         return loss
 
+    def render(self, cam_d):
+        """Inference render (render.py / gr.py:37-97 under torch.no_grad): forward only through the public API."""
+        from gaussmart_b200 import synthetic
+        S = self.gb.GaussianRasterizationSettings(**synthetic.settings_kwargs(cam_d, self.wl["deg"], self.bg))
+        L = self.leaves_data
+        with torch.no_grad():
+            return self.gb.GaussianRasterizer(S)(
+                means3D=L["means3D"], means2D=self.means2D, opacities=L["opacities"], shs=L["shs"], scales=L["scales"],
+                rotations=L["rotations"])
+
     def api_step_view_parallel(self, cams_step, gt):
         """N > 1: the public multi-GPU call, view_parallel_step_factored, with the loss of train.py's shape
         differentiated w.r.t. the rendered maps inside cotangent_fn (same work as api_step per rank)."""
@@ -248,6 +259,10 @@ class ReferenceArm:
         return ref.GaussianRasterizer(S)(
             means3D=L["means3D"], means2D=self.means2D, opacities=L["opacities"], shs=L["shs"], scales=L["scales"],
             rotations=L["rotations"])
+
+    def render(self, cam_d):
+        with torch.no_grad():
+            return self._render(cam_d)
 
     def value_step(self, view):
         color, radii, allmap = self._render(self.wl["cams_d"][view])
@@ -409,6 +424,36 @@ def knn_leg(wl, impl, reps=3):
             "checksum": float(out.double().sum().item())}
 
 
+def render_leg(arm, wl, world, rank, device, resolutions, reps=10):
+    """Render FPS (BASELINE.json metric, second half; configs[4] "render-only 4K sweep"): forward only through the
+    public API under no_grad on the workload's scene, rank r renders view (s*N + r) mod 8, no communication;
+    aggregate FPS = N * frames per rank / max-over-ranks device time."""
+    from gaussmart_b200 import synthetic
+    out = []
+    for (W, H) in resolutions:
+        cams = [synthetic.Camera(*[x.to(device) if isinstance(x, torch.Tensor) else x for x in c])
+                for c in synthetic.make_cameras(W, H, N_VIEWS)]
+        box = {}
+
+        def frame(s):
+            box["c"] = arm.render(cams[(s * world + rank) % N_VIEWS])[0]
+        ms = timed_loop(frame, reps, 3, world, rank)
+        out.append({"width": W, "height": H, "fps": world * reps / (ms * 1e-3), "ms_per_frame": ms / reps, "frames": reps * world,
+                    "checksum": float(box["c"].double().sum())})
+        if arm.name == "ours":  # one more pass with the stage timers on (not part of the timed frames)
+            from gaussmart_b200 import _lib
+            _lib.stage_timing_enable(True)
+            _lib.stage_timing_read(reset=True)
+            for s_ in range(4):
+                frame(s_)
+            torch.cuda.synchronize()
+            out[-1]["stages_ms"] = {k: v[0] / v[1] for k, v in _lib.stage_timing_read(reset=True).items() if v[1]}
+            _lib.stage_timing_enable(False)
+        del cams, box
+        torch.cuda.empty_cache()
+    return out
+
+
 def loss_leg(wl, photometric, reps=20):
     """The photometric loss of the iteration (train.py:113-114), value + gradient w.r.t. the image, at the
     workload's resolution: each arm's own implementation (fused gsm_photometric_loss / the reference's torch ops),
@@ -533,6 +578,11 @@ def main():
                "ms_per_step": ms_e2e / args.steps,
                "api": "GaussianRasterizationSettings/GaussianRasterizer + loss.backward()"}
 
+    render = None
+    if not args.no_render:
+        torch.cuda.empty_cache()
+        render = render_leg(arm, wl, world, rank, device, [(wl["W"], wl["H"]), (3840, 2160)])
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -554,6 +604,8 @@ def main():
                    "debug_P_override": args.P is not None},
         "clocks": clocks, "e2e": e2e,
     }
+    if render is not None:
+        line["render"] = render
     if args.impl == "reference":
         line["impl"] = "reference"
         line["gpu_launches"] = None

@@ -195,25 +195,49 @@ __device__ __forceinline__ unsigned digit_peers(uint32_t d, bool valid, int bits
   return peers;
 }
 
-template <int THREADS, int MAXBITS>
+// ITEMS > 0 and `cached`: the segment fits ITEMS elements per thread (shared-memory classes), so the elements and
+// their peer masks found in sweep 1 stay in registers for sweep 2 (no second read, no second round of ballots).
+template <int THREADS, int MAXBITS, int ITEMS>
 __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* __restrict__ B, uint32_t n,
                                            uint32_t kmin, int shift, int bits, uint32_t (*whist)[1 << MAXBITS],
-                                           uint32_t* warp_tot, int t, int lane, int warp) {
+                                           uint32_t* warp_tot, int t, int lane, int warp, bool cached) {
   constexpr int WARPS = THREADS / 32, MAXRADIX = 1 << MAXBITS;
   const uint32_t radix = 1u << bits, dmask = radix - 1u;
   const uint32_t chunk = ((n + THREADS - 1) / THREADS) * 32;
   const uint32_t wbeg = min(warp * chunk, n), wend = min(wbeg + chunk, n);
   for (int i = t; i < WARPS * MAXRADIX; i += THREADS) (&whist[0][0])[i] = 0u;
   __syncthreads();
+  uint2 ce[ITEMS];
+  unsigned cp[ITEMS];
   // sweep 1: per-warp digit histograms; lanes with equal digits are aggregated so that one lane per
   // distinct digit touches shared memory (no shared-memory atomics: 2 cycles per lane)
-  for (uint32_t it = wbeg; it < wend; it += 32) {
-    const uint32_t i = it + lane;
-    const bool valid = i < wend;
-    const uint32_t d = valid ? (((A[i].x - kmin) >> shift) & dmask) : 0u;
-    const unsigned peers = digit_peers(d, valid, bits);
-    if (valid && lane == __ffs(peers) - 1) whist[warp][d] += __popc(peers);
-    __syncwarp();
+  if (cached) {
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) {
+      const uint32_t it = wbeg + 32u * k;
+      cp[k] = 0u;
+      if (it < wend) {  // warp-uniform
+        const uint32_t i = it + lane;
+        const bool valid = i < wend;
+        uint2 e = make_uint2(0u, 0u);
+        if (valid) e = A[i];
+        const uint32_t d = valid ? (((e.x - kmin) >> shift) & dmask) : 0u;
+        const unsigned peers = digit_peers(d, valid, bits);
+        if (valid && lane == __ffs(peers) - 1) whist[warp][d] += __popc(peers);
+        ce[k] = e;
+        cp[k] = valid ? peers : 0u;
+        __syncwarp();
+      }
+    }
+  } else {
+    for (uint32_t it = wbeg; it < wend; it += 32) {
+      const uint32_t i = it + lane;
+      const bool valid = i < wend;
+      const uint32_t d = valid ? (((A[i].x - kmin) >> shift) & dmask) : 0u;
+      const unsigned peers = digit_peers(d, valid, bits);
+      if (valid && lane == __ffs(peers) - 1) whist[warp][d] += __popc(peers);
+      __syncwarp();
+    }
   }
   __syncthreads();
   // exclusive scan over (digit, warp): each thread owns DPT consecutive digits
@@ -252,6 +276,26 @@ __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* _
   }
   __syncthreads();
   // sweep 2: stable scatter
+  if (cached) {
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) {
+      if (wbeg + 32u * k < wend) {  // warp-uniform
+        const unsigned peers = cp[k];
+        const bool valid = peers != 0u;
+        const uint2 e = ce[k];
+        const uint32_t d = ((e.x - kmin) >> shift) & dmask;
+        const int leader = valid ? __ffs(peers) - 1 : lane;
+        const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+        uint32_t old = 0;
+        if (valid && lane == leader) { old = whist[warp][d]; whist[warp][d] = old + __popc(peers); }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        if (valid) B[old + rank] = e;
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    return;
+  }
   for (uint32_t it = wbeg; it < wend; it += 32) {
     const uint32_t i = it + lane;
     const bool valid = i < wend;
@@ -270,7 +314,7 @@ __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* _
   __syncthreads();
 }
 
-template <int THREADS, int MAXBITS>
+template <int THREADS, int MAXBITS, int ITEMS>
 __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams p) {
   constexpr int WARPS = THREADS / 32;
   extern __shared__ __align__(16) uint2 ts_dyn[];
@@ -308,7 +352,7 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
   const int passes = (nbits + MAXBITS - 1) / MAXBITS;
   const int bits = passes ? (nbits + passes - 1) / passes : 0;  // equal digit widths, <= MAXBITS
   for (int shift = 0; shift < nbits; shift += bits) {
-    radix_pass<THREADS, MAXBITS>(A, B, n, kmin, shift, bits, whist, warp_tot, t, lane, warp);
+    radix_pass<THREADS, MAXBITS, ITEMS>(A, B, n, kmin, shift, bits, whist, warp_tot, t, lane, warp, in_smem);
     uint2* tmp = A; A = B; B = tmp;
   }
   // equal depth bits: ascending surfel index (the reference's stable sort keeps emission order)
@@ -359,8 +403,8 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
 void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, uint32_t* point_list,
                       uint8_t* strip_mask, const short4* bbox, const float4* cull, int grid_x, int num_tiles,
                       int no_cull, cudaStream_t stream) {
-  auto small = tile_sort_kernel<TS_SMALL_THREADS, TS_SMALL_BITS>;
-  auto large = tile_sort_kernel<TS_LARGE_THREADS, TS_LARGE_BITS>;
+  auto small = tile_sort_kernel<TS_SMALL_THREADS, TS_SMALL_BITS, (TS_CAP_SMALL + TS_SMALL_THREADS - 1) / TS_SMALL_THREADS>;
+  auto large = tile_sort_kernel<TS_LARGE_THREADS, TS_LARGE_BITS, (TS_CAP_LARGE + TS_LARGE_THREADS - 1) / TS_LARGE_THREADS>;
   constexpr size_t hist_small = (size_t)(TS_SMALL_THREADS / 32) * (1u << TS_SMALL_BITS) * 4;
   constexpr size_t hist_large = (size_t)(TS_LARGE_THREADS / 32) * (1u << TS_LARGE_BITS) * 4;
   static bool configured = false;

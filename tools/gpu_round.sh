@@ -15,10 +15,10 @@ echo "bench exit $?"
 cut -c1-1500 gpurun_out/${TAG}_bench.json
 cut -c1-600 gpurun_out/${TAG}_bench_ref.json
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
-  --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --no-knn \
+  --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --no-knn --no-render \
   > gpurun_out/${TAG}_ncu_launches.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on \
   -k regex:'render_bwd_kernel|render_fwd_kernel|preprocess_bwd_kernel|preprocess_fwd_kernel|tile_sort_kernel|scatter_kernel' \
   --launch-skip 14 --launch-count 9 -o gpurun_out/${TAG}_full -f \
-  python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --no-knn > gpurun_out/${TAG}_ncu_full.log 2>&1
+  python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --no-knn --no-render > gpurun_out/${TAG}_ncu_full.log 2>&1
 ls -la gpurun_out/

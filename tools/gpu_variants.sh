@@ -6,7 +6,7 @@ mkdir -p gpurun_out
 for v in "$@"; do
   lib=gaussmart_b200/lib/libgaussmart_b200_$v.so
   [ "$v" = "default" ] && lib=gaussmart_b200/lib/libgaussmart_b200.so
-  GAUSSMART_B200_LIB=$PWD/$lib timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --no-knn \
+  GAUSSMART_B200_LIB=$PWD/$lib timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --no-knn --no-render \
     > gpurun_out/${OUT}_$v.json 2> gpurun_out/${OUT}_$v.err
   python - <<PY
 import json

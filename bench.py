@@ -454,6 +454,44 @@ def render_leg(arm, wl, world, rank, device, resolutions, reps=10):
     return out
 
 
+def adam_leg(wl, impl, reps=10):
+    """`gaussians.optimizer.step()` of the iteration (train.py:212) on the workload's six parameter
+    groups (gaussian_model.py:283-290; arguments/__init__.py:77-84 learning rates): the reference's own choice,
+    torch.optim.Adam(l, lr=0.0, eps=1e-15), for the reference arm; FusedAdam (one gsm_adam_step launch) for ours.
+    compulsory bytes: 16 read + 12 written per parameter element."""
+    P, M = wl["P"], wl["params"]["shs"].shape[1]
+    shapes = [("xyz", (P, 3), 0.00016), ("f_dc", (P, 1, 3), 0.0025), ("f_rest", (P, M - 1, 3), 0.0025 / 20.0),
+              ("opacity", (P, 1), 0.05), ("scaling", (P, 2), 0.005), ("rotation", (P, 4), 0.001)]
+    g = torch.Generator(device="cuda").manual_seed(5)
+    groups = []
+    for name, shape, lr in shapes:
+        p = torch.nn.Parameter(torch.randn(shape, device="cuda", generator=g))
+        p.grad = torch.randn(shape, device="cuda", generator=g) * 1e-3
+        groups.append({"params": [p], "lr": lr, "name": name})
+    if impl == "reference":
+        opt = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
+    else:
+        from gaussmart_b200.optim import FusedAdam
+        opt = FusedAdam(groups, lr=0.0, eps=1e-15)
+    for _ in range(3):
+        opt.step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        opt.step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    n = sum(gr["params"][0].numel() for gr in groups)
+    out = {"ms": ms, "elements": n, "calls": reps, "compulsory_gbs": 28.0 * n / (ms * 1e-3) / 1e9,
+           "frac_of_hbm_peak": 28.0 * n / (ms * 1e-3) / 1e9 / peaks()["hbm_gbs"],
+           "checksum": float(sum(gr["params"][0].detach().double().sum() for gr in groups))}
+    del opt, groups
+    torch.cuda.empty_cache()
+    return out
+
+
 def loss_leg(wl, photometric, reps=20):
     """The photometric loss of the iteration (train.py:113-114), value + gradient w.r.t. the image, at the
     workload's resolution: each arm's own implementation (fused gsm_photometric_loss / the reference's torch ops),
@@ -622,6 +660,7 @@ def main():
                 line["knn"] = {"error": repr(ex)[:200]}
             if hasattr(arm, "photometric"):
                 line["loss"] = loss_leg(wl, arm.photometric)
+            line["adam"] = adam_leg(wl, "reference")
         print(json.dumps(line))
         return 0
 
@@ -662,6 +701,7 @@ def main():
     if world == 1 and not args.no_knn:
         line["knn"] = knn_leg(wl, "ours")
         line["loss"] = loss_leg(wl, arm.photometric)
+        line["adam"] = adam_leg(wl, "ours")
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(int(wc["E_bwd"]), wl["deg"])
     print(json.dumps(line))

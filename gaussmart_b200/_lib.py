@@ -26,8 +26,14 @@ EXPORTS = [
     "gsm_knn_workspace_bytes", "gsm_knn_dist2",
     "gsm_stage_count", "gsm_stage_name", "gsm_stage_timing_enable", "gsm_stage_timing_read",
     "gsm_sort_pairs32_temp_bytes", "gsm_sort_pairs32", "gsm_sh_grad_expand",
-    "gsm_photometric_loss_workspace_bytes", "gsm_photometric_loss",
+    "gsm_photometric_loss_workspace_bytes", "gsm_photometric_loss", "gsm_adam_step",
 ]
+
+
+class AdamTensor(Structure):
+    _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p),
+                ("n", c_size_t), ("lr", ctypes.c_double), ("beta1", ctypes.c_double), ("beta2", ctypes.c_double),
+                ("eps", ctypes.c_double), ("step", c_int)]
 
 
 class ForwardArgs(Structure):
@@ -124,6 +130,8 @@ def load():
     lib.gsm_photometric_loss.restype = c_int
     lib.gsm_photometric_loss.argtypes = [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_void_p, c_void_p,
                                          c_void_p, c_size_t, c_void_p]
+    lib.gsm_adam_step.restype = c_int
+    lib.gsm_adam_step.argtypes = [POINTER(AdamTensor), c_int, c_void_p]
     if lib.gsm_abi_version() != ABI_VERSION:
         raise ImportError(f"gaussmart_b200: ABI version mismatch ({lib.gsm_abi_version()} != {ABI_VERSION})")
     _lib = lib

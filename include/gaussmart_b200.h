@@ -44,7 +44,7 @@ int gsm_abi_version(void);
  * cudaEvent pair on the launching stream.  gsm_stage_timing_read synchronises the outstanding
  * events and returns, per stage, the summed device milliseconds and the number of launches.
  * The reference has no equivalent (its only hook is debug's sync-after-stage, auxiliary.h:296-303). */
-#define GSM_NUM_STAGES 11
+#define GSM_NUM_STAGES 12
 int gsm_stage_count(void);
 const char* gsm_stage_name(int stage);
 int gsm_stage_timing_enable(int on); /* returns the previous setting */
@@ -189,6 +189,24 @@ size_t gsm_photometric_loss_workspace_bytes(int C, int H, int W);
 int gsm_photometric_loss(const float* image, const float* gt, int C, int H, int W, float lambda_dssim,
                          float grad_scale, float* loss_out, float* dL_dimage, void* workspace,
                          size_t workspace_bytes, void* stream);
+
+/* ---- optimizer step of the training iteration.  Replaces, fused into ONE launch over all parameter
+ *      tensors, `gaussians.optimizer.step()` (train.py:212) of torch.optim.Adam(l, lr=0.0, eps=1e-15)
+ *      (scene/gaussian_model.py:283-292): amsgrad off, weight_decay 0, every element updated.  Per tensor (in place):
+ *        exp_avg = lerp(exp_avg, grad, 1 - beta1);  exp_avg_sq = exp_avg_sq * beta2 + (1 - beta2) * grad^2;
+ *        param  -= lr / (1 - beta1^step) * exp_avg / (sqrt(exp_avg_sq) / sqrt(1 - beta2^step) + eps)
+ *      `step` is the step count AFTER this update (>= 1), as torch keeps it.  `tensors` is a HOST array; all device
+ *      pointers fp32, 16-byte aligned. */
+typedef struct gsm_adam_tensor {
+  float* param;
+  const float* grad;
+  float* exp_avg;
+  float* exp_avg_sq;
+  size_t n;
+  double lr, beta1, beta2, eps;
+  int step;
+} gsm_adam_tensor;
+int gsm_adam_step(const gsm_adam_tensor* tensors, int n_tensors, void* stream);
 
 /* ---- markVisible: replaces CudaRasterizer::Rasterizer::markVisible (rasterizer.h:24-31,
  *      rasterizer_impl.cu:141-153; rasterize_points.cu:235-254).  present is uint8[P]. */

@@ -136,15 +136,16 @@ def make_workload(args, device):
 
 
 LAMBDA_DSSIM = 0.2  # arguments/__init__.py:86 (OptimizationParams.lambda_dssim)
+DEPTH_RATIO, LAMBDA_NORMAL, LAMBDA_DIST = 0.0, 0.05, 100.0  # arguments/__init__.py:70,88; lambda_dist: 2DGS's setting for
+#                                                             bounded scenes (the reference's default 0.0 leaves that branch dead)
 
 
-def loss_fn(color, allmap, gt, photometric):
-    """train.py:113-143 shape: (1 - lambda) L1 + lambda (1 - SSIM) on the colour (train.py:113-114; `photometric`
-    is each arm's own implementation of it: the reference's torch ops for the reference arm, the fused
-    gsm_photometric_loss for ours) + small terms on every allmap channel so that every backward branch is
-    live (normal and distortion regularisers)."""
-    return (photometric(color, gt, LAMBDA_DSSIM) + 0.05 * allmap[2:5].abs().mean() + 100.0 * allmap[6].mean() +
-            0.01 * (allmap[0].mean() + allmap[1].mean() + allmap[5].mean()))
+def loss_fn(color, allmap, gt, cam, photometric, regularizer):
+    """train.py:113-143: (1 - lambda) L1 + lambda (1 - SSIM) on the colour (train.py:113-114) + normal-consistency and
+    distortion regularisers on the allmap (gaussian_renderer/__init__.py:117-147 post-processing, utils/point_utils.py
+    depth_to_normal, train.py:131-140).  `photometric` / `regularizer` are each arm's own implementation: the
+    reference's torch ops for the reference arm, the fused gsm_photometric_loss / gsm_surface_regularizer for ours."""
+    return photometric(color, gt, LAMBDA_DSSIM) + regularizer(allmap, cam, DEPTH_RATIO, LAMBDA_NORMAL, LAMBDA_DIST)
 
 
 class OursArm:
@@ -158,6 +159,8 @@ class OursArm:
         from gaussmart_b200.loss import photometric_loss
         self.gb, self.vp, self.wl, self.device, self.world = gb, vp, wl, device, world
         self.photometric = photometric_loss
+        from gaussmart_b200.regularizer import surface_regularizer
+        self.regularizer = surface_regularizer
         self.rank = int(os.environ.get("RANK", "0"))
         M = wl["params"]["shs"].shape[1]
         self.bucket = vp.GradBucket(wl["P"], M, device, with_stats=True) if world == 1 else None
@@ -185,7 +188,7 @@ class OursArm:
                                                                                 fused_stats=True),
             fused_stats=True)
 
-    def api_step(self, cam_d, gt):
+    def api_step(self, cam_d, gt, cam_h=None):
         """Public API: GaussianRasterizationSettings / GaussianRasterizer + autograd (gr.py:37-97 shape)."""
         from gaussmart_b200 import synthetic
         gb = self.gb
@@ -197,7 +200,7 @@ class OursArm:
         color, radii, allmap = gb.GaussianRasterizer(S)(
             means3D=L["means3D"], means2D=self.means2D, opacities=L["opacities"], shs=L["shs"], scales=L["scales"],
             rotations=L["rotations"])
-        loss = loss_fn(color, allmap, gt, self.photometric)
+        loss = loss_fn(color, allmap, gt, cam_d if cam_h is None else cam_h, self.photometric, self.regularizer)
         loss.backward()
         return loss
 
@@ -211,7 +214,7 @@ class OursArm:
                 means3D=L["means3D"], means2D=self.means2D, opacities=L["opacities"], shs=L["shs"], scales=L["scales"],
                 rotations=L["rotations"])
 
-    def api_step_view_parallel(self, cams_step, gt):
+    def api_step_view_parallel(self, cams_step, gt, cam_h=None):
         """N > 1: the public multi-GPU call, view_parallel_step_factored, with the loss of train.py's shape
         differentiated w.r.t. the rendered maps inside cotangent_fn (same work as api_step per rank)."""
         from gaussmart_b200.rasterizer import rasterize_into_bucket
@@ -220,7 +223,7 @@ class OursArm:
         def cot(v, color, allmap):
             c = color.detach().requires_grad_(True)
             a = allmap.detach().requires_grad_(True)
-            loss = loss_fn(c, a, gt, self.photometric)
+            loss = loss_fn(c, a, gt, cams_step[self.rank] if cam_h is None else cam_h, self.photometric, self.regularizer)
             loss.backward()
             box["loss"] = loss.detach()
             return c.grad, a.grad
@@ -243,6 +246,8 @@ class ReferenceArm:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import loss_oracle  # the reference's own torch loss (utils/loss_utils.py restated; pinned by tests/golden/loss_ref_*)
         self.photometric = loss_oracle.photometric_loss
+        import regularizer_oracle  # render()'s allmap post-processing + depth_to_normal + train.py:131-140, restated
+        self.regularizer = regularizer_oracle.surface_regularizer
         self.wl, self.device, self.world = wl, device, 1
         self.bg = torch.zeros(3, device=device)
         self.leaves = {k: v.clone().requires_grad_(True) for k, v in wl["params"].items()}
@@ -268,9 +273,9 @@ class ReferenceArm:
         color, radii, allmap = self._render(self.wl["cams_d"][view])
         torch.autograd.backward([color, allmap], [self.wl["cot_d"][0], self.wl["cot_d"][1]])
 
-    def api_step(self, cam_d, gt):
+    def api_step(self, cam_d, gt, cam_h=None):
         color, radii, allmap = self._render(cam_d)
-        loss = loss_fn(color, allmap, gt, self.photometric)
+        loss = loss_fn(color, allmap, gt, cam_d, self.photometric, self.regularizer)
         loss.backward()
         return loss
 
@@ -605,9 +610,9 @@ def main():
             if world > 1 and args.impl == "ours":
                 base = (v - rank) % N_VIEWS
                 cams_step = [cam_d if r == rank else wl["cams_d"][(base + r) % N_VIEWS] for r in range(world)]
-                loss = arm.api_step_view_parallel(cams_step, gt_dev)
+                loss = arm.api_step_view_parallel(cams_step, gt_dev, cam_h=c)
             else:
-                loss = arm.api_step(cam_d, gt_dev)
+                loss = arm.api_step(cam_d, gt_dev, cam_h=c)
             loss_host.copy_(loss.detach(), non_blocking=False)   # the per-iteration .item() of train.py:149
 
         ms_e2e = timed_loop(e2e_step, args.steps, max(3, args.warmup), world, rank)
@@ -620,6 +625,29 @@ def main():
     if not args.no_render:
         torch.cuda.empty_cache()
         render = render_leg(arm, wl, world, rank, device, [(wl["W"], wl["H"]), (3840, 2160)])
+
+    # ---- the full training iteration (BASELINE.json configs[3]): the e2e step + the optimizer step, each arm with its
+    #      own optimizer (torch.optim.Adam as gaussian_model.py:292 builds it / FusedAdam).  Run last: it moves the surfels.
+    train_iter = None
+    if e2e is not None and world == 1:
+        L = arm.leaves
+        # the leaves here are the ACTIVATED parameters, so the reference's raw-parameter learning rates would walk the
+        # scene away from the workload within a few steps; the optimizer's work does not depend on lr
+        groups = [{"params": [L[k]], "lr": 1e-8, "name": k} for k in ("means3D", "shs", "opacities", "scales", "rotations")]
+        if args.impl == "reference":
+            opt = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
+        else:
+            from gaussmart_b200.optim import FusedAdam
+            opt = FusedAdam(groups, lr=0.0, eps=1e-15)
+
+        def train_step(s):
+            e2e_step(s)
+            opt.step()
+        ms_train = timed_loop(train_step, args.steps, 3, world, rank)
+        train_iter = {"value": 1000.0 * args.steps / ms_train, "unit": UNIT, "ms_per_step": ms_train / args.steps,
+                      "includes": "H2D of camera + ground truth, render, L1+SSIM+regulariser loss, backward, loss read-back, "
+                                  "Adam step over all 58 floats/surfel"}
+        del opt
 
     if rank != 0:
         if world > 1:
@@ -644,6 +672,8 @@ def main():
     }
     if render is not None:
         line["render"] = render
+    if train_iter is not None:
+        line["train_iteration"] = train_iter
     if args.impl == "reference":
         line["impl"] = "reference"
         line["gpu_launches"] = None

@@ -27,7 +27,15 @@ EXPORTS = [
     "gsm_stage_count", "gsm_stage_name", "gsm_stage_timing_enable", "gsm_stage_timing_read",
     "gsm_sort_pairs32_temp_bytes", "gsm_sort_pairs32", "gsm_sh_grad_expand",
     "gsm_photometric_loss_workspace_bytes", "gsm_photometric_loss", "gsm_adam_step",
+    "gsm_surface_regularizer_workspace_bytes", "gsm_surface_regularizer",
 ]
+
+
+class RegularizerArgs(Structure):
+    _fields_ = [("allmap", c_void_p), ("H", c_int), ("W", c_int), ("ray_matrix", c_float * 9), ("ray_origin", c_float * 3),
+                ("view_rotation", c_float * 9), ("depth_ratio", c_float), ("lambda_normal", c_float), ("lambda_dist", c_float),
+                ("grad_scale", c_float), ("loss_out", c_void_p), ("dL_dallmap", c_void_p), ("rend_normal", c_void_p),
+                ("surf_normal", c_void_p), ("surf_depth", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
 
 
 class AdamTensor(Structure):
@@ -130,6 +138,10 @@ def load():
     lib.gsm_photometric_loss.restype = c_int
     lib.gsm_photometric_loss.argtypes = [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_void_p, c_void_p,
                                          c_void_p, c_size_t, c_void_p]
+    lib.gsm_surface_regularizer_workspace_bytes.restype = c_size_t
+    lib.gsm_surface_regularizer_workspace_bytes.argtypes = [c_int, c_int]
+    lib.gsm_surface_regularizer.restype = c_int
+    lib.gsm_surface_regularizer.argtypes = [POINTER(RegularizerArgs), c_void_p]
     lib.gsm_adam_step.restype = c_int
     lib.gsm_adam_step.argtypes = [POINTER(AdamTensor), c_int, c_void_p]
     if lib.gsm_abi_version() != ABI_VERSION:

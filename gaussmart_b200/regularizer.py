@@ -1,0 +1,102 @@
+"""Fused surface regularisers of the training iteration.
+
+Mirrors what GauSSmart does with the rasterizer's `allmap` between render() and total_loss.backward():
+gaussian_renderer/__init__.py:117-147 (rend_normal to world space, nan_to_num'd depths, surf_depth,
+surf_normal = depth_to_normal(view, surf_depth) * alpha.detach()), utils/point_utils.py:9-37 and the two loss terms of
+train.py:131-140.  One C-ABI call (gsm_surface_regularizer: two hand-written kernels, csrc/regularizer.cu) produces the
+loss terms AND dloss/dallmap.  No CPU or torch fallback.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+_constants = {}  # keyed by the camera matrices' storage + version: cameras are static during training
+
+
+def camera_constants(view):
+    """The per-camera constants of depths_to_points (utils/point_utils.py:9-24), formed with the reference's own fp32
+    expressions, once per camera (cached; the reference rebuilds them on the GPU every iteration):
+    ray_matrix = intrins.inverse().T @ c2w[:3,:3].T (3x3), ray_origin = c2w[:3,3], view_rotation = V[:3,:3]."""
+    wvt = view.world_view_transform
+    key = (wvt.data_ptr(), wvt._version, view.full_proj_transform.data_ptr(), int(view.image_width), int(view.image_height))
+    cached = _constants.get(key)
+    if cached is not None:
+        return cached
+    V = wvt.detach().float().cpu()
+    FP = view.full_proj_transform.detach().float().cpu()
+    W, H = int(view.image_width), int(view.image_height)
+    c2w = (V.T).inverse()
+    ndc2pix = torch.tensor([[W / 2, 0, 0, W / 2], [0, H / 2, 0, H / 2], [0, 0, 0, 1]]).float().T
+    intrins = ((c2w.T @ FP) @ ndc2pix)[:3, :3].T
+    ray_matrix = intrins.inverse().T @ c2w[:3, :3].T
+    out = (tuple(ray_matrix.reshape(-1).tolist()), tuple(c2w[:3, 3].tolist()), tuple(V[:3, :3].reshape(-1).tolist()))
+    if len(_constants) >= 4096:
+        _constants.clear()
+    _constants[key] = out
+    return out
+
+
+_ws = {}
+
+
+def surface_regularizer_and_grad(allmap, view, depth_ratio, lambda_normal, lambda_dist, grad_scale=1.0, want_maps=False):
+    """Returns (out[3] = normal_loss + dist_loss, normal_loss, dist_loss; dL_dallmap[7,H,W]; maps or None), on the device,
+    no sync.  maps = dict(rend_normal, surf_normal, surf_depth) as render() returns them."""
+    lib = _lib.load()
+    if not allmap.is_cuda:
+        raise RuntimeError("gaussmart_b200: allmap must be a CUDA tensor (there is no CPU path)")
+    if allmap.dtype != torch.float32 or allmap.dim() != 3 or allmap.shape[0] != 7 or not allmap.is_contiguous():
+        raise RuntimeError("allmap must be a contiguous float32 [7,H,W] tensor")
+    _, H, W = allmap.shape
+    dev = allmap.device
+    ray, origin, rot = camera_constants(view)
+    out = torch.empty(3, dtype=torch.float32, device=dev)
+    grad = torch.empty_like(allmap)
+    maps = None
+    if want_maps:
+        maps = dict(rend_normal=torch.empty(3, H, W, device=dev), surf_normal=torch.empty(3, H, W, device=dev),
+                    surf_depth=torch.empty(1, H, W, device=dev))
+    nbytes = lib.gsm_surface_regularizer_workspace_bytes(H, W)
+    ws = _ws.get(dev)
+    if ws is None or ws.numel() < nbytes:
+        ws = _ws[dev] = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    a = _lib.RegularizerArgs(allmap=allmap.data_ptr(), H=H, W=W, depth_ratio=float(depth_ratio),
+                             lambda_normal=float(lambda_normal), lambda_dist=float(lambda_dist), grad_scale=float(grad_scale),
+                             loss_out=out.data_ptr(), dL_dallmap=grad.data_ptr(), workspace=ws.data_ptr(),
+                             workspace_bytes=ws.numel())
+    a.ray_matrix[:] = ray
+    a.ray_origin[:] = origin
+    a.view_rotation[:] = rot
+    if maps is not None:
+        a.rend_normal, a.surf_normal, a.surf_depth = (maps["rend_normal"].data_ptr(), maps["surf_normal"].data_ptr(),
+                                                      maps["surf_depth"].data_ptr())
+    with torch.cuda.device(dev):
+        stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        _lib.check(lib.gsm_surface_regularizer(ctypes.byref(a), stream), "surface_regularizer")
+    return out, grad, maps
+
+
+class _SurfaceRegularizer(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, allmap, view, depth_ratio, lambda_normal, lambda_dist):
+        out, grad, _ = surface_regularizer_and_grad(allmap.contiguous(), view, depth_ratio, lambda_normal, lambda_dist)
+        ctx.save_for_backward(grad)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return grad * g, None, None, None, None
+
+
+def surface_regularizer(allmap, viewpoint_camera, depth_ratio=0.0, lambda_normal=0.05, lambda_dist=0.0):
+    """Scalar `normal_loss + dist_loss` of train.py:131-140 from the rasterizer's allmap, differentiable w.r.t. allmap.
+    Defaults: arguments/__init__.py (depth_ratio 0.0, lambda_normal 0.05, lambda_dist 0.0)."""
+    return _SurfaceRegularizer.apply(allmap, viewpoint_camera, depth_ratio, lambda_normal, lambda_dist)

@@ -44,7 +44,7 @@ int gsm_abi_version(void);
  * cudaEvent pair on the launching stream.  gsm_stage_timing_read synchronises the outstanding
  * events and returns, per stage, the summed device milliseconds and the number of launches.
  * The reference has no equivalent (its only hook is debug's sync-after-stage, auxiliary.h:296-303). */
-#define GSM_NUM_STAGES 12
+#define GSM_NUM_STAGES 13
 int gsm_stage_count(void);
 const char* gsm_stage_name(int stage);
 int gsm_stage_timing_enable(int on); /* returns the previous setting */
@@ -207,6 +207,34 @@ typedef struct gsm_adam_tensor {
   int step;
 } gsm_adam_tensor;
 int gsm_adam_step(const gsm_adam_tensor* tensors, int n_tensors, void* stream);
+
+/* ---- surface regularisers of the training iteration.  Replaces, fused, the allmap
+ *      post-processing of render() (gaussian_renderer/__init__.py:117-147: world-space normal, nan_to_num'd median and
+ *      expected depth, surf_depth, surf_normal = depth_to_normal(view, surf_depth) * alpha.detach()), depth_to_normal /
+ *      depths_to_points (utils/point_utils.py:9-37) and the two loss terms of train.py:131-140
+ *        normal_loss = lambda_normal * mean(1 - sum_c rend_normal_c * surf_normal_c),  dist_loss = lambda_dist * mean(rend_dist)
+ *      AND their autograd backward: dL_dallmap[7,H,W] = grad_scale * d(normal_loss + dist_loss)/d(allmap), overwritten.
+ *      Per-camera constants (host floats): ray_matrix (row-major 3x3, ray_dir(x, y) = [x y 1] * ray_matrix, i.e.
+ *      intrins.inverse().T @ c2w[:3,:3].T of point_utils.py:21), ray_origin (c2w[:3,3]), view_rotation
+ *      (world_view_transform[:3,:3] as stored).  Optional outputs may be NULL.  One deviation: where alpha == 0 torch's
+ *      backward of D/alpha yields 0/0 = NaN (pixels nothing was blended into, which no surfel reads); here 0 is written. */
+typedef struct gsm_regularizer_args {
+  const float* allmap; /* [7,H,W] device */
+  int H, W;
+  float ray_matrix[9];
+  float ray_origin[3];
+  float view_rotation[9];
+  float depth_ratio, lambda_normal, lambda_dist, grad_scale;
+  float* loss_out;     /* device [3]: normal_loss + dist_loss, normal_loss, dist_loss (may be NULL) */
+  float* dL_dallmap;   /* device [7,H,W] */
+  float* rend_normal;  /* optional device [3,H,W]: render_pkg["rend_normal"] */
+  float* surf_normal;  /* optional device [3,H,W]: render_pkg["surf_normal"] */
+  float* surf_depth;   /* optional device [H,W]:   render_pkg["surf_depth"] */
+  void* workspace;     /* gsm_surface_regularizer_workspace_bytes(H, W) */
+  size_t workspace_bytes;
+} gsm_regularizer_args;
+size_t gsm_surface_regularizer_workspace_bytes(int H, int W);
+int gsm_surface_regularizer(const gsm_regularizer_args* args, void* stream);
 
 /* ---- markVisible: replaces CudaRasterizer::Rasterizer::markVisible (rasterizer.h:24-31,
  *      rasterizer_impl.cu:141-153; rasterize_points.cu:235-254).  present is uint8[P]. */

@@ -497,6 +497,34 @@ def adam_leg(wl, impl, reps=10):
     return out
 
 
+def regularizer_leg(arm, wl, reps=20):
+    """The allmap regularisers of the iteration (render() post-processing + depth_to_normal + train.py:131-140), value +
+    gradient w.r.t. allmap, on a rendered allmap of the workload: each arm's own implementation, CUDA events
+    (SURVEY.md 8f row 4).  compulsory bytes: read 7 maps, write 7 gradient maps = 56 B per pixel."""
+    cam_d, cam_h = wl["cams_d"][0], wl["cams"][0]
+    allmap = arm.render(cam_d)[2].detach().contiguous()
+    cam = cam_h if arm.name == "ours" else cam_d
+
+    def once():
+        x = allmap.detach().requires_grad_(True)
+        loss = arm.regularizer(x, cam, DEPTH_RATIO, LAMBDA_NORMAL, LAMBDA_DIST)
+        loss.backward()
+        return loss, x.grad
+    for _ in range(3):
+        once()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        loss, grad = once()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    n = wl["H"] * wl["W"]
+    return {"ms": ms, "pixels": n, "calls": reps, "compulsory_gbs": 56.0 * n / (ms * 1e-3) / 1e9,
+            "loss": float(loss.detach()), "grad_checksum": float(torch.nan_to_num(grad, 0.0, 0.0, 0.0).double().abs().sum())}
+
+
 def loss_leg(wl, photometric, reps=20):
     """The photometric loss of the iteration (train.py:113-114), value + gradient w.r.t. the image, at the
     workload's resolution: each arm's own implementation (fused gsm_photometric_loss / the reference's torch ops),
@@ -643,10 +671,19 @@ def main():
         def train_step(s):
             e2e_step(s)
             opt.step()
+        if args.impl == "ours":
+            _lib.stage_timing_enable(True)
+            _lib.stage_timing_read(reset=True)
         ms_train = timed_loop(train_step, args.steps, 3, world, rank)
+        train_stages = None
+        if args.impl == "ours":
+            train_stages = {k: v[0] / args.steps for k, v in _lib.stage_timing_read(reset=True).items() if v[1]}
+            _lib.stage_timing_enable(False)
         train_iter = {"value": 1000.0 * args.steps / ms_train, "unit": UNIT, "ms_per_step": ms_train / args.steps,
                       "includes": "H2D of camera + ground truth, render, L1+SSIM+regulariser loss, backward, loss read-back, "
                                   "Adam step over all 58 floats/surfel"}
+        if train_stages:
+            train_iter["stages_ms_per_step"] = train_stages
         del opt
 
     if rank != 0:
@@ -691,6 +728,8 @@ def main():
             if hasattr(arm, "photometric"):
                 line["loss"] = loss_leg(wl, arm.photometric)
             line["adam"] = adam_leg(wl, "reference")
+            if hasattr(arm, "regularizer"):
+                line["regularizer"] = regularizer_leg(arm, wl)
         print(json.dumps(line))
         return 0
 
@@ -732,6 +771,7 @@ def main():
         line["knn"] = knn_leg(wl, "ours")
         line["loss"] = loss_leg(wl, arm.photometric)
         line["adam"] = adam_leg(wl, "ours")
+        line["regularizer"] = regularizer_leg(arm, wl)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(int(wc["E_bwd"]), wl["deg"])
     print(json.dumps(line))

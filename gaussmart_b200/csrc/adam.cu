@@ -40,15 +40,35 @@ struct AdamBatch {
   int count;
 };
 
+// IEEE division and square root, same results as __fdiv_rn / __fsqrt_rn, without their slow paths on the operands
+// this kernel meets all the time: surfels that no view has touched yet have grad = m = v = 0 and barely visible ones
+// have denormal second moments; the library routines branch to a subroutine for zero / denormal operands, and one
+// such lane stalls its warp (measured: 2.2 ms instead of 1.24 ms per step with 30 % zero rows).  Zero is answered
+// directly, tiny operands are scaled by an exact power of two into the normal range and the result scaled back.
+__device__ __forceinline__ float sqrt_guarded(float v) {
+  const bool zero = v == 0.0f, tiny = v < 5.4210109e-20f;                     // 2^-64
+  const float in = zero ? 1.0f : (tiny ? v * 1.8446744e19f : v);              // * 2^64, exact
+  const float r = __fsqrt_rn(in);
+  return zero ? 0.0f : (tiny ? r * 2.3283064e-10f : r);                       // * 2^-32, exact
+}
+__device__ __forceinline__ float div_guarded(float a, float b) {
+  const float ab = fabsf(b), aa = fabsf(a);
+  if (!(ab >= 1.0e-30f && ab <= 1.0e30f && aa <= 1.0e30f)) return __fdiv_rn(a, b);  // exotic operands: library path
+  const bool zero = aa == 0.0f, tiny = aa < 5.4210109e-20f;
+  const float in = zero ? 1.0f : (tiny ? a * 1.8446744e19f : a);
+  const float q = __fdiv_rn(in, b);
+  return zero ? 0.0f : (tiny ? q * 5.4210109e-20f : q);  // (a quotient below 2^-126 is rounded twice: beyond fp32 += reach)
+}
+
 __device__ __forceinline__ void adam_update(float& p, float g, float& m, float& v, const AdamTensor& t) {
   // lerp with |w| < 0.5: m + w (g - m); with w >= 0.5: g - (g - m)(1 - w)        (ATen/native/Lerp.h)
   const float diff = __fsub_rn(g, m);
   m = (fabsf(t.w1) < 0.5f) ? __fmaf_rn(t.w1, diff, m) : __fsub_rn(g, __fmul_rn(diff, __fsub_rn(1.0f, t.w1)));
   // _foreach_mul_(beta2) then _foreach_addcmul_(g, g, 1 - beta2): v*b2 + w2*(g*g)   (ForeachPointwiseOp.cu)
   v = __fmaf_rn(t.w2, __fmul_rn(g, g), __fmul_rn(v, t.beta2));
-  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), t.bc2_sqrt), t.eps);
+  const float denom = __fadd_rn(div_guarded(sqrt_guarded(v), t.bc2_sqrt), t.eps);
   // addcdiv_(m, denom, value = neg_step): p + neg_step * (m / denom)
-  p = __fmaf_rn(t.neg_step, __fdiv_rn(m, denom), p);
+  p = __fmaf_rn(t.neg_step, div_guarded(m, denom), p);
 }
 
 __global__ void __launch_bounds__(ADAM_THREADS) adam_step_kernel(const __grid_constant__ AdamBatch b) {

@@ -33,9 +33,11 @@ def set_grads(ga, gb, seed, sparsity=0.3):
     g = torch.Generator(device="cpu").manual_seed(seed)
     for a, b in zip(ga, gb):
         pa, pb = a["params"][0], b["params"][0]
-        grad = torch.randn(pa.shape, generator=g).cuda() * (10.0 ** float(torch.randint(-6, 1, (1,), generator=g)))
+        # magnitudes down to where g*g and the second moment are denormal (barely visible surfels)
+        grad = torch.randn(pa.shape, generator=g).cuda() * (10.0 ** float(torch.randint(-22, 1, (1,), generator=g)))
         invisible = (torch.rand(pa.shape[0], generator=g) < sparsity).cuda()
         grad[invisible] = 0.0  # surfels outside the view: zero gradient, still updated by their momentum
+        grad[: pa.shape[0] // 10] = 0.0  # surfels no view has touched yet: grad = exp_avg = exp_avg_sq = 0 throughout
         pa.grad, pb.grad = grad.clone(), grad.clone()
 
 

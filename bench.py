@@ -188,7 +188,7 @@ class OursArm:
                                                                                 fused_stats=True),
             fused_stats=True)
 
-    def api_step(self, cam_d, gt, cam_h=None):
+    def api_step(self, cam_d, gt, cam_h=None, gt_ready=None):
         """Public API: GaussianRasterizationSettings / GaussianRasterizer + autograd (gr.py:37-97 shape)."""
         from gaussmart_b200 import synthetic
         gb = self.gb
@@ -200,6 +200,8 @@ class OursArm:
         color, radii, allmap = gb.GaussianRasterizer(S)(
             means3D=L["means3D"], means2D=self.means2D, opacities=L["opacities"], shs=L["shs"], scales=L["scales"],
             rotations=L["rotations"])
+        if gt_ready is not None:
+            gt_ready()   # the ground-truth upload runs on a copy stream under the render
         loss = loss_fn(color, allmap, gt, cam_d if cam_h is None else cam_h, self.photometric, self.regularizer)
         loss.backward()
         return loss
@@ -214,7 +216,7 @@ class OursArm:
                 means3D=L["means3D"], means2D=self.means2D, opacities=L["opacities"], shs=L["shs"], scales=L["scales"],
                 rotations=L["rotations"])
 
-    def api_step_view_parallel(self, cams_step, gt, cam_h=None):
+    def api_step_view_parallel(self, cams_step, gt, cam_h=None, gt_ready=None):
         """N > 1: the public multi-GPU call, view_parallel_step_factored, with the loss of train.py's shape
         differentiated w.r.t. the rendered maps inside cotangent_fn (same work as api_step per rank)."""
         from gaussmart_b200.rasterizer import rasterize_into_bucket
@@ -223,6 +225,8 @@ class OursArm:
         def cot(v, color, allmap):
             c = color.detach().requires_grad_(True)
             a = allmap.detach().requires_grad_(True)
+            if gt_ready is not None:
+                gt_ready()
             loss = loss_fn(c, a, gt, cams_step[self.rank] if cam_h is None else cam_h, self.photometric, self.regularizer)
             loss.backward()
             box["loss"] = loss.detach()
@@ -273,8 +277,10 @@ class ReferenceArm:
         color, radii, allmap = self._render(self.wl["cams_d"][view])
         torch.autograd.backward([color, allmap], [self.wl["cot_d"][0], self.wl["cot_d"][1]])
 
-    def api_step(self, cam_d, gt, cam_h=None):
+    def api_step(self, cam_d, gt, cam_h=None, gt_ready=None):
         color, radii, allmap = self._render(cam_d)
+        if gt_ready is not None:
+            gt_ready()
         loss = loss_fn(color, allmap, gt, cam_d, self.photometric, self.regularizer)
         loss.backward()
         return loss
@@ -628,9 +634,16 @@ def main():
         loss_host = torch.empty((), dtype=torch.float32).pin_memory()
         from gaussmart_b200 import synthetic
 
+        copy_stream = torch.cuda.Stream(device=device)
+        gt_ready = lambda: torch.cuda.current_stream().wait_stream(copy_stream)
+
         def e2e_step(s):
             v = view_of(s)
-            gt_dev.copy_(wl["gt_host"][s % 2], non_blocking=True)
+            # this step's ground truth goes up on a copy stream while the render runs (the loss waits for it); the previous
+            # step ended with a blocking read of its loss, so gt_dev is free.  The camera is needed at once: main stream.
+            copy_stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(copy_stream):
+                gt_dev.copy_(wl["gt_host"][s % 2], non_blocking=True)
             mats_dev.copy_(mats_host[v], non_blocking=True)
             c = wl["cams"][v]
             cam_d = synthetic.Camera(c.image_width, c.image_height, c.FoVx, c.FoVy, c.tanfovx, c.tanfovy,
@@ -638,16 +651,17 @@ def main():
             if world > 1 and args.impl == "ours":
                 base = (v - rank) % N_VIEWS
                 cams_step = [cam_d if r == rank else wl["cams_d"][(base + r) % N_VIEWS] for r in range(world)]
-                loss = arm.api_step_view_parallel(cams_step, gt_dev, cam_h=c)
+                loss = arm.api_step_view_parallel(cams_step, gt_dev, cam_h=c, gt_ready=gt_ready)
             else:
-                loss = arm.api_step(cam_d, gt_dev, cam_h=c)
+                loss = arm.api_step(cam_d, gt_dev, cam_h=c, gt_ready=gt_ready)
             loss_host.copy_(loss.detach(), non_blocking=False)   # the per-iteration .item() of train.py:149
 
         ms_e2e = timed_loop(e2e_step, args.steps, max(3, args.warmup), world, rank)
         e2e = {"value": world * 1000.0 * args.steps / ms_e2e, "unit": UNIT,
                "h2d_bytes_per_step": int(3 * H * W * 4 + 35 * 4), "d2h_bytes_per_step": 4,
                "ms_per_step": ms_e2e / args.steps,
-               "api": "GaussianRasterizationSettings/GaussianRasterizer + loss.backward()"}
+               "api": "GaussianRasterizationSettings/GaussianRasterizer + train.py's loss (L1+SSIM, normal, distortion; each "
+                      "arm's own implementation: fused kernels here, the reference's torch ops there) + loss.backward()"}
 
     render = None
     if not args.no_render:

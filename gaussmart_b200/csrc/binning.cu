@@ -386,6 +386,19 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
         // keep only the blocks that meet the surfel's diagonal slabs (cull record: bounds of x+y and x-y over
         // its contribution region, slack included): with the box this bounds the region by an octagon
         const float4 dg = __ldg(p.cull + e.y);
+#if GSM_BLOCK_W == 8
+        // 2 x 4 blocks of 8 x 4 pixels: block (bx, by) sits on the diagonals u = 2bx + by (x+y = s + 4u) and
+        // v = 2bx - by (x-y = d + 4v), so each slab bound is a range of u or v and the four tests
+        //   x1+y1 = s+4u+10 >= dg.x,  x0+y0 = s+4u <= dg.y,  x1-y0 = d+4v+7 >= dg.z,  x0-y1 = d+4v-3 <= dg.w
+        // become four table lookups (one byte per threshold: the blocks on the right side of it) -- no loop over blocks
+        const float s = (float)(tx + ty), d = (float)(tx - ty);
+        const int ulo = (int)fminf(fmaxf(ceilf((dg.x - 10.0f - s) * 0.25f), 0.0f), 6.0f);
+        const int uhi = (int)fminf(fmaxf(floorf((dg.y - s) * 0.25f), -1.0f), 5.0f);
+        const int vlo = (int)fminf(fmaxf(ceilf((dg.z - 7.0f - d) * 0.25f), -3.0f), 3.0f);
+        const int vhi = (int)fminf(fmaxf(floorf((dg.w + 3.0f - d) * 0.25f), -4.0f), 2.0f);
+        mask &= (uint32_t)((0x80a0e8fafeffull >> (8 * ulo)) & (0xff7f5f17050100ull >> (8 * (uhi + 1))) &
+                           (0x20a2bafbfffull >> (8 * (vlo + 3))) & (0xfffdf5d4504000ull >> (8 * (vhi + 4)))) & 0xffu;
+#else
         uint32_t keep = 0;
         for (uint32_t rest = mask; rest; rest &= rest - 1u) {
           const int b = __ffs(rest) - 1;
@@ -394,6 +407,7 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
           if (x1 + y1 >= dg.x && x0 + y0 <= dg.y && x1 - y0 >= dg.z && x0 - y1 <= dg.w) keep |= 1u << b;
         }
         mask = keep;
+#endif
       }
     }
     p.strip_mask[range.x + i] = (uint8_t)mask;

@@ -264,7 +264,8 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     rp.point_list = bin ? (const uint32_t*)(bin + B.point_list) : nullptr;
     rp.records = records; rp.background = a->background;
     rp.strip_mask = bin ? (uint8_t*)(bin + B.strip_mask) : nullptr;
-    rp.pix_mask = bin ? (uint32_t*)(bin + B.pix_mask) : nullptr; rp.pix_plane = a->binning_capacity;
+    // debug bit 2: inference render, no backward will follow -> the forward skips the hand-over (no per-entry pixel sets)
+    rp.pix_mask = (bin && !(a->debug & 4)) ? (uint32_t*)(bin + B.pix_mask) : nullptr; rp.pix_plane = a->binning_capacity;
     rp.bbox = (const short4*)(geom + G.bbox); rp.no_cull = (a->debug & 2) ? 1 : 0;
     rp.final_T = (float*)(img + I.final_T); rp.n_contrib = (uint32_t*)(img + I.n_contrib);
     rp.out_color = a->out_color; rp.out_others = a->out_others;

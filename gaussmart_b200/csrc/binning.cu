@@ -39,48 +39,54 @@ constexpr int TSCAN_THREADS = 1024;
 __global__ void __launch_bounds__(TSCAN_THREADS)
 tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_cursor,
                  uint2* __restrict__ ranges, int num_tiles, unsigned long long* __restrict__ total_out) {
-  __shared__ unsigned long long warp_sums[TSCAN_THREADS / 32];
+  // one CTA walks the tiles in chunks of TSCAN_THREADS, one tile (TILE_SUBS counters = 32 B) per thread and chunk, so
+  // every access is coalesced; the next chunk's counters are requested before the current chunk is scanned
+  __shared__ unsigned long long warp_sums[2][TSCAN_THREADS / 32];
+  static_assert(TILE_SUBS == 8, "a tile's counters are read as two uint4");
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const int per = (num_tiles + TSCAN_THREADS - 1) / TSCAN_THREADS;
-  const int begin = min(t * per, num_tiles), end = min(begin + per, num_tiles);
-  unsigned long long local = 0;
-  static_assert(TILE_SUBS % 4 == 0, "tile counters are read as uint4");
   const uint4* cnt4 = reinterpret_cast<const uint4*>(tile_count);
-  for (int i = begin * (TILE_SUBS / 4); i < end * (TILE_SUBS / 4); i++) {
-    const uint4 c = __ldg(cnt4 + i);
-    local += (unsigned long long)c.x + c.y + c.z + c.w;
-  }
-  unsigned long long inc = local;
+  uint4* cur4 = reinterpret_cast<uint4*>(tile_cursor);
+  const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+  unsigned long long carry = 0;
+  uint4 n0 = zero, n1 = zero;
+  if (t < num_tiles) { n0 = __ldg(cnt4 + 2 * (size_t)t); n1 = __ldg(cnt4 + 2 * (size_t)t + 1); }
+  int buf = 0;
+  for (int base = 0; base < num_tiles; base += TSCAN_THREADS, buf ^= 1) {
+    const int i = base + t;
+    const uint4 c0 = n0, c1 = n1;
+    const int nxt = i + TSCAN_THREADS;
+    n0 = zero; n1 = zero;
+    if (nxt < num_tiles) { n0 = __ldg(cnt4 + 2 * (size_t)nxt); n1 = __ldg(cnt4 + 2 * (size_t)nxt + 1); }
+    const unsigned long long local = (unsigned long long)c0.x + c0.y + c0.z + c0.w + c1.x + c1.y + c1.z + c1.w;
+    unsigned long long inc = local;
 #pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += v;
-  }
-  if (lane == 31) warp_sums[warp] = inc;
-  __syncthreads();
-  unsigned long long warp_off = 0, total = 0;
-  for (int w = 0; w < TSCAN_THREADS / 32; w++) {
-    const unsigned long long s = warp_sums[w];
-    if (w < warp) warp_off += s;
-    total += s;
-  }
-  unsigned long long run = warp_off + inc - local;
-  for (int i = begin; i < end; i++) {
-    const unsigned long long first = run;
-    uint4* cur4 = reinterpret_cast<uint4*>(tile_cursor) + (size_t)i * (TILE_SUBS / 4);
-#pragma unroll
-    for (int k = 0; k < TILE_SUBS / 4; k++) {
-      const uint4 c = __ldg(cnt4 + (size_t)i * (TILE_SUBS / 4) + k);
-      uint4 o;  // absolute slot of each sub-segment's next pair
-      o.x = (uint32_t)run; run += c.x;
-      o.y = (uint32_t)run; run += c.y;
-      o.z = (uint32_t)run; run += c.z;
-      o.w = (uint32_t)run; run += c.w;
-      cur4[k] = o;
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += v;
     }
-    ranges[i] = run > first ? make_uint2((uint32_t)first, (uint32_t)run) : make_uint2(0u, 0u);
+    if (lane == 31) warp_sums[buf][warp] = inc;
+    __syncthreads();  // (double-buffered sums: one barrier per chunk)
+    unsigned long long warp_off = 0, total = 0;
+    for (int w = 0; w < TSCAN_THREADS / 32; w++) {
+      const unsigned long long s = warp_sums[buf][w];
+      if (w < warp) warp_off += s;
+      total += s;
+    }
+    if (i < num_tiles) {
+      unsigned long long run = carry + warp_off + inc - local;
+      const unsigned long long first = run;
+      uint4 o;  // absolute slot of each sub-segment's next pair
+      o.x = (uint32_t)run; run += c0.x; o.y = (uint32_t)run; run += c0.y;
+      o.z = (uint32_t)run; run += c0.z; o.w = (uint32_t)run; run += c0.w;
+      cur4[2 * (size_t)i] = o;
+      o.x = (uint32_t)run; run += c1.x; o.y = (uint32_t)run; run += c1.y;
+      o.z = (uint32_t)run; run += c1.z; o.w = (uint32_t)run; run += c1.w;
+      cur4[2 * (size_t)i + 1] = o;
+      ranges[i] = run > first ? make_uint2((uint32_t)first, (uint32_t)run) : make_uint2(0u, 0u);
+    }
+    carry += total;
   }
-  if (t == 0) *total_out = total;
+  if (t == 0) *total_out = carry;
 }
 
 void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* ranges, int num_tiles,

@@ -43,7 +43,8 @@ struct FwdWarpSmem {
   float cut[FWD_CHUNK];            // per staged entry: upper bound of rho for alpha >= 1/255 (pre-test below)
 };
 
-template <bool STATS>
+// HANDOVER: collect what the backward needs (per-entry pixel sets, dead block bits); false for inference renders
+template <bool STATS, bool HANDOVER>
 __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRenderParams p) {
   __shared__ __align__(16) FwdWarpSmem smem_all[FWD_WARPS];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -117,7 +118,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
     const float4* __restrict__ q4 = sm.q[s][4];
     const uint32_t* __restrict__ qpos = sm.pos[s];
     bool all_done = false;
-    sm.hit[lane] = 0u;
+    if (HANDOVER) sm.hit[lane] = 0u;
     // alpha = min(0.99, o exp(-rho/2)) >= 1/255 needs rho <= 2 ln(255 o); 0.1 % + 1e-3 covers every rounding of
     // the exact evaluation below (expf, the products, the two divisions: a few ulp).  Negative for o < 1/255.
     if (lane < n_cur) sm.cut[lane] = p.no_cull ? 3.0e38f : FMA(2.0f * __logf(255.0f * q2[lane].w), 1.001f, 1.0e-3f);
@@ -173,7 +174,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
       C0 = FMA(w, col.x, C0); C1 = FMA(w, col.y, C1); C2 = FMA(w, col.z, C2);
       T = test_T;
       last_contributor = contributor;
-      atomicOr(&sm.hit[j], 1u << lane);
+      if (HANDOVER) atomicOr(&sm.hit[j], 1u << lane);
       if (STATS) n_contributing++;
     }
     // Hand the backward pass what this pass found out.  The backward's activity test of a pair is this kernel's
@@ -183,7 +184,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
     //  * for the others the 32-bit set of blending pixels is stored (pix_mask[block][entry]): the backward walks,
     //    per pixel, exactly its own contributors.
     // Only this warp reads this bit / writes this word, and it is past these entries.
-    {
+    if (HANDOVER) {
       __syncwarp();
       const uint32_t my_mask = sm.hit[lane];  // lane j: the pixels that blended entry j
       if (lane < n_cur) {
@@ -237,8 +238,9 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
 void launch_render_fwd(const FwdRenderParams& p, cudaStream_t stream) {
   const unsigned strips = (unsigned)(p.grid_x * p.grid_y) * STRIPS_PER_TILE;
   const unsigned grid = (strips + FWD_WARPS - 1) / FWD_WARPS;
-  if (p.stats) render_fwd_kernel<true><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
-  else render_fwd_kernel<false><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
+  if (p.stats) render_fwd_kernel<true, true><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
+  else if (p.pix_mask == nullptr) render_fwd_kernel<false, false><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
+  else render_fwd_kernel<false, true><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
 }
 
 }  // namespace gsm

@@ -61,9 +61,10 @@ class _Workspaces(NamedTuple):
 
 def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3Ds_precomp,
                   viewmatrix, projmatrix, tanfovx, tanfovy, image_height, image_width, sh, sh_degree, campos,
-                  prefiltered, debug, work_counters=None):
+                  prefiltered, debug, work_counters=None, forward_only=False):
     """Equivalent of RasterizeGaussiansCUDA (rasterize_points.cu:39-134).
-    work_counters: optional zeroed int64[4] CUDA tensor receiving work counts (bench only)."""
+    work_counters: optional zeroed int64[4] CUDA tensor receiving work counts (bench only).
+    forward_only: inference render (no backward will follow): sets debug bit 2 of the C ABI."""
     lib = _lib.load()
     if means3D.ndim != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
@@ -99,7 +100,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
         a = _lib.ForwardArgs()
         a.P, a.D, a.M, a.width, a.height = P, int(sh_degree), M, W, H
         a.tan_fovx, a.tan_fovy, a.scale_modifier = float(tanfovx), float(tanfovy), float(scale_modifier)
-        a.prefiltered, a.debug = int(bool(prefiltered)), int(debug)
+        a.prefiltered, a.debug = int(bool(prefiltered)), int(debug) | (4 if forward_only else 0)
         a.background, a.means3D, a.shs, a.colors_precomp = _ptr(bg), _ptr(means3D), _ptr(sh), _ptr(colors_precomp)
         a.opacities, a.scales, a.rotations = _ptr(opacities), _ptr(scales), _ptr(rotations)
         a.transMat_precomp = _ptr(cov3Ds_precomp)
@@ -206,6 +207,16 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
+    inputs = (means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
+    if not (torch.is_grad_enabled() and any(isinstance(t, torch.Tensor) and t.requires_grad for t in inputs)):
+        # inference (render.py, torch.no_grad): autograd would record nothing, so the forward runs without the
+        # forward->backward hand-over
+        rs = raster_settings
+        _, color, depth, radii, _, _, _ = _forward_impl(
+            rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos,
+            rs.prefiltered, rs.debug, forward_only=True)
+        return color, radii, depth
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
                                      cov3Ds_precomp, raster_settings)
 

@@ -86,7 +86,10 @@ typedef struct gsm_forward_args {
   int prefiltered;   /* kept for API parity; a culled surfel with prefiltered set is an error flag */
   int debug;         /* bit 0: synchronise + check after every stage (auxiliary.h:296-303);
                         bit 1: disable the conservative per-warp culling in the compositing kernels
-                        (every (pixel, list entry) pair is evaluated, as the reference does) */
+                        (every (pixel, list entry) pair is evaluated, as the reference does);
+                        bit 2: inference render (render.py, torch.no_grad): no backward will follow, so the
+                        compositing kernel skips what it would hand to gsm_backward; calling gsm_backward on
+                        the buffers of such a forward is invalid (undefined gradients) */
   const float* background;       /* [3] */
   const float* means3D;          /* [P,3] */
   const float* shs;              /* [P,M,3] or NULL */

@@ -383,3 +383,23 @@ def test_factored_sh_gradient_matches_dense_path(P, deg):
             assert torch.equal(g["shs"][:, 0], dc0)
         assert torch.allclose(ex.stats[0], dense.stats[0], rtol=1e-4, atol=1e-7) and torch.equal(ex.stats[1], dense.stats[1])
         assert torch.equal(ex.max_radii, dense.max_radii)
+
+
+def test_inference_render_equals_training_forward():
+    """debug bit 2 (forward_only: torch.no_grad / no input requires grad) skips the forward->backward hand-over and must
+    not change a single output bit."""
+    import gaussmart_b200 as gb
+    W, H, deg = 200, 150, 3
+    scene = synthetic.make_scene(20000, W, deg, 77)
+    scene = scene._replace(scales=scene.scales * 3.0)
+    cam = synthetic.make_camera(W, H, 0.4)
+    cam_d = synthetic.Camera(*[x.cuda() if isinstance(x, torch.Tensor) else x for x in cam])
+    S = gb.GaussianRasterizationSettings(**synthetic.settings_kwargs(cam_d, deg, torch.zeros(3).cuda()))
+    tensors = dict(means3D=scene.means3D.cuda(), opacities=scene.opacities.cuda(), shs=scene.shs.cuda(),
+                   scales=scene.scales.cuda(), rotations=scene.rotations.cuda())
+    with torch.no_grad():
+        c0, r0, a0 = gb.GaussianRasterizer(S)(means2D=torch.zeros_like(tensors["means3D"]), **tensors)
+    leaves = {k: v.clone().requires_grad_(True) for k, v in tensors.items()}
+    c1, r1, a1 = gb.GaussianRasterizer(S)(means2D=torch.zeros_like(tensors["means3D"], requires_grad=True), **leaves)
+    assert c1.requires_grad and not c0.requires_grad
+    assert torch.equal(c0, c1.detach()) and torch.equal(r0, r1) and torch.equal(a0, a1.detach())

@@ -17,7 +17,7 @@ GSM_ERR_BINNING_OVERFLOW = 10002
 GSM_ERR_WORKSPACE_TOO_SMALL = 10003
 GSM_SURFEL_RECORD_BYTES = 80
 GSM_GRAD_RECORD_FLOATS = 20
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 EXPORTS = [
     "gsm_last_error", "gsm_abi_version", "gsm_geometry_bytes", "gsm_image_bytes", "gsm_binning_bytes", "gsm_binning_persistent_bytes",
@@ -57,6 +57,7 @@ class ForwardArgs(Structure):
         ("image", c_void_p), ("image_bytes", c_size_t),
         ("binning", c_void_p), ("binning_bytes", c_size_t), ("binning_capacity", c_size_t),
         ("num_rendered_host", POINTER(c_int)), ("work_counters", c_void_p),
+        ("shs_rest", c_void_p), ("raw_params", c_int),
     ]
 
 
@@ -75,6 +76,7 @@ class BackwardArgs(Structure):
         ("dL_dscales", c_void_p), ("dL_drotations", c_void_p), ("accumulate", c_int),
         ("dL_drgb", c_void_p),
         ("densify_grad_norm", c_void_p), ("densify_visible", c_void_p), ("max_radii", c_void_p),
+        ("shs_rest", c_void_p), ("dL_dsh_rest", c_void_p), ("opacities", c_void_p), ("raw_params", c_int),
     ]
 
 

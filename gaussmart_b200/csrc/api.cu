@@ -207,6 +207,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     pp.scale_modifier = a->scale_modifier; pp.prefiltered = a->prefiltered;
     pp.means3D = a->means3D; pp.scales = a->scales; pp.rotations = a->rotations; pp.opacities = a->opacities;
     pp.shs = a->shs; pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;
+    pp.shs_rest = a->shs ? a->shs_rest : nullptr; pp.raw = a->raw_params ? 1 : 0;
     pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
     pp.radii = a->radii; pp.records = records; pp.bbox = (short4*)(geom + G.bbox); pp.cull = (float4*)(geom + G.cull); pp.clamp = (uint8_t*)(geom + G.clamp); pp.rects = (uint4*)(geom + G.rects); pp.tile_count = tile_count; pp.flags = flags;
     { StageMark m(GSM_STAGE_PREPROCESS_FWD, stream); launch_preprocess_fwd(pp, stream); }
@@ -334,6 +335,11 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   pp.dL_dmeans3D = a->dL_dmeans3D; pp.dL_dtransMat = a->dL_dtransMat; pp.dL_dsh = a->dL_dsh;
   pp.dL_dscales = a->dL_dscales; pp.dL_drotations = a->dL_drotations; pp.dL_drgb = a->dL_drgb;
   pp.stat_norm = a->densify_grad_norm; pp.stat_vis = a->densify_visible; pp.max_radii = a->max_radii;
+  pp.shs_rest = a->shs ? a->shs_rest : nullptr; pp.dL_dsh_rest = a->dL_dsh_rest; pp.opacities = a->opacities; pp.raw = a->raw_params ? 1 : 0;
+  if (pp.raw && pp.opacities == nullptr) { set_error("gsm_backward: raw_params needs the raw opacities"); return GSM_ERR_INVALID_ARGUMENT; }
+  if (pp.shs_rest != nullptr && pp.dL_dsh != nullptr && pp.dL_dsh_rest == nullptr && a->M > 1 && a->dL_drgb == nullptr) {
+    set_error("gsm_backward: shs_rest given without dL_dsh_rest"); return GSM_ERR_INVALID_ARGUMENT;
+  }
   { StageMark m(GSM_STAGE_PREPROCESS_BWD, stream); launch_preprocess_bwd(pp, stream); }
   GSM_STAGE("backward preprocess");
   return GSM_OK;

@@ -150,6 +150,23 @@ class StageMark {  // RAII: records a cudaEvent pair around a stage when timing 
   cudaEvent_t a_;
 };
 
+// ---- raw-parameter activations (gaussian_model.py:104-113), evaluated as torch's CUDA kernels evaluate them ----------
+struct ActivatedRotation { float4 q; float norm; };  // norm = max(||raw||, eps)
+__device__ __forceinline__ float2 activate_scaling(float2 s) { return make_float2(expf(s.x), expf(s.y)); }  // torch.exp
+__device__ __forceinline__ float activate_opacity(float x) {  // torch.sigmoid: 1 / (1 + exp(-x))
+  return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x)));
+}
+__device__ __forceinline__ ActivatedRotation activate_rotation(float4 r) {
+  // F.normalize(dim=-1): x / max(||x||_2, 1e-12); torch's row reduction over 4 elements adds the rounded squares as a
+  // shuffle tree, (x0^2 + x2^2) + (x1^2 + x3^2) -- found by tools/activation_probe.py, bit-identical on 1 M rows
+  const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(r.x, r.x), __fmul_rn(r.z, r.z)), __fadd_rn(__fmul_rn(r.y, r.y), __fmul_rn(r.w, r.w)));
+  const float n = fmaxf(__fsqrt_rn(n2), 1e-12f);
+  ActivatedRotation a;
+  a.q = make_float4(__fdiv_rn(r.x, n), __fdiv_rn(r.y, n), __fdiv_rn(r.z, n), __fdiv_rn(r.w, n));
+  a.norm = n;
+  return a;
+}
+
 // ---- stage launchers (one translation unit each) ----------------------------------------
 struct FwdPreprocessParams {
   int P, D, M, W, H;
@@ -161,6 +178,8 @@ struct FwdPreprocessParams {
   const float* rotations;
   const float* opacities;
   const float* shs;
+  const float* shs_rest;  // optional: shs = features_dc [P,1,3], shs_rest = features_rest [P,M-1,3]
+  int raw;                // scales / rotations / opacities are the raw parameters: activated in-kernel
   const float* transMat_precomp;
   const float* colors_precomp;
   const float* viewmatrix;
@@ -253,6 +272,10 @@ struct BwdPreprocessParams {
   float* stat_norm;  // optional [P]: += ||dL_dmeans2D.xy|| of visible surfels
   float* stat_vis;   // optional [P]: += 1 for visible surfels
   int* max_radii;    // optional [P]: max= radii
+  const float* shs_rest;  // optional: split SH storage (see FwdPreprocessParams)
+  float* dL_dsh_rest;     // with shs_rest: dL_dsh = d/d features_dc [P,1,3], dL_dsh_rest = d/d features_rest [P,M-1,3]
+  const float* opacities; // raw mode only: the raw opacities (sigmoid' needs them)
+  int raw;                // gradients are taken w.r.t. the RAW scales / rotations / opacities
 };
 void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream);
 void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,

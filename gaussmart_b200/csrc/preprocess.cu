@@ -108,9 +108,12 @@ constexpr int PFWD_THREADS = 128;
 
 // Cooperative, coalesced load of the SH rows of the warp's visible surfels into shared memory
 // (row r at wsm[r * (3M + 1)]: odd stride, conflict-free per-lane reads).
-__device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict__ g, int M, int rows,
+// (rl floats per source row, landing at column col0 of the shared-memory row of stride rs: the full [P,M,3] tensor is
+// rl = 3M, col0 = 0; split storage (features_dc [P,1,3] + features_rest [P,M-1,3], gaussian_model.py:115-118 without the
+// torch.cat) is two calls, rl = 3 at column 0 and rl = 3M-3 at column 3)
+__device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict__ g, int rl, int rs, int col0, int rows,
                                              unsigned vis_mask, int lane) {
-  const int rl = 3 * M, rs = rl + 1, total = rows * rl;
+  const int total = rows * rl;
   const unsigned rmagic = 0xffffffffu / (unsigned)rl + 1u;  // idx / rl == umulhi(idx, rmagic) for idx < 2^16 (one division per thread instead of one per element)
   if (rows == 32 && (reinterpret_cast<size_t>(g) & 15) == 0) {
     const float4* g4 = reinterpret_cast<const float4*>(g);
@@ -138,14 +141,14 @@ __device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict
 #pragma unroll
         for (int e = 0; e < 4; e++) {
           const int i = e0 + e, r = (int)__umulhi((unsigned)i, rmagic);
-          wsm[r * rs + (i - r * rl)] = vv[e];
+          wsm[r * rs + col0 + (i - r * rl)] = vv[e];
         }
       }
     }
   } else {
     for (int i = lane; i < total; i += 32) {
       const int r = (int)__umulhi((unsigned)i, rmagic);
-      if ((vis_mask >> r) & 1u) wsm[r * rs + (i - r * rl)] = __ldg(g + i);
+      if ((vis_mask >> r) & 1u) wsm[r * rs + col0 + (i - r * rl)] = __ldg(g + i);
     }
   }
 }
@@ -186,7 +189,14 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
     sc_in = __ldg(reinterpret_cast<const float2*>(p.scales) + idx);
     q_in = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
   }
-  const float opac_in = __ldg(p.opacities + idx);
+  float opac_in = __ldg(p.opacities + idx);
+  if (p.raw) {
+    // raw parameters (gaussian_model.py:104-113): scaling_activation = exp, rotation_activation = F.normalize,
+    // opacity_activation = sigmoid, evaluated as torch's CUDA kernels evaluate them
+    sc_in = activate_scaling(sc_in);
+    q_in = activate_rotation(q_in).q;
+    opac_in = activate_opacity(opac_in);
+  }
 
   // p_view = [p 1] * V   (auxiliary.h:79-87), association: m12 + fma(z,m8, fma(x,m0, y*m4))
   const float vx = ADD(vm[12], FMA(pz, vm[8], FMA(px, vm[0], MUL(py, vm[4]))));
@@ -321,7 +331,13 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
   if (p.colors_precomp == nullptr) {
     float* wsm = sh_smem + (size_t)warp * 32 * (3 * p.M + 1);
     if (vis_mask != 0) {
-      sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, p.M, min(32, p.P - warp_first), vis_mask, lane);
+      const int rows = min(32, p.P - warp_first), rs = 3 * p.M + 1;
+      if (p.shs_rest == nullptr) {
+        sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, 3 * p.M, rs, 0, rows, vis_mask, lane);
+      } else {  // features_dc + features_rest, no concatenated copy
+        sh_rows_load(wsm, p.shs + (size_t)warp_first * 3, 3, rs, 0, rows, vis_mask, lane);
+        if (p.M > 1) sh_rows_load(wsm, p.shs_rest + (size_t)warp_first * (p.M - 1) * 3, 3 * p.M - 3, rs, 3, rows, vis_mask, lane);
+      }
       __syncwarp();
     }
     if (visible) {

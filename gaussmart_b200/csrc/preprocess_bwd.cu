@@ -120,9 +120,12 @@ constexpr int PBWD_THREADS = 128;
 // are read and written as fully coalesced 128-bit accesses by the warp instead of 3M scalar accesses
 // per thread at a 12*M-byte stride.  Row r of the warp sits at smem[r * (3M + 1)] (odd stride: the
 // per-lane accesses of the SH polynomial are bank-conflict free).
-__device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict__ g, int M, int rows,
+// (rl floats per source row, landing at column col0 of the shared-memory row of stride rs: the full [P,M,3] tensor is
+// rl = 3M, col0 = 0; split storage (features_dc [P,1,3] + features_rest [P,M-1,3], gaussian_model.py:115-118 without the
+// torch.cat) is two calls, rl = 3 at column 0 and rl = 3M-3 at column 3)
+__device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict__ g, int rl, int rs, int col0, int rows,
                                              unsigned vis_mask, int lane) {
-  const int rl = 3 * M, rs = rl + 1, total = rows * rl;
+  const int total = rows * rl;
   const unsigned rmagic = 0xffffffffu / (unsigned)rl + 1u;  // idx / rl == umulhi(idx, rmagic) for idx < 2^16 (one division per thread instead of one per element)
   if (rows == 32 && (reinterpret_cast<size_t>(g) & 15) == 0) {
     const float4* g4 = reinterpret_cast<const float4*>(g);
@@ -150,21 +153,21 @@ __device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict
 #pragma unroll
         for (int e = 0; e < 4; e++) {
           const int idx = e0 + e, r = (int)__umulhi((unsigned)idx, rmagic);
-          wsm[r * rs + (idx - r * rl)] = vv[e];
+          wsm[r * rs + col0 + (idx - r * rl)] = vv[e];
         }
       }
     }
   } else {
     for (int idx = lane; idx < total; idx += 32) {
       const int r = (int)__umulhi((unsigned)idx, rmagic);
-      if ((vis_mask >> r) & 1u) wsm[r * rs + (idx - r * rl)] = __ldg(g + idx);
+      if ((vis_mask >> r) & 1u) wsm[r * rs + col0 + (idx - r * rl)] = __ldg(g + idx);
     }
   }
 }
 
-__device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restrict__ g, int M, int rows,
+__device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restrict__ g, int rl, int rs, int col0, int rows,
                                               unsigned vis_mask, bool acc, int lane) {
-  const int rl = 3 * M, rs = rl + 1, total = rows * rl;
+  const int total = rows * rl;
   const unsigned rmagic = 0xffffffffu / (unsigned)rl + 1u;  // idx / rl == umulhi(idx, rmagic) for idx < 2^16 (one division per thread instead of one per element)
   if (rows == 32 && (reinterpret_cast<size_t>(g) & 15) == 0) {
     float4* g4 = reinterpret_cast<float4*>(g);
@@ -176,7 +179,7 @@ __device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restric
       for (int e = 0; e < 4; e++) {
         const int idx = e0 + e, r = (int)__umulhi((unsigned)idx, rmagic);
         const bool vis = (vis_mask >> r) & 1u;
-        vv[e] = vis ? wsm[r * rs + (idx - r * rl)] : 0.0f;
+        vv[e] = vis ? wsm[r * rs + col0 + (idx - r * rl)] : 0.0f;
         any |= vis;
       }
       if (acc) {
@@ -191,7 +194,7 @@ __device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restric
     for (int idx = lane; idx < total; idx += 32) {
       const int r = (int)__umulhi((unsigned)idx, rmagic);
       const bool vis = (vis_mask >> r) & 1u;
-      const float v = vis ? wsm[r * rs + (idx - r * rl)] : 0.0f;
+      const float v = vis ? wsm[r * rs + col0 + (idx - r * rl)] : 0.0f;
       if (acc) { if (vis) g[idx] += v; }
       else g[idx] = v;
     }
@@ -228,7 +231,12 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
     pos = mk(__ldg(p.means3D + 3 * i), __ldg(p.means3D + 3 * i + 1), __ldg(p.means3D + 3 * i + 2));
   }
   if (has_sh) {
-    sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, p.M, rows, vis_mask, lane);
+    if (p.shs_rest == nullptr) {
+      sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, 3 * p.M, 3 * p.M + 1, 0, rows, vis_mask, lane);
+    } else {
+      sh_rows_load(wsm, p.shs + (size_t)warp_first * 3, 3, 3 * p.M + 1, 0, rows, vis_mask, lane);
+      if (p.M > 1) sh_rows_load(wsm, p.shs_rest + (size_t)warp_first * (p.M - 1) * 3, 3 * p.M - 3, 3 * p.M + 1, 3, rows, vis_mask, lane);
+    }
     __syncwarp();
   }
 
@@ -263,6 +271,7 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
     float Pm[3][4];           // P[k][r] = (world2ndc * ndc2pix)[k][r]
     float2 sc = make_float2(0, 0);
     float4 q = make_float4(0, 0, 0, 0);
+    float raw_norm = 1.0f;
     if (precomp) {
       const float* T = p.transMat_precomp + 9 * i;
       T0 = mk(__ldg(T + 0), __ldg(T + 1), __ldg(T + 2));
@@ -271,6 +280,12 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
     } else {
       sc = __ldg(reinterpret_cast<const float2*>(p.scales) + idx);
       q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+      if (p.raw) {  // the forward's activations (common.cuh), re-evaluated
+        sc = activate_scaling(sc);
+        const ActivatedRotation ar = activate_rotation(q);
+        q = ar.q;
+        raw_norm = ar.norm;
+      }
       const float s = rsqrtf(q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z);
       const float w = q.x * s, x = q.y * s, y = q.z * s, z = q.w * s;
       R0 = mk(1.f - 2.f * (y * y + z * z), 2.f * (x * y + w * z), 2.f * (x * z - w * y));
@@ -355,6 +370,19 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
       dscale_x = dot(dRS0, R0);
       dscale_y = dot(dRS1, R1);
       dmean3D = dM[2];
+      if (p.raw) {
+        // chain through the activations: exp' = exp; normalize: (g - q (q.g)) / max(||raw||, eps) (the clamp's own
+        // derivative is zero); sigmoid' = o (1 - o)
+        dscale_x *= sc.x; dscale_y *= sc.y;
+        const float qg = q.x * drot.x + q.y * drot.y + q.z * drot.z + q.w * drot.w;
+        const float inv = 1.0f / raw_norm;
+        if (raw_norm > 1e-12f) drot = make_float4((drot.x - q.x * qg) * inv, (drot.y - q.y * qg) * inv, (drot.z - q.z * qg) * inv, (drot.w - q.w * qg) * inv);
+        else drot = make_float4(drot.x * inv, drot.y * inv, drot.z * inv, drot.w * inv);
+      }
+    }
+    if (p.raw) {
+      const float o = activate_opacity(__ldg(p.opacities + i));
+      dopacity *= o * (1.0f - o);
     }
 
     if (has_sh) {
@@ -382,7 +410,12 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
     if (valid) store3(p.dL_drgb + 3 * i, drgb_masked);  // per view: never accumulated
   } else if (has_sh) {
     __syncwarp();
-    sh_rows_store(wsm, p.dL_dsh + (size_t)warp_first * p.M * 3, p.M, rows, vis_mask, acc, lane);
+    if (p.dL_dsh_rest == nullptr) {
+      sh_rows_store(wsm, p.dL_dsh + (size_t)warp_first * p.M * 3, 3 * p.M, 3 * p.M + 1, 0, rows, vis_mask, acc, lane);
+    } else {  // gradients of features_dc and features_rest, no concatenated gradient to slice afterwards
+      sh_rows_store(wsm, p.dL_dsh + (size_t)warp_first * 3, 3, 3 * p.M + 1, 0, rows, vis_mask, acc, lane);
+      if (p.M > 1) sh_rows_store(wsm, p.dL_dsh_rest + (size_t)warp_first * (p.M - 1) * 3, 3 * p.M - 3, 3 * p.M + 1, 3, rows, vis_mask, acc, lane);
+    }
   } else if (p.dL_dsh != nullptr && valid && !acc) {
     float* o = p.dL_dsh + i * p.M * 3;
     for (int k = 0; k < p.M * 3; k++) o[k] = 0.f;
@@ -477,7 +510,7 @@ sh_grad_expand_kernel(int P, int D, int M, int n_views, const float* __restrict_
     for (int k = 16; k < M; k++) { my_row[3 * k] = 0.f; my_row[3 * k + 1] = 0.f; my_row[3 * k + 2] = 0.f; }
   }
   __syncwarp();
-  sh_rows_store(wsm, dL_dsh + (size_t)warp_first * M * 3, M, rows, vis_mask, accumulate != 0, lane);
+  sh_rows_store(wsm, dL_dsh + (size_t)warp_first * M * 3, 3 * M, 3 * M + 1, 0, rows, vis_mask, accumulate != 0, lane);
 }
 
 void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,

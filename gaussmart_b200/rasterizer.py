@@ -61,10 +61,12 @@ class _Workspaces(NamedTuple):
 
 def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3Ds_precomp,
                   viewmatrix, projmatrix, tanfovx, tanfovy, image_height, image_width, sh, sh_degree, campos,
-                  prefiltered, debug, work_counters=None, forward_only=False):
+                  prefiltered, debug, work_counters=None, forward_only=False, sh_rest=None, raw_params=False):
     """Equivalent of RasterizeGaussiansCUDA (rasterize_points.cu:39-134).
     work_counters: optional zeroed int64[4] CUDA tensor receiving work counts (bench only).
-    forward_only: inference render (no backward will follow): sets debug bit 2 of the C ABI."""
+    forward_only: inference render (no backward will follow): sets debug bit 2 of the C ABI.
+    sh_rest / raw_params: the raw-parameter entry (rasterize_gaussians_raw): sh = features_dc [P,1,3] with
+    sh_rest = features_rest [P,M-1,3]; scales / rotations / opacities as stored, activated in-kernel."""
     lib = _lib.load()
     if means3D.ndim != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
@@ -87,6 +89,12 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
     sh = _f32c("sh", sh)
     campos = _f32c("campos", campos)
     M = sh.shape[1] if sh.numel() != 0 else 0
+    if sh_rest is not None:
+        _check_cuda("sh_rest", sh_rest)
+        sh_rest = _f32c("sh_rest", sh_rest)
+        if M != 1 or sh_rest.shape[0] != P:
+            raise RuntimeError("split SH storage needs sh = features_dc [P,1,3] and sh_rest = features_rest [P,M-1,3]")
+        M = 1 + sh_rest.shape[1]
 
     with torch.cuda.device(dev):
         out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
@@ -102,6 +110,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
         a.tan_fovx, a.tan_fovy, a.scale_modifier = float(tanfovx), float(tanfovy), float(scale_modifier)
         a.prefiltered, a.debug = int(bool(prefiltered)), int(debug) | (4 if forward_only else 0)
         a.background, a.means3D, a.shs, a.colors_precomp = _ptr(bg), _ptr(means3D), _ptr(sh), _ptr(colors_precomp)
+        a.shs_rest, a.raw_params = (_ptr(sh_rest) if sh_rest is not None and sh_rest.numel() else None), int(bool(raw_params))
         a.opacities, a.scales, a.rotations = _ptr(opacities), _ptr(scales), _ptr(rotations)
         a.transMat_precomp = _ptr(cov3Ds_precomp)
         a.viewmatrix, a.projmatrix, a.campos = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
@@ -131,8 +140,12 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
 def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp, viewmatrix,
                    projmatrix, tanfovx, tanfovy, grad_out_color, grad_depth, sh, sh_degree, campos, geomBuffer,
                    num_rendered, binningBuffer, imgBuffer, debug, out=None, accumulate=False, binning_capacity=None,
-                   rgb_out=None, stats=None):
+                   rgb_out=None, stats=None, sh_rest=None, raw_opacities=None):
     """Equivalent of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:136-233).
+
+    sh_rest / raw_opacities: the raw-parameter entry (must match the forward): with sh_rest the SH gradient comes back as
+    the pair (dL_dfeatures_dc [P,1,3], dL_dfeatures_rest [P,M-1,3]) in place of dL_dsh; with raw_opacities the gradients
+    of scales / rotations / opacities are w.r.t. the RAW parameters.
 
     `out` (optional) maps means3D / shs / opacities / scales / rotations to preallocated tensors the
     kernel writes into (or adds to, with `accumulate`) -- the view-parallel gradient bucket.
@@ -144,6 +157,11 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
     H, W = grad_out_color.shape[1], grad_out_color.shape[2]
     dev = means3D.device
     M = sh.shape[1] if sh.numel() != 0 else 0
+    split = sh_rest is not None and sh_rest.numel() != 0
+    if split:
+        M = 1 + sh_rest.shape[1]
+        if rgb_out is not None:
+            raise RuntimeError("split SH storage and the factored SH gradient are not combined")
     grad_out_color = _f32c("dL_dout_color", grad_out_color)
     grad_depth = _f32c("dL_dout_others", grad_depth)
     with torch.cuda.device(dev):
@@ -170,7 +188,8 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
         if rgb_out is not None and (M == 0 or tuple(rgb_out.shape) != (P, 3) or rgb_out.dtype != torch.float32
                                     or not rgb_out.is_contiguous() or rgb_out.device != dev):
             raise RuntimeError("rgb_out must be a contiguous float32 [P,3] tensor on the surfels' device (and shs given)")
-        dL_dsh = _out("shs", (P, M, 3)) if (M != 0 and rgb_out is None) else None
+        dL_dsh = _out("shs", (P, 1 if split else M, 3)) if (M != 0 and rgb_out is None) else None
+        dL_dsh_rest = _out("shs_rest", (P, M - 1, 3)) if split else None
         dL_dscales = _out("scales", (P, 2)) if scales.numel() != 0 else None
         dL_drotations = _out("rotations", (P, 4)) if rotations.numel() != 0 else None
         if P != 0:
@@ -194,6 +213,10 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
             a.dL_dscales, a.dL_drotations = _ptr(dL_dscales), _ptr(dL_drotations)
             a.accumulate = int(bool(accumulate))
             a.dL_drgb = _ptr(rgb_out)
+            if split:
+                a.shs_rest, a.dL_dsh_rest = _ptr(sh_rest), _ptr(dL_dsh_rest)
+            if raw_opacities is not None:
+                a.opacities, a.raw_params = _ptr(_f32c("opacity", raw_opacities)), 1
             if stats is not None:  # (grad_norm[P] f32, visible[P] f32, max_radii[P] i32): fused densification statistics
                 gn, vis, mr = stats
                 for t, dt in ((gn, torch.float32), (vis, torch.float32), (mr, torch.int32)):
@@ -202,6 +225,8 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
                 a.densify_grad_norm, a.densify_visible, a.max_radii = _ptr(gn), _ptr(vis), _ptr(mr)
             stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
             _lib.check(lib.gsm_backward(ctypes.byref(a), stream), "backward")
+    if split:
+        dL_dsh = (dL_dsh, dL_dsh_rest)
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dtransMat, dL_dsh, dL_dscales, dL_drotations
 
 
@@ -219,6 +244,59 @@ def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales,
         return color, radii, depth
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
                                      cov3Ds_precomp, raster_settings)
+
+
+def rasterize_gaussians_raw(xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw,
+                            raster_settings):
+    """Raw-parameter entry: what render() computes as
+        rasterizer(means3D=pc.get_xyz, means2D=..., shs=pc.get_features, opacities=pc.get_opacity,
+                   scales=pc.get_scaling, rotations=pc.get_rotation)             (gaussian_renderer/__init__.py:60-106)
+    from the STORED parameters `_xyz, _features_dc, _features_rest, _opacity, _scaling, _rotation`: the getters of
+    scene/gaussian_model.py:104-123 (exp, F.normalize, sigmoid, torch.cat) run inside the preprocess kernels, forward
+    and backward, so no activated copy, no concatenated SH tensor and none of their autograd nodes exist.
+    Returns (color, radii, allmap) like GaussianRasterizer.forward; gradients flow to the raw parameters."""
+    return _RasterizeGaussiansRaw.apply(xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw,
+                                        raster_settings)
+
+
+class _RasterizeGaussiansRaw(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw, rs):
+        e = torch.empty(0, device=xyz.device)
+        needs_grad = any(ctx.needs_input_grad)
+        num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer = _forward_impl(
+            rs.bg, xyz, e, opacity_raw, scaling_raw, rotation_raw, rs.scale_modifier, e, rs.viewmatrix, rs.projmatrix,
+            rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, features_dc, rs.sh_degree, rs.campos, rs.prefiltered,
+            rs.debug, forward_only=not needs_grad, sh_rest=features_rest, raw_params=True)
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.binning_capacity = binningBuffer.gsm_capacity
+        ctx.save_for_backward(xyz, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw, radii, geomBuffer,
+                              binningBuffer, imgBuffer)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, depth
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_radii, grad_depth):
+        rs = ctx.raster_settings
+        (xyz, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw, radii, geomBuffer, binningBuffer,
+         imgBuffer) = ctx.saved_tensors
+        H, W = rs.image_height, rs.image_width
+        if grad_out_color is None:
+            grad_out_color = torch.zeros((3, H, W), dtype=torch.float32, device=xyz.device)
+        if grad_depth is None:
+            grad_depth = torch.zeros((7, H, W), dtype=torch.float32, device=xyz.device)
+        e = torch.empty(0, device=xyz.device)
+        (dL_dmeans2D, _, dL_dopacity, dL_dmeans3D, _, dL_dsh, dL_dscales, dL_drotations) = _backward_impl(
+            rs.bg, xyz, radii, e, scaling_raw, rotation_raw, rs.scale_modifier, e, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+            rs.tanfovy, grad_out_color, grad_depth, features_dc, rs.sh_degree, rs.campos, geomBuffer, ctx.num_rendered,
+            binningBuffer, imgBuffer, rs.debug, binning_capacity=ctx.binning_capacity, sh_rest=features_rest,
+            raw_opacities=opacity_raw)
+        if isinstance(dL_dsh, tuple):
+            d_dc, d_rest = dL_dsh
+        else:
+            d_dc, d_rest = dL_dsh, torch.zeros_like(features_rest)
+        return dL_dmeans3D, dL_dmeans2D, d_dc, d_rest, dL_dopacity.view_as(opacity_raw), dL_dscales, dL_drotations, None
 
 
 class _RasterizeGaussians(torch.autograd.Function):

@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 4
+#define GSM_ABI_VERSION 5
 
 #define GSM_OK 0
 #define GSM_ERR_INVALID_ARGUMENT 10001
@@ -112,6 +112,13 @@ typedef struct gsm_forward_args {
                                     pairs the reference's loop would evaluate, [1] contributing pairs,
                                     [2] records staged, [3] pairs evaluated after culling.
                                     NULL in production; used by bench.py for the roofline model. */
+  /* raw-parameter entry, both optional, zero / NULL for the reference's behaviour:
+     the getters of scene/gaussian_model.py:104-123 fused into the preprocess kernels */
+  const float* shs_rest;         /* when given: shs = _features_dc [P,1,3] and shs_rest = _features_rest [P,M-1,3]
+                                    (get_features without the torch.cat copy, gaussian_model.py:115-118) */
+  int raw_params;                /* 1: scales = _scaling, rotations = _rotation, opacities = _opacity as STORED;
+                                    exp / F.normalize / sigmoid (gaussian_model.py:104-113) are applied in-kernel,
+                                    evaluated as torch's CUDA kernels evaluate them */
 } gsm_forward_args;
 
 /* Runs preprocess + scan, waits for R (one stream synchronisation, as rasterizer_impl.cu:282),
@@ -168,6 +175,14 @@ typedef struct gsm_backward_args {
   float* densify_grad_norm;
   float* densify_visible;
   int* max_radii;
+  /* raw-parameter entry, as in gsm_forward_args (must match the forward's call): with shs_rest, dL_dsh receives
+     d/d_features_dc [P,1,3] and dL_dsh_rest d/d_features_rest [P,M-1,3]; with raw_params, dL_dscales / dL_drotations /
+     dL_dopacity are gradients w.r.t. the RAW parameters (chained through exp / normalize / sigmoid in the backward
+     preprocess) and `opacities` (the raw ones) must be given */
+  const float* shs_rest;
+  float* dL_dsh_rest;
+  const float* opacities;
+  int raw_params;
 } gsm_backward_args;
 
 size_t gsm_grad_workspace_bytes(int P);

@@ -206,6 +206,22 @@ class OursArm:
         loss.backward()
         return loss
 
+    def raw_step(self, raw, m2d, cam_d, gt, cam_h, gt_ready):
+        """render() level (gaussian_renderer/__init__.py:60-106) from the STORED parameters: the raw-parameter entry, the
+        getters of gaussian_model.py:104-123 fused into the preprocess kernels."""
+        from gaussmart_b200 import synthetic
+        from gaussmart_b200.rasterizer import rasterize_gaussians_raw
+        S = self.gb.GaussianRasterizationSettings(**synthetic.settings_kwargs(cam_d, self.wl["deg"], self.bg))
+        for v in raw.values():
+            v.grad = None
+        m2d.grad = None
+        color, radii, allmap = rasterize_gaussians_raw(raw["xyz"], m2d, raw["f_dc"], raw["f_rest"], raw["opacity"],
+                                                       raw["scaling"], raw["rotation"], S)
+        gt_ready()
+        loss = loss_fn(color, allmap, gt, cam_h, self.photometric, self.regularizer)
+        loss.backward()
+        return loss
+
     def render(self, cam_d):
         """Inference render (render.py / gr.py:37-97 under torch.no_grad): forward only through the public API."""
         from gaussmart_b200 import synthetic
@@ -272,6 +288,24 @@ class ReferenceArm:
     def render(self, cam_d):
         with torch.no_grad():
             return self._render(cam_d)
+
+    def raw_step(self, raw, m2d, cam_d, gt, cam_h, gt_ready):
+        """render() level from the STORED parameters, the reference's way: the getters of gaussian_model.py:104-123 as
+        torch ops (exp, F.normalize, sigmoid, torch.cat) in front of its rasterizer, autograd behind."""
+        from gaussmart_b200 import synthetic
+        ref = self.ref
+        S = ref.GaussianRasterizationSettings(**synthetic.settings_kwargs(cam_d, self.wl["deg"], self.bg))
+        for v in raw.values():
+            v.grad = None
+        m2d.grad = None
+        color, radii, allmap = ref.GaussianRasterizer(S)(
+            means3D=raw["xyz"], means2D=m2d, shs=torch.cat((raw["f_dc"], raw["f_rest"]), dim=1),
+            opacities=torch.sigmoid(raw["opacity"]), scales=torch.exp(raw["scaling"]),
+            rotations=torch.nn.functional.normalize(raw["rotation"]))
+        gt_ready()
+        loss = loss_fn(color, allmap, gt, cam_d, self.photometric, self.regularizer)
+        loss.backward()
+        return loss
 
     def value_step(self, view):
         color, radii, allmap = self._render(self.wl["cams_d"][view])
@@ -672,10 +706,14 @@ def main():
     #      own optimizer (torch.optim.Adam as gaussian_model.py:292 builds it / FusedAdam).  Run last: it moves the surfels.
     train_iter = None
     if e2e is not None and world == 1:
-        L = arm.leaves
-        # the leaves here are the ACTIVATED parameters, so the reference's raw-parameter learning rates would walk the
-        # scene away from the workload within a few steps; the optimizer's work does not depend on lr
-        groups = [{"params": [L[k]], "lr": 1e-8, "name": k} for k in ("means3D", "shs", "opacities", "scales", "rotations")]
+        prm = wl["params"]
+        o_ = prm["opacities"].clamp(1e-6, 1 - 1e-6)
+        raw = {"xyz": prm["means3D"].clone(), "f_dc": prm["shs"][:, :1].contiguous(), "f_rest": prm["shs"][:, 1:].contiguous(),
+               "opacity": torch.log(o_ / (1 - o_)), "scaling": torch.log(prm["scales"]), "rotation": prm["rotations"].clone()}
+        raw = {k: v.requires_grad_(True) for k, v in raw.items()}   # the STORED parameters of gaussian_model.py:50-56
+        m2d = torch.zeros_like(raw["xyz"], requires_grad=True)
+        # tiny learning rates: the optimizer's work does not depend on lr, and the workload stays the workload
+        groups = [{"params": [raw[k]], "lr": 1e-8, "name": k} for k in ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")]
         if args.impl == "reference":
             opt = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
         else:
@@ -683,7 +721,16 @@ def main():
             opt = FusedAdam(groups, lr=0.0, eps=1e-15)
 
         def train_step(s):
-            e2e_step(s)
+            v = view_of(s)
+            copy_stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(copy_stream):
+                gt_dev.copy_(wl["gt_host"][s % 2], non_blocking=True)
+            mats_dev.copy_(mats_host[v], non_blocking=True)
+            c = wl["cams"][v]
+            cam_d = synthetic.Camera(c.image_width, c.image_height, c.FoVx, c.FoVy, c.tanfovx, c.tanfovy,
+                                     mats_dev[0:16].view(4, 4), mats_dev[16:32].view(4, 4), mats_dev[32:35])
+            loss = arm.raw_step(raw, m2d, cam_d, gt_dev, c, gt_ready)
+            loss_host.copy_(loss.detach(), non_blocking=False)
             opt.step()
         if args.impl == "ours":
             _lib.stage_timing_enable(True)
@@ -694,8 +741,9 @@ def main():
             train_stages = {k: v[0] / args.steps for k, v in _lib.stage_timing_read(reset=True).items() if v[1]}
             _lib.stage_timing_enable(False)
         train_iter = {"value": 1000.0 * args.steps / ms_train, "unit": UNIT, "ms_per_step": ms_train / args.steps,
-                      "includes": "H2D of camera + ground truth, render, L1+SSIM+regulariser loss, backward, loss read-back, "
-                                  "Adam step over all 58 floats/surfel"}
+                      "includes": "H2D of camera + ground truth, render() from the STORED parameters (getters of "
+                                  "gaussian_model.py:104-123: torch ops for the reference, fused raw entry here), "
+                                  "L1+SSIM+regulariser loss, backward, loss read-back, Adam step over all 58 floats/surfel"}
         if train_stages:
             train_iter["stages_ms_per_step"] = train_stages
         del opt

@@ -157,6 +157,8 @@ __device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict
 // the extents it feeds only need to err upwards)
 __device__ __forceinline__ double sqrt_up(double x) { return (double)__fsqrt_ru(__double2float_ru(x)); }
 
+// RAW: the raw-parameter entry (in-kernel activations and / or split SH storage); the standard entry compiles without it
+template <bool RAW>
 __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdPreprocessParams p) {
   extern __shared__ float sh_smem[];
   const int gidx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -190,7 +192,7 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
     q_in = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
   }
   float opac_in = __ldg(p.opacities + idx);
-  if (p.raw) {
+  if (RAW && p.raw) {
     // raw parameters (gaussian_model.py:104-113): scaling_activation = exp, rotation_activation = F.normalize,
     // opacity_activation = sigmoid, evaluated as torch's CUDA kernels evaluate them
     sc_in = activate_scaling(sc_in);
@@ -332,7 +334,7 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
     float* wsm = sh_smem + (size_t)warp * 32 * (3 * p.M + 1);
     if (vis_mask != 0) {
       const int rows = min(32, p.P - warp_first), rs = 3 * p.M + 1;
-      if (p.shs_rest == nullptr) {
+      if (!RAW || p.shs_rest == nullptr) {
         sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, 3 * p.M, rs, 0, rows, vis_mask, lane);
       } else {  // features_dc + features_rest, no concatenated copy
         sh_rows_load(wsm, p.shs + (size_t)warp_first * 3, 3, rs, 0, rows, vis_mask, lane);
@@ -377,10 +379,12 @@ void launch_preprocess_fwd(const FwdPreprocessParams& p, cudaStream_t stream) {
                           ? (size_t)(PFWD_THREADS / 32) * 32 * (3 * p.M + 1) * sizeof(float) : 0;
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
-    cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(preprocess_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(preprocess_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured = smem;
   }
-  preprocess_fwd_kernel<<<(p.P + PFWD_THREADS - 1) / PFWD_THREADS, PFWD_THREADS, smem, stream>>>(p);
+  if (p.raw || p.shs_rest != nullptr) preprocess_fwd_kernel<true><<<(p.P + PFWD_THREADS - 1) / PFWD_THREADS, PFWD_THREADS, smem, stream>>>(p);
+  else preprocess_fwd_kernel<false><<<(p.P + PFWD_THREADS - 1) / PFWD_THREADS, PFWD_THREADS, smem, stream>>>(p);
 }
 
 // markVisible (rasterizer_impl.cu:54-66): present = view_z > 0.2

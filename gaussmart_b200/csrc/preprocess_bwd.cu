@@ -204,6 +204,7 @@ __device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restric
 #ifndef GSM_PBWD_MIN_CTAS
 #define GSM_PBWD_MIN_CTAS 6
 #endif
+template <bool RAW>  // the raw-parameter entry (activation chain, split SH storage); the standard entry compiles without it
 __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bwd_kernel(const BwdPreprocessParams p) {
   extern __shared__ float sh_smem[];
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -231,7 +232,7 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
     pos = mk(__ldg(p.means3D + 3 * i), __ldg(p.means3D + 3 * i + 1), __ldg(p.means3D + 3 * i + 2));
   }
   if (has_sh) {
-    if (p.shs_rest == nullptr) {
+    if (!RAW || p.shs_rest == nullptr) {
       sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, 3 * p.M, 3 * p.M + 1, 0, rows, vis_mask, lane);
     } else {
       sh_rows_load(wsm, p.shs + (size_t)warp_first * 3, 3, 3 * p.M + 1, 0, rows, vis_mask, lane);
@@ -280,7 +281,7 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
     } else {
       sc = __ldg(reinterpret_cast<const float2*>(p.scales) + idx);
       q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
-      if (p.raw) {  // the forward's activations (common.cuh), re-evaluated
+      if (RAW && p.raw) {  // the forward's activations (common.cuh), re-evaluated
         sc = activate_scaling(sc);
         const ActivatedRotation ar = activate_rotation(q);
         q = ar.q;
@@ -370,7 +371,7 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
       dscale_x = dot(dRS0, R0);
       dscale_y = dot(dRS1, R1);
       dmean3D = dM[2];
-      if (p.raw) {
+      if (RAW && p.raw) {
         // chain through the activations: exp' = exp; normalize: (g - q (q.g)) / max(||raw||, eps) (the clamp's own
         // derivative is zero); sigmoid' = o (1 - o)
         dscale_x *= sc.x; dscale_y *= sc.y;
@@ -380,7 +381,7 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
         else drot = make_float4(drot.x * inv, drot.y * inv, drot.z * inv, drot.w * inv);
       }
     }
-    if (p.raw) {
+    if (RAW && p.raw) {
       const float o = activate_opacity(__ldg(p.opacities + i));
       dopacity *= o * (1.0f - o);
     }
@@ -410,7 +411,7 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
     if (valid) store3(p.dL_drgb + 3 * i, drgb_masked);  // per view: never accumulated
   } else if (has_sh) {
     __syncwarp();
-    if (p.dL_dsh_rest == nullptr) {
+    if (!RAW || p.dL_dsh_rest == nullptr) {
       sh_rows_store(wsm, p.dL_dsh + (size_t)warp_first * p.M * 3, 3 * p.M, 3 * p.M + 1, 0, rows, vis_mask, acc, lane);
     } else {  // gradients of features_dc and features_rest, no concatenated gradient to slice afterwards
       sh_rows_store(wsm, p.dL_dsh + (size_t)warp_first * 3, 3, 3 * p.M + 1, 0, rows, vis_mask, acc, lane);
@@ -532,10 +533,12 @@ void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream) {
   const size_t smem = (size_t)(PBWD_THREADS / 32) * 32 * (3 * p.M + 1) * sizeof(float);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
-    cudaFuncSetAttribute(preprocess_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(preprocess_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured = smem;
   }
-  preprocess_bwd_kernel<<<(p.P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(p);
+  if (p.raw || p.shs_rest != nullptr) preprocess_bwd_kernel<true><<<(p.P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(p);
+  else preprocess_bwd_kernel<false><<<(p.P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(p);
 }
 
 }  // namespace gsm

@@ -12,6 +12,8 @@ The data path has exactly one exchange step (the gradient all-reduce); rendering
 """
 from typing import Callable, Dict, List, NamedTuple, Optional, Sequence
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -192,8 +194,9 @@ def exchange_factored(ex: FactoredExchange, group=None, after_gather: Optional[C
         wg = dist.all_gather(list(ex.rgb_recv.unbind(0)), ex.rgb_send, group=group, async_op=True)
     wr = dist.all_reduce(ex.flat, op=dist.ReduceOp.SUM, group=group, async_op=True)   # gradients + statistics sums
     wm = dist.all_reduce(ex.max_radii, op=dist.ReduceOp.MAX, group=group, async_op=True) if ex.max_radii is not None else None
+    dbg = os.environ.get("GSM_VP_PROBE", "")   # timing probes only (tools/): which part of the exchange is exposed
     wg.wait()
-    if after_gather is not None:
+    if after_gather is not None and "skip_expand" not in dbg:
         after_gather()
     wr.wait()
     if wm is not None:

@@ -38,3 +38,38 @@ def test_regularizer_oracle_matches_reference_depth_to_normal(path):
     assert (torch.nan_to_num(allmap.grad, 0.0, 0.0, 0.0) - g).abs().max() <= 1e-6 * g.abs().max()
     # torch's backward of D/alpha is NaN exactly where alpha == 0 and nowhere else in channels 0 and 1
     assert torch.equal(torch.isnan(allmap.grad[0]), allmap.detach()[1] == 0)
+
+
+def test_camera_constants_reproduce_the_reference_rays():
+    """gaussmart_b200.regularizer.camera_constants (host side of gsm_surface_regularizer: the per-camera ray matrix,
+    origin and view rotation passed by value) against depths_to_points' per-pixel rays (utils/point_utils.py:9-22)."""
+    from gaussmart_b200.regularizer import camera_constants
+    W, H = 57, 41
+    cam = synthetic.make_camera(W, H, 1.3)
+    ray, origin, rot = camera_constants(cam)
+    dirs, o = ro.pixel_rays(cam, "cpu")
+    M = torch.tensor(ray).view(3, 3)
+    gx, gy = torch.meshgrid(torch.arange(W).float(), torch.arange(H).float(), indexing="xy")
+    pix = torch.stack([gx, gy, torch.ones_like(gx)], dim=-1).reshape(-1, 3)
+    assert (pix @ M - dirs).abs().max() <= 1e-6 * dirs.abs().max()
+    assert torch.allclose(torch.tensor(origin), o, atol=1e-7)
+    assert torch.equal(torch.tensor(rot).view(3, 3), cam.world_view_transform[:3, :3])
+    assert camera_constants(cam) is camera_constants(cam)   # cached per camera
+
+
+def test_host_mirrors_refuse_cpu_tensors_and_unsupported_settings():
+    """No CPU fallback anywhere on the widened path: the host mirrors raise before touching the library."""
+    from gaussmart_b200 import loss as gl, regularizer as gr
+    from gaussmart_b200.optim import FusedAdam
+    with pytest.raises(RuntimeError):
+        gl.photometric_loss(torch.rand(3, 8, 8), torch.rand(3, 8, 8))
+    with pytest.raises(RuntimeError):
+        gr.surface_regularizer(torch.zeros(7, 4, 4), synthetic.make_camera(4, 4, 0.0))
+    p = torch.nn.Parameter(torch.ones(4))
+    with pytest.raises(ValueError):
+        FusedAdam([p], weight_decay=0.1)
+    with pytest.raises(ValueError):
+        FusedAdam([p], amsgrad=True)
+    p.grad = torch.ones(4)
+    with pytest.raises(RuntimeError):
+        FusedAdam([p], lr=0.1).step()

@@ -59,41 +59,60 @@ ssim_forward_kernel(const float* __restrict__ img1, const float* __restrict__ im
   load_tile(t1, img1 + plane, H, W, x0, y0);
   load_tile(t2, img2 + plane, H, W, x0, y0);
   __syncthreads();
-  for (int i = threadIdx.x; i < LTH * LT; i += LOSS_THREADS) {
-    const int r = i / LT, c = i - r * LT;
-    float s1 = 0.f, s2 = 0.f, s11 = 0.f, s22 = 0.f, s12 = 0.f;
+  // horizontal pass, 4 adjacent outputs per thread: 14 + 14 shared-memory reads feed 4 x 5 sums (was 22 per output)
+  for (int i = threadIdx.x; i < LTH * (LT / 4); i += LOSS_THREADS) {
+    const int r = i / (LT / 4), c0 = (i - r * (LT / 4)) * 4;
+    float a[LW + 3], b[LW + 3];
 #pragma unroll
-    for (int k = 0; k < LW; k++) {
-      const float w = c_gauss[k], a = t1[r][c + k], b = t2[r][c + k];
-      s1 += w * a; s2 += w * b; s11 += w * a * a; s22 += w * b * b; s12 += w * a * b;
+    for (int k = 0; k < LW + 3; k++) { a[k] = t1[r][c0 + k]; b[k] = t2[r][c0 + k]; }
+#pragma unroll
+    for (int o = 0; o < 4; o++) {
+      float s1 = 0.f, s2 = 0.f, s11 = 0.f, s22 = 0.f, s12 = 0.f;
+#pragma unroll
+      for (int k = 0; k < LW; k++) {
+        const float w = c_gauss[k], x = a[o + k], y = b[o + k];
+        s1 += w * x; s2 += w * y; s11 += w * x * x; s22 += w * y * y; s12 += w * x * y;
+      }
+      hz[0][r][c0 + o] = s1; hz[1][r][c0 + o] = s2; hz[2][r][c0 + o] = s11; hz[3][r][c0 + o] = s22; hz[4][r][c0 + o] = s12;
     }
-    hz[0][r][c] = s1; hz[1][r][c] = s2; hz[2][r][c] = s11; hz[3][r][c] = s22; hz[4][r][c] = s12;
   }
   __syncthreads();
   const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
   double l1_sum = 0.0, s_sum = 0.0;
-  for (int i = threadIdx.x; i < LT * LT; i += LOSS_THREADS) {
-    const int r = i / LT, c = i - r * LT;
-    const int y = y0 + r, x = x0 + c;
-    if (y >= H || x >= W) continue;
-    float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+  // vertical pass, 4 stacked outputs per thread (one thread per column and group of 4 rows: exactly one round)
+  for (int i = threadIdx.x; i < (LT / 4) * LT; i += LOSS_THREADS) {
+    const int r0 = (i / LT) * 4, c = i % LT;
+    const int x = x0 + c;
+    if (x >= W || y0 + r0 >= H) continue;
+    float m1[4] = {0.f, 0.f, 0.f, 0.f}, m2[4] = {0.f, 0.f, 0.f, 0.f}, e11[4] = {0.f, 0.f, 0.f, 0.f},
+          e22[4] = {0.f, 0.f, 0.f, 0.f}, e12[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int k = 0; k < LW; k++) {
-      const float w = c_gauss[k];
-      m1 += w * hz[0][r + k][c]; m2 += w * hz[1][r + k][c];
-      e11 += w * hz[2][r + k][c]; e22 += w * hz[3][r + k][c]; e12 += w * hz[4][r + k][c];
+    for (int k = 0; k < LW + 3; k++) {
+      const float h0 = hz[0][r0 + k][c], h1 = hz[1][r0 + k][c], h2 = hz[2][r0 + k][c], h3 = hz[3][r0 + k][c], h4 = hz[4][r0 + k][c];
+#pragma unroll
+      for (int o = 0; o < 4; o++) {
+        if (k - o >= 0 && k - o < LW) {
+          const float w = c_gauss[k - o];
+          m1[o] += w * h0; m2[o] += w * h1; e11[o] += w * h2; e22[o] += w * h3; e12[o] += w * h4;
+        }
+      }
     }
-    const float s1 = e11 - m1 * m1, s2 = e22 - m2 * m2, s12 = e12 - m1 * m2;
-    const float A1 = 2.f * m1 * m2 + C1, A2 = 2.f * s12 + C2;
-    const float B1 = m1 * m1 + m2 * m2 + C1, B2 = s1 + s2 + C2;
-    const float iB1 = 1.0f / B1, iB2 = 1.0f / B2;
-    const float S = A1 * A2 * iB1 * iB2;
-    const size_t at = plane + (size_t)y * W + x;
-    map_a[at] = 2.f * m2 * (A2 - A1) * iB1 * iB2 + 2.f * m1 * S * (iB2 - iB1);
-    map_b[at] = -S * iB2;
-    map_c[at] = 2.f * A1 * iB1 * iB2;
-    s_sum += (double)S;
-    l1_sum += (double)fabsf(t1[r + LH][c + LH] - t2[r + LH][c + LH]);
+#pragma unroll
+    for (int o = 0; o < 4; o++) {
+      const int r = r0 + o, y = y0 + r;
+      if (y >= H) break;
+      const float s1 = e11[o] - m1[o] * m1[o], s2 = e22[o] - m2[o] * m2[o], s12 = e12[o] - m1[o] * m2[o];
+      const float A1 = 2.f * m1[o] * m2[o] + C1, A2 = 2.f * s12 + C2;
+      const float B1 = m1[o] * m1[o] + m2[o] * m2[o] + C1, B2 = s1 + s2 + C2;
+      const float iB1 = 1.0f / B1, iB2 = 1.0f / B2;
+      const float S = A1 * A2 * iB1 * iB2;
+      const size_t at = plane + (size_t)y * W + x;
+      map_a[at] = 2.f * m2[o] * (A2 - A1) * iB1 * iB2 + 2.f * m1[o] * S * (iB2 - iB1);
+      map_b[at] = -S * iB2;
+      map_c[at] = 2.f * A1 * iB1 * iB2;
+      s_sum += (double)S;
+      l1_sum += (double)fabsf(t1[r + LH][c + LH] - t2[r + LH][c + LH]);
+    }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -131,33 +150,50 @@ ssim_backward_kernel(const float* __restrict__ img1, const float* __restrict__ i
   load_tile(t[1], map_b + plane, H, W, x0, y0);
   load_tile(t[2], map_c + plane, H, W, x0, y0);
   __syncthreads();
-  for (int i = threadIdx.x; i < LTH * LT; i += LOSS_THREADS) {
-    const int r = i / LT, c = i - r * LT;
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+  for (int i = threadIdx.x; i < LTH * (LT / 4); i += LOSS_THREADS) {
+    const int r = i / (LT / 4), c0 = (i - r * (LT / 4)) * 4;
 #pragma unroll
-    for (int k = 0; k < LW; k++) {
-      const float w = c_gauss[k];
-      s0 += w * t[0][r][c + k]; s1 += w * t[1][r][c + k]; s2 += w * t[2][r][c + k];
+    for (int m = 0; m < 3; m++) {
+      float a[LW + 3];
+#pragma unroll
+      for (int k = 0; k < LW + 3; k++) a[k] = t[m][r][c0 + k];
+#pragma unroll
+      for (int o = 0; o < 4; o++) {
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < LW; k++) acc += c_gauss[k] * a[o + k];
+        hz[m][r][c0 + o] = acc;
+      }
     }
-    hz[0][r][c] = s0; hz[1][r][c] = s1; hz[2][r][c] = s2;
   }
   __syncthreads();
   const float k_l1 = grad_scale * (1.0f - lambda) / (float)n, k_ss = -grad_scale * lambda / (float)n;
-  for (int i = threadIdx.x; i < LT * LT; i += LOSS_THREADS) {
-    const int r = i / LT, c = i - r * LT;
-    const int y = y0 + r, x = x0 + c;
-    if (y >= H || x >= W) continue;
-    float fa = 0.f, fb = 0.f, fc = 0.f;
+  for (int i = threadIdx.x; i < (LT / 4) * LT; i += LOSS_THREADS) {
+    const int r0 = (i / LT) * 4, c = i % LT;
+    const int x = x0 + c;
+    if (x >= W || y0 + r0 >= H) continue;
+    float fa[4] = {0.f, 0.f, 0.f, 0.f}, fb[4] = {0.f, 0.f, 0.f, 0.f}, fc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int k = 0; k < LW; k++) {
-      const float w = c_gauss[k];
-      fa += w * hz[0][r + k][c]; fb += w * hz[1][r + k][c]; fc += w * hz[2][r + k][c];
+    for (int k = 0; k < LW + 3; k++) {
+      const float h0 = hz[0][r0 + k][c], h1 = hz[1][r0 + k][c], h2 = hz[2][r0 + k][c];
+#pragma unroll
+      for (int o = 0; o < 4; o++) {
+        if (k - o >= 0 && k - o < LW) {
+          const float w = c_gauss[k - o];
+          fa[o] += w * h0; fb[o] += w * h1; fc[o] += w * h2;
+        }
+      }
     }
-    const size_t at = plane + (size_t)y * W + x;
-    const float xv = __ldg(img1 + at), yv = __ldg(img2 + at);
-    const float d = xv - yv;
-    const float sgn = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);  // torch.abs backward: sign, 0 at 0
-    dL_dimg[at] = k_l1 * sgn + k_ss * (fa + 2.f * xv * fb + yv * fc);
+#pragma unroll
+    for (int o = 0; o < 4; o++) {
+      const int y = y0 + r0 + o;
+      if (y >= H) break;
+      const size_t at = plane + (size_t)y * W + x;
+      const float xv = __ldg(img1 + at), yv = __ldg(img2 + at);
+      const float d = xv - yv;
+      const float sgn = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);  // torch.abs backward: sign, 0 at 0
+      dL_dimg[at] = k_l1 * sgn + k_ss * (fa[o] + 2.f * xv * fb[o] + yv * fc[o]);
+    }
   }
 }
 

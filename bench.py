@@ -537,6 +537,45 @@ def adam_leg(wl, impl, reps=10):
     return out
 
 
+def densification_leg(wl, impl, reps=20):
+    """Densification bookkeeping of the iteration (train.py:199-203 + gaussian_model.py:551-553; SURVEY.md 8f row 3,
+    second half) at the workload's surfel count with ~70 % of the surfels visible: the reference's own indexed torch
+    statements for the reference arm, one gsm_densification_stats launch for ours.
+    compulsory bytes: 4 (radii) + visible x (12 gradient + 3 x 8 read-modify-write) per surfel."""
+    P = wl["P"]
+    g = torch.Generator(device="cuda").manual_seed(7)
+    radii = torch.randint(1, 200, (P,), device="cuda", generator=g, dtype=torch.int32)
+    radii[torch.rand(P, device="cuda", generator=g) < 0.3] = 0
+    grad = torch.randn(P, 3, device="cuda", generator=g) * 1e-4 * (radii > 0).unsqueeze(1)
+    mr, acc, den = torch.zeros(P, device="cuda"), torch.zeros(P, 1, device="cuda"), torch.zeros(P, 1, device="cuda")
+    if impl == "reference":
+        def step():
+            vf = radii > 0  # gaussian_renderer/__init__.py: visibility_filter
+            mr[vf] = torch.max(mr[vf], radii[vf])
+            acc[vf] += torch.norm(grad[vf], dim=-1, keepdim=True)
+            den[vf] += 1
+    else:
+        from gaussmart_b200.optim import add_densification_stats
+
+        def step():
+            add_densification_stats(mr, acc, den, radii, grad)
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    vis = int((radii > 0).sum())
+    nbytes = 4.0 * P + 36.0 * vis
+    return {"ms": ms, "surfels": P, "visible": vis, "calls": reps, "compulsory_gbs": nbytes / (ms * 1e-3) / 1e9,
+            "frac_of_hbm_peak": nbytes / (ms * 1e-3) / 1e9 / peaks()["hbm_gbs"],
+            "checksum": [float(mr.double().sum()), float(acc.double().sum()), float(den.double().sum())]}
+
+
 def regularizer_leg(arm, wl, reps=20):
     """The allmap regularisers of the iteration (render() post-processing + depth_to_normal + train.py:131-140), value +
     gradient w.r.t. allmap, on a rendered allmap of the workload: each arm's own implementation, CUDA events
@@ -790,6 +829,10 @@ def main():
             if hasattr(arm, "photometric"):
                 line["loss"] = loss_leg(wl, arm.photometric)
             line["adam"] = adam_leg(wl, "reference")
+            try:
+                line["densification_stats"] = densification_leg(wl, "reference")
+            except Exception as ex:  # pragma: no cover
+                line["densification_stats"] = {"error": repr(ex)[:200]}
             if hasattr(arm, "regularizer"):
                 line["regularizer"] = regularizer_leg(arm, wl)
         print(json.dumps(line))
@@ -833,6 +876,7 @@ def main():
         line["knn"] = knn_leg(wl, "ours")
         line["loss"] = loss_leg(wl, arm.photometric)
         line["adam"] = adam_leg(wl, "ours")
+        line["densification_stats"] = densification_leg(wl, "ours")
         line["regularizer"] = regularizer_leg(arm, wl)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(int(wc["E_bwd"]), wl["deg"])

@@ -17,7 +17,7 @@ GSM_ERR_BINNING_OVERFLOW = 10002
 GSM_ERR_WORKSPACE_TOO_SMALL = 10003
 GSM_SURFEL_RECORD_BYTES = 80
 GSM_GRAD_RECORD_FLOATS = 20
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 EXPORTS = [
     "gsm_last_error", "gsm_abi_version", "gsm_geometry_bytes", "gsm_image_bytes", "gsm_binning_bytes", "gsm_binning_persistent_bytes",
@@ -26,7 +26,7 @@ EXPORTS = [
     "gsm_knn_workspace_bytes", "gsm_knn_dist2",
     "gsm_stage_count", "gsm_stage_name", "gsm_stage_timing_enable", "gsm_stage_timing_read",
     "gsm_sort_pairs32_temp_bytes", "gsm_sort_pairs32", "gsm_sh_grad_expand",
-    "gsm_photometric_loss_workspace_bytes", "gsm_photometric_loss", "gsm_adam_step",
+    "gsm_photometric_loss_workspace_bytes", "gsm_photometric_loss", "gsm_adam_step", "gsm_densification_stats",
     "gsm_surface_regularizer_workspace_bytes", "gsm_surface_regularizer",
 ]
 
@@ -146,6 +146,8 @@ def load():
     lib.gsm_surface_regularizer.argtypes = [POINTER(RegularizerArgs), c_void_p]
     lib.gsm_adam_step.restype = c_int
     lib.gsm_adam_step.argtypes = [POINTER(AdamTensor), c_int, c_void_p]
+    lib.gsm_densification_stats.restype = c_int
+    lib.gsm_densification_stats.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
     if lib.gsm_abi_version() != ABI_VERSION:
         raise ImportError(f"gaussmart_b200: ABI version mismatch ({lib.gsm_abi_version()} != {ABI_VERSION})")
     _lib = lib

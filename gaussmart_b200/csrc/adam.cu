@@ -108,6 +108,61 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_step_kernel(const __grid_co
   }
 }
 
+
+// ---- densification bookkeeping of the same iteration (train.py:199-203 and
+// scene/gaussian_model.py:551-553): for every surfel the filter selects (radii > 0 when no filter is passed, which is
+// render()'s visibility_filter),
+//     max_radii2D = max(max_radii2D, (float)radii);  xyz_gradient_accum += ||viewspace_grad[i, :]||_2;  denom += 1
+// Six indexed torch ops with boolean-mask gathers in the reference; here one pass, four surfels per thread so that every
+// stream is a 128-bit access ([P,3] gradient rows: 3 x float4 per four surfels).  The norm is sqrt((x*x + y*y) + z*z)
+// with separately rounded products (no fma contraction), the association of torch's three-element norm reduction.
+constexpr int DENS_THREADS = 256;
+
+__device__ __forceinline__ void dens_update(bool on, int r, float gx, float gy, float gz, float& mr, float& acc, float& den) {
+  if (!on) return;
+  mr = fmaxf(mr, (float)r);
+  const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy)), __fmul_rn(gz, gz));
+  acc = __fadd_rn(acc, sqrt_guarded(n2));
+  den = __fadd_rn(den, 1.0f);
+}
+
+__global__ void __launch_bounds__(DENS_THREADS)
+densification_stats_kernel(const int* __restrict__ radii, const float* __restrict__ grad, const unsigned char* __restrict__ filter,
+                           float* __restrict__ max_radii, float* __restrict__ accum, float* __restrict__ denom, size_t P) {
+  const size_t q = (size_t)blockIdx.x * DENS_THREADS + threadIdx.x;  // group of four surfels
+  const size_t i0 = q * 4;
+  if (i0 >= P) return;
+  if (i0 + 4 <= P) {
+    const int4 r = __ldg(reinterpret_cast<const int4*>(radii) + q);
+    bool on[4];
+    if (filter != nullptr) {
+      const uchar4 f = __ldg(reinterpret_cast<const uchar4*>(filter) + q);
+      on[0] = f.x != 0; on[1] = f.y != 0; on[2] = f.z != 0; on[3] = f.w != 0;
+    } else {
+      on[0] = r.x > 0; on[1] = r.y > 0; on[2] = r.z > 0; on[3] = r.w > 0;
+    }
+    if (!(on[0] | on[1] | on[2] | on[3])) return;
+    const float4* g4 = reinterpret_cast<const float4*>(grad) + q * 3;
+    const float4 a = __ldg(g4), b = __ldg(g4 + 1), c = __ldg(g4 + 2);
+    float4 mr = reinterpret_cast<float4*>(max_radii)[q];
+    float4 ac = reinterpret_cast<float4*>(accum)[q];
+    float4 dn = reinterpret_cast<float4*>(denom)[q];
+    dens_update(on[0], r.x, a.x, a.y, a.z, mr.x, ac.x, dn.x);
+    dens_update(on[1], r.y, a.w, b.x, b.y, mr.y, ac.y, dn.y);
+    dens_update(on[2], r.z, b.z, b.w, c.x, mr.z, ac.z, dn.z);
+    dens_update(on[3], r.w, c.y, c.z, c.w, mr.w, ac.w, dn.w);
+    reinterpret_cast<float4*>(max_radii)[q] = mr;
+    reinterpret_cast<float4*>(accum)[q] = ac;
+    reinterpret_cast<float4*>(denom)[q] = dn;
+  } else {  // ragged tail (P not a multiple of four)
+    for (size_t i = i0; i < P; i++) {
+      const int r = radii[i];
+      const bool on = filter != nullptr ? filter[i] != 0 : r > 0;
+      dens_update(on, r, grad[3 * i], grad[3 * i + 1], grad[3 * i + 2], max_radii[i], accum[i], denom[i]);
+    }
+  }
+}
+
 }  // namespace gsm
 
 using namespace gsm;
@@ -153,6 +208,25 @@ extern "C" int gsm_adam_step(const gsm_adam_tensor* tensors, int n_tensors, void
     for (int k = b.count; k <= ADAM_MAX_TENSORS; k++) b.first_chunk[k] = chunks;
     if (chunks) adam_step_kernel<<<chunks, ADAM_THREADS, 0, stream>>>(b);
   }
+  GSM_CUDA(cudaGetLastError());
+  return GSM_OK;
+}
+
+extern "C" int gsm_densification_stats(const int* radii, const float* viewspace_grad, const unsigned char* update_filter,
+                                       float* max_radii2D, float* xyz_gradient_accum, float* denom, size_t P, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P == 0) return GSM_OK;
+  if (radii == nullptr || viewspace_grad == nullptr || max_radii2D == nullptr || xyz_gradient_accum == nullptr || denom == nullptr) {
+    set_error("gsm_densification_stats: null pointer"); return GSM_ERR_INVALID_ARGUMENT;
+  }
+  if ((((uintptr_t)radii | (uintptr_t)viewspace_grad | (uintptr_t)max_radii2D | (uintptr_t)xyz_gradient_accum | (uintptr_t)denom) & 15u) != 0 ||
+      ((uintptr_t)update_filter & 3u) != 0) {
+    set_error("gsm_densification_stats: arrays must be 16-byte aligned (the filter 4-byte)"); return GSM_ERR_INVALID_ARGUMENT;
+  }
+  const size_t groups = (P + 3) / 4, ctas = (groups + DENS_THREADS - 1) / DENS_THREADS;
+  if (ctas > 0x7fffffffull) { set_error("gsm_densification_stats: too many surfels"); return GSM_ERR_INVALID_ARGUMENT; }
+  densification_stats_kernel<<<(unsigned)ctas, DENS_THREADS, 0, stream>>>(radii, viewspace_grad, update_filter, max_radii2D,
+                                                                        xyz_gradient_accum, denom, P);
   GSM_CUDA(cudaGetLastError());
   return GSM_OK;
 }

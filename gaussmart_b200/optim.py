@@ -64,3 +64,35 @@ class FusedAdam(torch.optim.Optimizer):
                 stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
                 _lib.check(lib.gsm_adam_step(arr, len(tensors), stream), "adam_step")
         return loss
+
+
+@torch.no_grad()
+def add_densification_stats(max_radii2D, xyz_gradient_accum, denom, radii, viewspace_grad, update_filter=None):
+    """train.py:199-203 + GaussianModel.add_densification_stats (scene/gaussian_model.py:551-553) in one launch
+    (gsm_densification_stats, csrc/adam.cu), in place on the model's three statistics tensors:
+
+        max_radii2D[f] = max(max_radii2D[f], radii[f]);  xyz_gradient_accum[f] += ||viewspace_grad[f]||;  denom[f] += 1
+
+    `update_filter` None means radii > 0 (render()'s visibility_filter).  A maintainer's call site:
+        add_densification_stats(g.max_radii2D, g.xyz_gradient_accum, g.denom, radii, viewspace_point_tensor.grad)
+    No CPU or torch fallback."""
+    P = radii.shape[0]
+    for name, t, dt, n in (("max_radii2D", max_radii2D, torch.float32, P), ("xyz_gradient_accum", xyz_gradient_accum, torch.float32, P),
+                           ("denom", denom, torch.float32, P), ("radii", radii, torch.int32, P),
+                           ("viewspace_grad", viewspace_grad, torch.float32, 3 * P)):
+        if not t.is_cuda:
+            raise RuntimeError(f"gaussmart_b200.add_densification_stats: {name} must be a CUDA tensor (there is no CPU path)")
+        if t.dtype != dt or t.numel() != n or not t.is_contiguous():
+            raise ValueError(f"gaussmart_b200.add_densification_stats: {name} must be contiguous {dt} with {n} elements")
+    f = None
+    if update_filter is not None:
+        if not update_filter.is_cuda:
+            raise RuntimeError("gaussmart_b200.add_densification_stats: update_filter must be a CUDA tensor")
+        if update_filter.dtype not in (torch.bool, torch.uint8) or update_filter.numel() != P or not update_filter.is_contiguous():
+            raise ValueError(f"gaussmart_b200.add_densification_stats: update_filter must be contiguous bool with {P} elements")
+        f = update_filter.data_ptr()
+    lib = _lib.load()
+    with torch.cuda.device(radii.device):
+        stream = ctypes.c_void_p(torch.cuda.current_stream(radii.device).cuda_stream)
+        _lib.check(lib.gsm_densification_stats(radii.data_ptr(), viewspace_grad.data_ptr(), f, max_radii2D.data_ptr(),
+                                               xyz_gradient_accum.data_ptr(), denom.data_ptr(), P, stream), "densification_stats")

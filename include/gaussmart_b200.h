@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 5
+#define GSM_ABI_VERSION 6
 
 #define GSM_OK 0
 #define GSM_ERR_INVALID_ARGUMENT 10001
@@ -225,6 +225,16 @@ typedef struct gsm_adam_tensor {
   int step;
 } gsm_adam_tensor;
 int gsm_adam_step(const gsm_adam_tensor* tensors, int n_tensors, void* stream);
+
+/* ---- densification bookkeeping of the training iteration (second half).  Replaces, in ONE pass,
+ *      train.py:199-203  `gaussians.max_radii2D[vf] = torch.max(gaussians.max_radii2D[vf], radii[vf])`  and
+ *      GaussianModel.add_densification_stats (scene/gaussian_model.py:551-553)
+ *        xyz_gradient_accum[uf] += torch.norm(viewspace_point_tensor.grad[uf], dim=-1, keepdim=True);  denom[uf] += 1
+ *      radii int32 [P] (the rasterizer's output), viewspace_grad fp32 [P,3] (the gradient the backward leaves on
+ *      means2D), update_filter bool/uint8 [P] or NULL (= radii > 0, render()'s visibility_filter);
+ *      max_radii2D [P], xyz_gradient_accum [P,1], denom [P,1] fp32, updated in place.  16-byte aligned arrays. */
+int gsm_densification_stats(const int* radii, const float* viewspace_grad, const unsigned char* update_filter,
+                            float* max_radii2D, float* xyz_gradient_accum, float* denom, size_t P, void* stream);
 
 /* ---- surface regularisers of the training iteration.  Replaces, fused, the allmap
  *      post-processing of render() (gaussian_renderer/__init__.py:117-147: world-space normal, nan_to_num'd median and

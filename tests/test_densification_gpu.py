@@ -1,0 +1,66 @@
+"""gsm_densification_stats / gaussmart_b200.optim.add_densification_stats against the reference's own statements
+(train.py:199-203 and scene/gaussian_model.py:551-553), run with torch on the same device and inputs.
+
+Bar: max_radii2D and denom bit-exact (integer-valued fp32); xyz_gradient_accum within 1 ulp of torch's three-element norm
+per accumulation (|a - b| <= 2.4e-7 * |b| after each call, written here) -- and the fraction that is equal to the last
+bit is printed and must be >= 99 %."""
+import pytest
+import torch
+
+from gaussmart_b200.optim import add_densification_stats
+
+pytestmark = pytest.mark.gpu
+
+
+def reference_update(max_radii2D, xyz_gradient_accum, denom, radii, grad, update_filter=None):
+    visibility_filter = radii > 0 if update_filter is None else update_filter
+    max_radii2D[visibility_filter] = torch.max(max_radii2D[visibility_filter], radii[visibility_filter])  # train.py:199-202
+    xyz_gradient_accum[visibility_filter] += torch.norm(grad[visibility_filter], dim=-1, keepdim=True)  # gaussian_model.py:552
+    denom[visibility_filter] += 1  # gaussian_model.py:553
+
+
+def make(P, seed):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    radii = torch.randint(0, 300, (P,), generator=g, dtype=torch.int32)
+    radii[torch.rand(P, generator=g) < 0.3] = 0  # culled surfels
+    grad = torch.randn(P, 3, generator=g) * 10.0 ** torch.randint(-24, 1, (P, 1), generator=g).float()  # down to denormal squares
+    grad[radii == 0] = 0.0
+    grad[torch.rand(P, generator=g) < 0.05] = 0.0  # visible, no gradient
+    return radii.cuda(), grad.cuda()
+
+
+@pytest.mark.parametrize("P", [0, 1, 3, 4, 5, 1023, 100_003, 1_000_000])
+@pytest.mark.parametrize("explicit_filter", [False, True])
+def test_densification_stats_matches_reference_statements(P, explicit_filter):
+    ours = [torch.zeros(P, device="cuda"), torch.zeros(P, 1, device="cuda"), torch.zeros(P, 1, device="cuda")]
+    ref = [t.clone() for t in ours]
+    for it in range(3):
+        radii, grad = make(P, 100 * P + it)
+        filt = None
+        if explicit_filter:  # a filter that is not radii > 0: some culled surfels selected, some visible ones not
+            filt = (torch.rand(P, generator=torch.Generator().manual_seed(it)) < 0.6).cuda()
+        add_densification_stats(*ours, radii, grad, filt)
+        reference_update(*ref, radii, grad, filt)
+        torch.cuda.synchronize()
+        assert torch.equal(ours[0], ref[0]), "max_radii2D"
+        assert torch.equal(ours[2], ref[2]), "denom"
+        assert torch.all((ours[1] - ref[1]).abs() <= 2.4e-7 * ref[1].abs()), "xyz_gradient_accum beyond 1 ulp"
+        if P:
+            same = (ours[1] == ref[1]).float().mean().item()
+            print(f"P={P} it={it} bit-identical accum: {100 * same:.3f} %")
+            assert same >= 0.99
+        ours[1].copy_(ref[1])  # the next accumulation starts from the same state
+
+
+def test_densification_stats_rejects_bad_arguments():
+    P = 8
+    mr, acc, den = torch.zeros(P, device="cuda"), torch.zeros(P, 1, device="cuda"), torch.zeros(P, 1, device="cuda")
+    radii, grad = make(P, 1)
+    with pytest.raises(ValueError):
+        add_densification_stats(mr, acc, den, radii.long(), grad)
+    with pytest.raises(ValueError):
+        add_densification_stats(mr, acc, den, radii, grad[:, :2].contiguous())
+    with pytest.raises(ValueError):
+        add_densification_stats(mr, acc, den, radii, grad, torch.ones(P + 1, dtype=torch.bool, device="cuda"))
+    with pytest.raises(RuntimeError):
+        add_densification_stats(mr.cpu(), acc, den, radii, grad)

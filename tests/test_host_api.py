@@ -62,6 +62,9 @@ def test_cpu_tensors_are_rejected_not_silently_computed():
         gb.distCUDA2(torch.zeros(8, 3))
     with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
         r.markVisible(x)
+    from gaussmart_b200.optim import add_densification_stats
+    with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+        add_densification_stats(torch.zeros(4), torch.zeros(4, 1), torch.zeros(4, 1), torch.ones(4, dtype=torch.int32), x)
 
 
 def test_means3d_shape_message():

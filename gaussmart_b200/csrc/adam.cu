@@ -114,14 +114,15 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_step_kernel(const __grid_co
 // render()'s visibility_filter),
 //     max_radii2D = max(max_radii2D, (float)radii);  xyz_gradient_accum += ||viewspace_grad[i, :]||_2;  denom += 1
 // Six indexed torch ops with boolean-mask gathers in the reference; here one pass, four surfels per thread so that every
-// stream is a 128-bit access ([P,3] gradient rows: 3 x float4 per four surfels).  The norm is sqrt((x*x + y*y) + z*z)
-// with separately rounded products (no fma contraction), the association of torch's three-element norm reduction.
+// stream is a 128-bit access ([P,3] gradient rows: 3 x float4 per four surfels).  The norm is sqrt((x*x + z*z) + y*y)
+// with separately rounded products (no fma contraction): the association of torch's reduction over a contiguous dimension
+// of three (two lanes per output: lane 0 sums elements 0 and 2, lane 1 holds element 1, then one shuffle-add).
 constexpr int DENS_THREADS = 256;
 
 __device__ __forceinline__ void dens_update(bool on, int r, float gx, float gy, float gz, float& mr, float& acc, float& den) {
   if (!on) return;
   mr = fmaxf(mr, (float)r);
-  const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy)), __fmul_rn(gz, gz));
+  const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gz, gz)), __fmul_rn(gy, gy));
   acc = __fadd_rn(acc, sqrt_guarded(n2));
   den = __fadd_rn(den, 1.0f);
 }

@@ -1,9 +1,10 @@
 """gsm_densification_stats / gaussmart_b200.optim.add_densification_stats against the reference's own statements
 (train.py:199-203 and scene/gaussian_model.py:551-553), run with torch on the same device and inputs.
 
-Bar: max_radii2D and denom bit-exact (integer-valued fp32); xyz_gradient_accum within 1 ulp of torch's three-element norm
-per accumulation (|a - b| <= 2.4e-7 * |b| after each call, written here) -- and the fraction that is equal to the last
-bit is printed and must be >= 99 %."""
+Bar: all three tensors bit-exact in practice.  Written tolerance: max_radii2D and denom torch.equal (integer-valued fp32);
+xyz_gradient_accum within 1 ulp of torch's three-element norm per accumulation (|a - b| <= 2.4e-7 * |b| after each call)
+AND >= 99 % of the elements equal to the last bit (100 % observed: the kernel follows torch's association, see
+test_norm_association_probe)."""
 import pytest
 import torch
 
@@ -64,3 +65,17 @@ def test_densification_stats_rejects_bad_arguments():
         add_densification_stats(mr, acc, den, radii, grad, torch.ones(P + 1, dtype=torch.bool, device="cuda"))
     with pytest.raises(RuntimeError):
         add_densification_stats(mr.cpu(), acc, den, radii, grad)
+
+
+def test_norm_association_probe():
+    """Which association torch's own three-element norm uses on this build (printed with -s; the kernel follows the one
+    that matches, csrc/adam.cu dens_update)."""
+    _, grad = make(1_000_000, 3)
+    x, y, z = grad[:, 0], grad[:, 1], grad[:, 2]
+    ref = torch.norm(grad, dim=-1)
+    xy_z = torch.sqrt((x * x + y * y) + z * z)
+    xz_y = torch.sqrt((x * x + z * z) + y * y)
+    yz_x = torch.sqrt((y * y + z * z) + x * x)
+    fr = [float((c == ref).float().mean()) for c in (xy_z, xz_y, yz_x)]
+    print("torch.norm == sqrt((xx+yy)+zz): %.4f  ((xx+zz)+yy): %.4f  ((yy+zz)+xx): %.4f" % tuple(fr))
+    assert max(fr) > 0.5

@@ -220,6 +220,7 @@ class OursArm:
         gt_ready()
         loss = loss_fn(color, allmap, gt, cam_h, self.photometric, self.regularizer)
         loss.backward()
+        self.last_radii = radii
         return loss
 
     def render(self, cam_d):
@@ -305,6 +306,7 @@ class ReferenceArm:
         gt_ready()
         loss = loss_fn(color, allmap, gt, cam_d, self.photometric, self.regularizer)
         loss.backward()
+        self.last_radii = radii
         return loss
 
     def value_step(self, view):
@@ -759,6 +761,11 @@ def main():
             from gaussmart_b200.optim import FusedAdam
             opt = FusedAdam(groups, lr=0.0, eps=1e-15)
 
+        P_ = raw["xyz"].shape[0]  # max_radii2D, xyz_gradient_accum, denom (gaussian_model.py:58-60)
+        dens = [torch.zeros(P_, device=device), torch.zeros(P_, 1, device=device), torch.zeros(P_, 1, device=device)]
+        if args.impl != "reference":
+            from gaussmart_b200.optim import add_densification_stats
+
         def train_step(s):
             v = view_of(s)
             copy_stream.wait_stream(torch.cuda.current_stream())
@@ -770,6 +777,15 @@ def main():
                                      mats_dev[0:16].view(4, 4), mats_dev[16:32].view(4, 4), mats_dev[32:35])
             loss = arm.raw_step(raw, m2d, cam_d, gt_dev, c, gt_ready)
             loss_host.copy_(loss.detach(), non_blocking=False)
+            radii = arm.last_radii
+            if args.impl == "reference":  # train.py:199-203 + gaussian_model.py:551-553, the reference's statements
+                with torch.no_grad():
+                    vf = radii > 0
+                    dens[0][vf] = torch.max(dens[0][vf], radii[vf])
+                    dens[1][vf] += torch.norm(m2d.grad[vf], dim=-1, keepdim=True)
+                    dens[2][vf] += 1
+            else:
+                add_densification_stats(dens[0], dens[1], dens[2], radii, m2d.grad)
             opt.step()
         if args.impl == "ours":
             _lib.stage_timing_enable(True)
@@ -782,7 +798,9 @@ def main():
         train_iter = {"value": 1000.0 * args.steps / ms_train, "unit": UNIT, "ms_per_step": ms_train / args.steps,
                       "includes": "H2D of camera + ground truth, render() from the STORED parameters (getters of "
                                   "gaussian_model.py:104-123: torch ops for the reference, fused raw entry here), "
-                                  "L1+SSIM+regulariser loss, backward, loss read-back, Adam step over all 58 floats/surfel"}
+                                  "L1+SSIM+regulariser loss, backward, loss read-back, densification bookkeeping "
+                                  "(train.py:199-203), Adam step over all 58 floats/surfel",
+                      "densification_checksum": [float(t.double().sum()) for t in dens]}
         if train_stages:
             train_iter["stages_ms_per_step"] = train_stages
         del opt

@@ -905,4 +905,14 @@ def main():
 
 
 if __name__ == "__main__":
-    sys.exit(main())
+    # stdout carries the ONE JSON line and nothing else: libraries that write to file descriptor 1 (NCCL prints its
+    # version banner there when NCCL_DEBUG is set on the box) are sent to stderr for the duration of the run.
+    sys.stdout.flush()
+    _json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = _json_out
+    try:
+        _rc = main()
+    finally:
+        _json_out.flush()
+    sys.exit(_rc)

@@ -17,7 +17,7 @@ GSM_ERR_BINNING_OVERFLOW = 10002
 GSM_ERR_WORKSPACE_TOO_SMALL = 10003
 GSM_SURFEL_RECORD_BYTES = 80
 GSM_GRAD_RECORD_FLOATS = 20
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 EXPORTS = [
     "gsm_last_error", "gsm_abi_version", "gsm_geometry_bytes", "gsm_image_bytes", "gsm_binning_bytes", "gsm_binning_persistent_bytes",
@@ -28,6 +28,7 @@ EXPORTS = [
     "gsm_sort_pairs32_temp_bytes", "gsm_sort_pairs32", "gsm_sh_grad_expand",
     "gsm_photometric_loss_workspace_bytes", "gsm_photometric_loss", "gsm_adam_step", "gsm_densification_stats",
     "gsm_surface_regularizer_workspace_bytes", "gsm_surface_regularizer",
+    "gsm_status_create", "gsm_status_destroy", "gsm_status_query", "gsm_status_wait",
 ]
 
 
@@ -57,7 +58,7 @@ class ForwardArgs(Structure):
         ("image", c_void_p), ("image_bytes", c_size_t),
         ("binning", c_void_p), ("binning_bytes", c_size_t), ("binning_capacity", c_size_t),
         ("num_rendered_host", POINTER(c_int)), ("work_counters", c_void_p),
-        ("shs_rest", c_void_p), ("raw_params", c_int),
+        ("shs_rest", c_void_p), ("raw_params", c_int), ("status", c_void_p),
     ]
 
 
@@ -148,6 +149,14 @@ def load():
     lib.gsm_adam_step.argtypes = [POINTER(AdamTensor), c_int, c_void_p]
     lib.gsm_densification_stats.restype = c_int
     lib.gsm_densification_stats.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
+    lib.gsm_status_create.restype = c_int
+    lib.gsm_status_create.argtypes = [POINTER(c_void_p)]
+    lib.gsm_status_destroy.restype = c_int
+    lib.gsm_status_destroy.argtypes = [c_void_p]
+    lib.gsm_status_query.restype = c_int
+    lib.gsm_status_query.argtypes = [c_void_p]
+    lib.gsm_status_wait.restype = c_int
+    lib.gsm_status_wait.argtypes = [c_void_p, POINTER(ctypes.c_longlong), POINTER(c_int), POINTER(c_int)]
     if lib.gsm_abi_version() != ABI_VERSION:
         raise ImportError(f"gaussmart_b200: ABI version mismatch ({lib.gsm_abi_version()} != {ABI_VERSION})")
     _lib = lib

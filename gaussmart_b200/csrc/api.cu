@@ -159,6 +159,55 @@ extern "C" size_t gsm_grad_workspace_bytes(int P) {
   return align_up((size_t)(P > 0 ? P : 0) * GSM_GRAD_RECORD_FLOATS * 4, 128) + 128;
 }
 
+// ---- status slots of the asynchronous forward ---------------------------------------------------------------
+namespace {
+struct StatusSlot {
+  ForwardStatus* host;  // pinned
+  cudaEvent_t ready;    // recorded right after the status copy, i.e. behind the scan, not behind the whole forward
+  bool armed;
+};
+}  // namespace
+
+extern "C" int gsm_status_create(void** out) {
+  if (out == nullptr) { set_error("gsm_status_create: null output"); return GSM_ERR_INVALID_ARGUMENT; }
+  StatusSlot* s = new StatusSlot{nullptr, nullptr, false};
+  cudaError_t e = cudaHostAlloc((void**)&s->host, sizeof(ForwardStatus), cudaHostAllocDefault);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s->ready, cudaEventDisableTiming);
+  if (e != cudaSuccess) {
+    if (s->host) cudaFreeHost(s->host);
+    delete s;
+    return cuda_fail(e, "gsm_status_create");
+  }
+  memset(s->host, 0, sizeof(ForwardStatus));
+  *out = s;
+  return GSM_OK;
+}
+extern "C" int gsm_status_destroy(void* status) {
+  StatusSlot* s = (StatusSlot*)status;
+  if (s == nullptr) return GSM_OK;
+  cudaEventDestroy(s->ready);
+  cudaFreeHost(s->host);
+  delete s;
+  return GSM_OK;
+}
+extern "C" int gsm_status_query(void* status) {
+  StatusSlot* s = (StatusSlot*)status;
+  if (s == nullptr || !s->armed) return 1;
+  const cudaError_t e = cudaEventQuery(s->ready);
+  if (e == cudaSuccess) return 1;
+  if (e == cudaErrorNotReady) return 0;
+  return -cuda_fail(e, "gsm_status_query");
+}
+extern "C" int gsm_status_wait(void* status, long long* num_rendered, int* overflow, int* prefiltered_violation) {
+  StatusSlot* s = (StatusSlot*)status;
+  if (s == nullptr) { set_error("gsm_status_wait: null status"); return GSM_ERR_INVALID_ARGUMENT; }
+  if (s->armed) GSM_CUDA(cudaEventSynchronize(s->ready));
+  if (num_rendered) *num_rendered = (long long)s->host->num_rendered;
+  if (overflow) *overflow = (int)s->host->overflow;
+  if (prefiltered_violation) *prefiltered_violation = (int)s->host->prefiltered_violation;
+  return GSM_OK;
+}
+
 static char* aligned_base(const void* p) {
   return reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), 128));
 }
@@ -196,7 +245,12 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
   uint2* ranges = (uint2*)(img + I.ranges);
   uint32_t* tile_count = (uint32_t*)(img + I.tile_count);
   uint32_t* tile_cursor = (uint32_t*)(img + I.tile_cursor);
-  unsigned long long* total_dev = (unsigned long long*)(img + I.num_rendered);
+  ForwardStatus* status_dev = (ForwardStatus*)(img + I.num_rendered);
+  StatusSlot* slot = (StatusSlot*)a->status;
+  const BinningLayout B = binning_layout(a->binning_capacity, W, H);
+  if (slot != nullptr && P > 0 && (a->binning == nullptr || a->binning_bytes < B.total)) {
+    set_error("gsm_forward: the asynchronous mode needs the binning workspace up front"); return GSM_ERR_WORKSPACE_TOO_SMALL;
+  }
 
   int R = 0;
   if (P > 0) {
@@ -214,32 +268,44 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     GSM_STAGE("forward preprocess");
     {
       StageMark m(GSM_STAGE_SCAN, stream);
-      launch_tile_scan(tile_count, tile_cursor, ranges, num_tiles, total_dev, stream);
+      launch_tile_scan(tile_count, tile_cursor, ranges, num_tiles, (unsigned long long)a->binning_capacity, flags,
+                       status_dev, stream);
     }
     GSM_STAGE("tile-count scan");
-    // S1: the one host<-device dependency of the forward (rasterizer_impl.cu:282)
-    unsigned long long host_total = 0;
-    uint32_t host_flag = 0;
-    GSM_CUDA(cudaMemcpyAsync(&host_total, total_dev, 8, cudaMemcpyDeviceToHost, stream));
-    GSM_CUDA(cudaMemcpyAsync(&host_flag, flags, 4, cudaMemcpyDeviceToHost, stream));
-    GSM_CUDA(cudaStreamSynchronize(stream));
-    if (host_flag != 0) {
-      set_error("Point is filtered although prefiltered is set. This shouldn't happen!");
-      return GSM_ERR_INVALID_ARGUMENT;
+    if (slot != nullptr) {
+      // asynchronous mode: R travels to the pinned slot behind the scan; nothing below depends on it on the host
+      GSM_CUDA(cudaMemcpyAsync(slot->host, status_dev, sizeof(ForwardStatus), cudaMemcpyDeviceToHost, stream));
+      GSM_CUDA(cudaEventRecord(slot->ready, stream));
+      slot->armed = true;
+      R = -1;
+    } else {
+      // S1: the one host<-device dependency of the reference's forward (rasterizer_impl.cu:282)
+      ForwardStatus host_status{};
+      GSM_CUDA(cudaMemcpyAsync(&host_status, status_dev, sizeof(ForwardStatus), cudaMemcpyDeviceToHost, stream));
+      GSM_CUDA(cudaStreamSynchronize(stream));
+      if (host_status.prefiltered_violation != 0) {
+        set_error("Point is filtered although prefiltered is set. This shouldn't happen!");
+        return GSM_ERR_INVALID_ARGUMENT;
+      }
+      if (host_status.num_rendered > 0x7fffffffull) { set_error("gsm_forward: too many instances"); return GSM_ERR_INVALID_ARGUMENT; }
+      R = (int)host_status.num_rendered;
     }
-    if (host_total > 0x7fffffffull) { set_error("gsm_forward: too many instances"); return GSM_ERR_INVALID_ARGUMENT; }
-    R = (int)host_total;
   } else {
     GSM_CUDA(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream));
+    GSM_CUDA(cudaMemsetAsync(status_dev, 0, sizeof(ForwardStatus), stream));
+    if (slot != nullptr) {
+      GSM_CUDA(cudaMemcpyAsync(slot->host, status_dev, sizeof(ForwardStatus), cudaMemcpyDeviceToHost, stream));
+      GSM_CUDA(cudaEventRecord(slot->ready, stream));
+      slot->armed = true;
+    }
   }
   *a->num_rendered_host = R;
-  if ((size_t)R > a->binning_capacity) {
+  if (R >= 0 && (size_t)R > a->binning_capacity) {
     set_error("gsm_forward: binning capacity %zu < num_rendered %d", a->binning_capacity, R);
     return GSM_ERR_BINNING_OVERFLOW;
   }
-  const BinningLayout B = binning_layout(a->binning_capacity, W, H);
   char* bin = nullptr;
-  if (R > 0) {
+  if (R != 0) {
     if (a->binning == nullptr || a->binning_bytes < B.total) {
       set_error("gsm_forward: binning workspace too small"); return GSM_ERR_WORKSPACE_TOO_SMALL;
     }
@@ -247,14 +313,14 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     uint2* pairs = (uint2*)(bin + B.pairs);
     {
       StageMark m(GSM_STAGE_DUPLICATE, stream);
-      launch_scatter(P, (const uint4*)(geom + G.rects), a->radii, tile_cursor, pairs, grid_x, stream);
+      launch_scatter(P, (const uint4*)(geom + G.rects), a->radii, tile_cursor, pairs, grid_x, status_dev, stream);
     }
     GSM_STAGE("scatter");
     {
       StageMark m(GSM_STAGE_SORT, stream);
       launch_tile_sort(ranges, pairs, (uint64_t*)(bin + B.keys_sorted), (uint32_t*)(bin + B.point_list),
                        (uint8_t*)(bin + B.strip_mask), (const short4*)(geom + G.bbox), (const float4*)(geom + G.cull), grid_x, num_tiles,
-                       (a->debug & 2) ? 1 : 0, stream);
+                       (a->debug & 2) ? 1 : 0, status_dev, stream);
     }
     GSM_STAGE("tile sort");
   }
@@ -271,6 +337,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     rp.final_T = (float*)(img + I.final_T); rp.n_contrib = (uint32_t*)(img + I.n_contrib);
     rp.out_color = a->out_color; rp.out_others = a->out_others;
     rp.stats = (unsigned long long*)a->work_counters;
+    rp.status = status_dev;
     { StageMark m(GSM_STAGE_RENDER_FWD, stream); launch_render_fwd(rp, stream); }
     GSM_STAGE("forward render");
   } else {

@@ -38,7 +38,8 @@ constexpr int TSCAN_THREADS = 1024;
 // serialise in L2 (~27 cycles each): one cursor per tile makes the hottest tile the critical path.
 __global__ void __launch_bounds__(TSCAN_THREADS)
 tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_cursor,
-                 uint2* __restrict__ ranges, int num_tiles, unsigned long long* __restrict__ total_out) {
+                 uint2* __restrict__ ranges, int num_tiles, unsigned long long capacity,
+                 const uint32_t* __restrict__ flags, ForwardStatus* __restrict__ status) {
   // one CTA walks the tiles in chunks of TSCAN_THREADS, one tile (TILE_SUBS counters = 32 B) per thread and chunk, so
   // every access is coalesced; the next chunk's counters are requested before the current chunk is scanned
   __shared__ unsigned long long warp_sums[2][TSCAN_THREADS / 32];
@@ -86,12 +87,20 @@ tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__
     }
     carry += total;
   }
-  if (t == 0) *total_out = carry;
+  if (t == 0) {
+    // R, and whether it fits the binning workspace the host sized from its high-water mark: if not, every kernel
+    // behind this one treats the frame as empty (see ForwardStatus) and the host renders it again with a larger one
+    ForwardStatus st;
+    st.num_rendered = carry;
+    st.overflow = carry > capacity ? 1u : 0u;
+    st.prefiltered_violation = flags[0];
+    *status = st;
+  }
 }
 
 void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* ranges, int num_tiles,
-                      unsigned long long* total_out, cudaStream_t stream) {
-  tile_scan_kernel<<<1, TSCAN_THREADS, 0, stream>>>(tile_count, tile_cursor, ranges, num_tiles, total_out);
+                      unsigned long long capacity, const uint32_t* flags, ForwardStatus* status, cudaStream_t stream) {
+  tile_scan_kernel<<<1, TSCAN_THREADS, 0, stream>>>(tile_count, tile_cursor, ranges, num_tiles, capacity, flags, status);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -100,7 +109,9 @@ void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* 
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ radii,
-               uint32_t* __restrict__ tile_cursor, uint2* __restrict__ pairs, int grid_x) {
+               uint32_t* __restrict__ tile_cursor, uint2* __restrict__ pairs, int grid_x,
+               const ForwardStatus* __restrict__ status) {
+  if (status->overflow) return;  // R exceeds the pair buffer: nothing may be appended
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
   int r = 0;
@@ -153,9 +164,9 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ r
 }
 
 void launch_scatter(int P, const uint4* rects, const int* radii, uint32_t* tile_cursor, uint2* pairs,
-                    int grid_x, cudaStream_t stream) {
+                    int grid_x, const ForwardStatus* status, cudaStream_t stream) {
   if (P <= 0) return;
-  scatter_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, rects, radii, tile_cursor, pairs, grid_x);
+  scatter_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, rects, radii, tile_cursor, pairs, grid_x, status);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -183,6 +194,7 @@ struct TileSortParams {
   int no_cull;
   uint32_t n_lo, n_hi;     // this launch handles segments with n_lo < n <= n_hi
   uint32_t cap;            // pairs per shared-memory buffer (0: global-memory class)
+  const ForwardStatus* status;
 };
 
 // One stable LSD pass over `bits` bits at `shift`: A -> B.  Warp w owns the contiguous range
@@ -203,7 +215,8 @@ __device__ __forceinline__ unsigned digit_peers(uint32_t d, bool valid, int bits
 
 // ITEMS > 0 and `cached`: the segment fits ITEMS elements per thread (shared-memory classes), so the elements and
 // their peer masks found in sweep 1 stay in registers for sweep 2 (no second read, no second round of ballots).
-template <int THREADS, int MAXBITS, int ITEMS>
+// BY_ID: digits are taken from the surfel index (e.y) instead of the depth bits (e.x): the tie-break passes.
+template <int THREADS, int MAXBITS, int ITEMS, bool BY_ID>
 __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* __restrict__ B, uint32_t n,
                                            uint32_t kmin, int shift, int bits, uint32_t (*whist)[1 << MAXBITS],
                                            uint32_t* warp_tot, int t, int lane, int warp, bool cached) {
@@ -227,7 +240,7 @@ __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* _
         const bool valid = i < wend;
         uint2 e = make_uint2(0u, 0u);
         if (valid) e = A[i];
-        const uint32_t d = valid ? (((e.x - kmin) >> shift) & dmask) : 0u;
+        const uint32_t d = valid ? ((((BY_ID ? e.y : e.x) - kmin) >> shift) & dmask) : 0u;
         const unsigned peers = digit_peers(d, valid, bits);
         if (valid && lane == __ffs(peers) - 1) whist[warp][d] += __popc(peers);
         ce[k] = e;
@@ -239,7 +252,7 @@ __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* _
     for (uint32_t it = wbeg; it < wend; it += 32) {
       const uint32_t i = it + lane;
       const bool valid = i < wend;
-      const uint32_t d = valid ? (((A[i].x - kmin) >> shift) & dmask) : 0u;
+      const uint32_t d = valid ? ((((BY_ID ? A[i].y : A[i].x) - kmin) >> shift) & dmask) : 0u;
       const unsigned peers = digit_peers(d, valid, bits);
       if (valid && lane == __ffs(peers) - 1) whist[warp][d] += __popc(peers);
       __syncwarp();
@@ -289,7 +302,7 @@ __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* _
         const unsigned peers = cp[k];
         const bool valid = peers != 0u;
         const uint2 e = ce[k];
-        const uint32_t d = ((e.x - kmin) >> shift) & dmask;
+        const uint32_t d = (((BY_ID ? e.y : e.x) - kmin) >> shift) & dmask;
         const int leader = valid ? __ffs(peers) - 1 : lane;
         const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
         uint32_t old = 0;
@@ -307,7 +320,7 @@ __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* _
     const bool valid = i < wend;
     uint2 e = make_uint2(0u, 0u);
     if (valid) e = A[i];
-    const uint32_t d = valid ? (((e.x - kmin) >> shift) & dmask) : 0u;
+    const uint32_t d = valid ? ((((BY_ID ? e.y : e.x) - kmin) >> shift) & dmask) : 0u;
     const unsigned peers = digit_peers(d, valid, bits);
     const int leader = valid ? __ffs(peers) - 1 : lane;
     const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
@@ -331,7 +344,7 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
   const uint32_t tile = blockIdx.x;
   const uint2 range = __ldg(p.ranges + tile);
   const uint32_t n = range.y - range.x;
-  if (n <= p.n_lo || n > p.n_hi) return;
+  if (n <= p.n_lo || n > p.n_hi || p.status->overflow) return;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const bool in_smem = p.cap != 0;
   uint2* A = in_smem ? ts_dyn : p.pairs + range.x;
@@ -358,20 +371,50 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
   const int passes = (nbits + MAXBITS - 1) / MAXBITS;
   const int bits = passes ? (nbits + passes - 1) / passes : 0;  // equal digit widths, <= MAXBITS
   for (int shift = 0; shift < nbits; shift += bits) {
-    radix_pass<THREADS, MAXBITS, ITEMS>(A, B, n, kmin, shift, bits, whist, warp_tot, t, lane, warp, in_smem);
+    radix_pass<THREADS, MAXBITS, ITEMS, false>(A, B, n, kmin, shift, bits, whist, warp_tot, t, lane, warp, in_smem);
     uint2* tmp = A; A = B; B = tmp;
   }
-  // equal depth bits: ascending surfel index (the reference's stable sort keeps emission order)
-  for (uint32_t i = t; i + 1 < n; i += THREADS) {
-    const uint32_t k = A[i].x;
-    if (A[i + 1].x == k && (i == 0 || A[i - 1].x != k)) {
-      uint32_t j = i + 1;
-      while (j + 1 < n && A[j + 1].x == k) j++;
-      for (uint32_t a = i + 1; a <= j; a++) {  // insertion sort of the run's surfel indices
-        const uint32_t v = A[a].y;
-        uint32_t b = a;
-        while (b > i && A[b - 1].y > v) { A[b].y = A[b - 1].y; b--; }
-        A[b].y = v;
+  // Equal depth bits must come out in ascending surfel index (the reference's STABLE sort keeps its emission order,
+  // rasterizer_impl.cu:70-111,304-309), and the scatter appended in arbitrary order.  Ties are rare (cloned surfels:
+  // runs of 2), so short runs are fixed in place; a segment with a run longer than TIE_RUN (a fronto-parallel planar
+  // cloud: thousands of equal view depths in one tile) is instead re-sorted as a whole on (depth, surfel): LSD passes
+  // over the surfel-index span first, then the depth passes again -- O(n) per pass, no O(run^2) cliff.
+  constexpr uint32_t TIE_RUN = 4;
+  bool long_run = false;
+  for (uint32_t i = t; i + TIE_RUN < n; i += THREADS) long_run |= A[i].x == A[i + TIE_RUN].x;
+  if (__syncthreads_or(long_run)) {
+    uint32_t imin = 0xffffffffu, imax = 0u;
+    for (uint32_t i = t; i < n; i += THREADS) { const uint32_t k = A[i].y; imin = min(imin, k); imax = max(imax, k); }
+    imin = __reduce_min_sync(0xffffffffu, imin);
+    imax = __reduce_max_sync(0xffffffffu, imax);
+    if (lane == 0) { warp_tot[warp] = imax; warp_min[warp] = imin; }
+    __syncthreads();
+    for (int w = 0; w < WARPS; w++) { imax = max(imax, warp_tot[w]); imin = min(imin, warp_min[w]); }
+    __syncthreads();
+    const uint32_t ispan = imax - imin;
+    const int ibits_all = ispan ? 32 - __clz(ispan) : 0;
+    const int ipasses = (ibits_all + MAXBITS - 1) / MAXBITS;
+    const int ibits = ipasses ? (ibits_all + ipasses - 1) / ipasses : 0;
+    for (int shift = 0; shift < ibits_all; shift += ibits) {
+      radix_pass<THREADS, MAXBITS, ITEMS, true>(A, B, n, imin, shift, ibits, whist, warp_tot, t, lane, warp, in_smem);
+      uint2* tmp = A; A = B; B = tmp;
+    }
+    for (int shift = 0; shift < nbits; shift += bits) {
+      radix_pass<THREADS, MAXBITS, ITEMS, false>(A, B, n, kmin, shift, bits, whist, warp_tot, t, lane, warp, in_smem);
+      uint2* tmp = A; A = B; B = tmp;
+    }
+  } else {
+    for (uint32_t i = t; i + 1 < n; i += THREADS) {
+      const uint32_t k = A[i].x;
+      if (A[i + 1].x == k && (i == 0 || A[i - 1].x != k)) {
+        uint32_t j = i + 1;
+        while (j + 1 < n && A[j + 1].x == k) j++;
+        for (uint32_t a = i + 1; a <= j; a++) {  // insertion sort of the run's <= TIE_RUN surfel indices
+          const uint32_t v = A[a].y;
+          uint32_t b = a;
+          while (b > i && A[b - 1].y > v) { A[b].y = A[b - 1].y; b--; }
+          A[b].y = v;
+        }
       }
     }
   }
@@ -422,20 +465,19 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
 
 void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, uint32_t* point_list,
                       uint8_t* strip_mask, const short4* bbox, const float4* cull, int grid_x, int num_tiles,
-                      int no_cull, cudaStream_t stream) {
+                      int no_cull, const ForwardStatus* status, cudaStream_t stream) {
   auto small = tile_sort_kernel<TS_SMALL_THREADS, TS_SMALL_BITS, (TS_CAP_SMALL + TS_SMALL_THREADS - 1) / TS_SMALL_THREADS>;
   auto large = tile_sort_kernel<TS_LARGE_THREADS, TS_LARGE_BITS, (TS_CAP_LARGE + TS_LARGE_THREADS - 1) / TS_LARGE_THREADS>;
   constexpr size_t hist_small = (size_t)(TS_SMALL_THREADS / 32) * (1u << TS_SMALL_BITS) * 4;
   constexpr size_t hist_large = (size_t)(TS_LARGE_THREADS / 32) * (1u << TS_LARGE_BITS) * 4;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceLevel configured;  // the dynamic shared-memory limit is a per-device attribute
+  configured.ensure(1, [&] {
     cudaFuncSetAttribute(small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * TS_CAP_SMALL * sizeof(uint2) + hist_small));
     cudaFuncSetAttribute(large, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * TS_CAP_LARGE * sizeof(uint2) + hist_large));
-    configured = true;
-  }
+  });
   TileSortParams p{};
   p.ranges = ranges; p.pairs = pairs; p.keys_sorted = keys_sorted; p.point_list = point_list;
-  p.strip_mask = strip_mask; p.bbox = bbox; p.cull = cull; p.grid_x = grid_x; p.no_cull = no_cull;
+  p.strip_mask = strip_mask; p.bbox = bbox; p.cull = cull; p.grid_x = grid_x; p.no_cull = no_cull; p.status = status;
   p.n_lo = 0; p.n_hi = TS_CAP_SMALL; p.cap = TS_CAP_SMALL;
   small<<<num_tiles, TS_SMALL_THREADS, 2 * TS_CAP_SMALL * sizeof(uint2) + hist_small, stream>>>(p);
   p.n_lo = TS_CAP_SMALL; p.n_hi = TS_CAP_LARGE; p.cap = TS_CAP_LARGE;

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
+#include <mutex>
 #include "../../include/gaussmart_b200.h"
 
 namespace gsm {
@@ -94,13 +95,21 @@ struct GeometryLayout {
 };
 GeometryLayout geometry_layout(int P);
 
+// Device-side status of a forward (image workspace; copied to the pinned status slot in the asynchronous mode).
+// overflow != 0: R exceeded the binning capacity -> every kernel behind the scan treats the frame as EMPTY.
+struct ForwardStatus {
+  unsigned long long num_rendered;
+  uint32_t overflow;
+  uint32_t prefiltered_violation;
+};
+
 struct ImageLayout {
   size_t final_T;    // f32[3*N]  (T, M1, M2)
   size_t n_contrib;  // u32[2*N]  (last contributor, median contributor)
   size_t ranges;     // uint2[Nt]
   size_t tile_count;   // u32[Nt][TILE_SUBS]  instances per tile and sub-cursor (counted by the forward preprocess)
   size_t tile_cursor;  // u32[Nt][TILE_SUBS]  append cursors of the scatter
-  size_t num_rendered; // u64      R
+  size_t num_rendered; // ForwardStatus (R first)
   size_t total;
 };
 ImageLayout image_layout(int width, int height);
@@ -133,6 +142,25 @@ int cuda_fail(cudaError_t e, const char* what);
     if (_e == cudaSuccess && debug) _e = cudaStreamSynchronize(stream);         \
     if (_e != cudaSuccess) return gsm::cuda_fail(_e, stage_name);               \
   } while (0)
+
+// ---- per-device one-time configuration -----------------------------------------------------
+// cudaFuncSetAttribute and __constant__ uploads are PER DEVICE; a per-process flag would leave the second device of a
+// process unconfigured.  ensure(want, f) runs f() on the current device unless that device already reached `want`.
+class PerDeviceLevel {
+ public:
+  template <class F>
+  void ensure(size_t want, F&& f) {
+    int d = 0;
+    cudaGetDevice(&d);
+    std::lock_guard<std::mutex> lk(mu_);
+    if (d < 0 || d >= kMax) { f(); return; }
+    if (level_[d] < want) { f(); level_[d] = want; }
+  }
+ private:
+  static constexpr int kMax = 64;
+  std::mutex mu_;
+  size_t level_[kMax] = {};
+};
 
 // ---- optional per-stage timing (api.cu) --------------------------------------------------
 enum {
@@ -199,12 +227,12 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
                          cudaStream_t stream);
 
 void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* ranges, int num_tiles,
-                      unsigned long long* total_out, cudaStream_t stream);
+                      unsigned long long capacity, const uint32_t* flags, ForwardStatus* status, cudaStream_t stream);
 void launch_scatter(int P, const uint4* rects, const int* radii, uint32_t* tile_cursor, uint2* pairs,
-                    int grid_x, cudaStream_t stream);
+                    int grid_x, const ForwardStatus* status, cudaStream_t stream);
 void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, uint32_t* point_list,
                       uint8_t* strip_mask, const short4* bbox, const float4* cull, int grid_x, int num_tiles, int no_cull,
-                      cudaStream_t stream);
+                      const ForwardStatus* status, cudaStream_t stream);
 
 struct FwdRenderParams {
   int W, H, grid_x, grid_y;
@@ -222,6 +250,7 @@ struct FwdRenderParams {
   float* out_color;
   float* out_others;
   unsigned long long* stats;  // optional work counters (NULL in production)
+  const ForwardStatus* status;  // overflow => the frame is composited as empty
 };
 void launch_render_fwd(const FwdRenderParams& p, cudaStream_t stream);
 
@@ -241,6 +270,7 @@ struct BwdRenderParams {
   const float* dL_dpix;
   const float* dL_dothers;
   float* grad_records;  // [P*GREC], zero-initialised
+  // (after an overflowed asynchronous forward n_contrib is 0 everywhere: the replay finds nothing to do)
 };
 void launch_render_bwd(const BwdRenderParams& p, cudaStream_t stream);
 

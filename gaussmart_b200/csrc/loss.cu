@@ -224,8 +224,8 @@ extern "C" int gsm_photometric_loss(const float* image, const float* gt, int C, 
   if (image == nullptr || gt == nullptr || dL_dimage == nullptr) { set_error("gsm_photometric_loss: null image / gt / gradient"); return GSM_ERR_INVALID_ARGUMENT; }
   const LossLayout L = loss_layout(C, H, W);
   if (workspace == nullptr || workspace_bytes < L.total) { set_error("gsm_photometric_loss: workspace too small"); return GSM_ERR_WORKSPACE_TOO_SMALL; }
-  static bool window_ready = false;
-  if (!window_ready) { upload_window(); window_ready = true; }
+  static PerDeviceLevel window_ready;  // c_gauss is a per-device symbol
+  window_ready.ensure(1, [] { upload_window(); });
   char* ws = (char*)workspace;
   double* sums = (double*)(ws + L.sums);
   const size_t n = (size_t)C * H * W;

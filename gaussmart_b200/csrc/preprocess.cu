@@ -377,12 +377,11 @@ void launch_preprocess_fwd(const FwdPreprocessParams& p, cudaStream_t stream) {
   if (p.P <= 0) return;
   const size_t smem = (p.colors_precomp == nullptr)
                           ? (size_t)(PFWD_THREADS / 32) * 32 * (3 * p.M + 1) * sizeof(float) : 0;
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  static PerDeviceLevel configured;
+  if (smem > 48 * 1024) configured.ensure(smem, [&] {
     cudaFuncSetAttribute(preprocess_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(preprocess_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = smem;
-  }
+  });
   if (p.raw || p.shs_rest != nullptr) preprocess_fwd_kernel<true><<<(p.P + PFWD_THREADS - 1) / PFWD_THREADS, PFWD_THREADS, smem, stream>>>(p);
   else preprocess_fwd_kernel<false><<<(p.P + PFWD_THREADS - 1) / PFWD_THREADS, PFWD_THREADS, smem, stream>>>(p);
 }

@@ -518,11 +518,10 @@ void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3
                            const float* drgb_all, float* dL_dsh, int accumulate, cudaStream_t stream) {
   if (P <= 0 || M <= 0) return;
   const size_t smem = (size_t)(PBWD_THREADS / 32) * 32 * (3 * M + 1) * sizeof(float);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  static PerDeviceLevel configured;
+  if (smem > 48 * 1024) configured.ensure(smem, [&] {
     cudaFuncSetAttribute(sh_grad_expand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = smem;
-  }
+  });
   sh_grad_expand_kernel<<<(P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(
       P, D, M, n_views, means3D, campos_all, drgb_all, dL_dsh, accumulate);
 }
@@ -531,12 +530,11 @@ void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3
 void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream) {
   if (p.P <= 0) return;
   const size_t smem = (size_t)(PBWD_THREADS / 32) * 32 * (3 * p.M + 1) * sizeof(float);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  static PerDeviceLevel configured;
+  if (smem > 48 * 1024) configured.ensure(smem, [&] {
     cudaFuncSetAttribute(preprocess_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = smem;
-  }
+  });
   if (p.raw || p.shs_rest != nullptr) preprocess_bwd_kernel<true><<<(p.P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(p);
   else preprocess_bwd_kernel<false><<<(p.P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(p);
 }

@@ -58,7 +58,8 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
   const uint32_t pixy = tile_y * TILE_Y + (uint32_t)block_py((int)strip, lane);
   const bool inside = pixx < (uint32_t)p.W && pixy < (uint32_t)p.H;
   const float pxf = (float)pixx, pyf = (float)pixy;
-  const uint2 range = __ldg(p.ranges + tile);
+  uint2 range = __ldg(p.ranges + tile);
+  if (p.status->overflow) range = make_uint2(0u, 0u);  // R exceeded the binning capacity: the frame is rendered empty
   const uint32_t total = range.y - range.x;
   const uint32_t strip_bit = 1u << strip;
 
@@ -238,7 +239,8 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
 void launch_render_fwd(const FwdRenderParams& p, cudaStream_t stream) {
   const unsigned strips = (unsigned)(p.grid_x * p.grid_y) * STRIPS_PER_TILE;
   const unsigned grid = (strips + FWD_WARPS - 1) / FWD_WARPS;
-  if (p.stats) render_fwd_kernel<true, true><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
+  if (p.stats && p.pix_mask != nullptr) render_fwd_kernel<true, true><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
+  else if (p.stats) render_fwd_kernel<true, false><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
   else if (p.pix_mask == nullptr) render_fwd_kernel<false, false><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
   else render_fwd_kernel<false, true><<<grid, FWD_WARPS * 32, 0, stream>>>(p);
 }

@@ -15,6 +15,7 @@ PyTorch is used for device memory, streams and autograd plumbing only; every ker
 shared library.  There is no CPU path: CPU tensors raise, as in rasterize_points.cu:27-28.
 """
 import ctypes
+import os
 from typing import NamedTuple
 
 import torch
@@ -47,9 +48,118 @@ def _f32c(name, t):
     return t.contiguous()
 
 
-# grow-only high-water mark of (surfel,tile) instances per device: sizes the binning workspace so
-# that steady-state iterations never take the overflow/retry path.
+# ---- sizing of the binning workspace without a per-forward host stall -------------------------------------------------
+# The reference reads R = num_rendered back with a blocking cudaMemcpy in the middle of every forward
+# (rasterizer_impl.cu:282) to size its binning buffer.  Here the workspace is sized from a grow-only high-water mark of
+# R per device, the whole forward is enqueued at once (gsm_forward's asynchronous mode), and R comes back through a
+# pinned status slot behind the scan.  WHEN the host looks at it is the policy:
+#   "event" (default) after everything is enqueued, wait for the slot's event -- it sits behind the SCAN, so the host
+#           resumes while scatter / sort / compositing are still queued or running and the device never idles; on
+#           overflow (R > capacity: the device rendered an empty frame) the forward is issued again with a larger
+#           workspace before anything is returned.  Exactly the reference's semantics.
+#   "lazy"  never wait in the forward: the status is read at backward entry, on the next forward of the device, or when
+#           `num_rendered` is converted to an int.  An overflow (R more than doubled against everything seen before)
+#           can then only be REPORTED -- the frame was rendered empty -- so it raises; for loops that own the whole
+#           iteration (view_parallel) and replay it.  Opt in with set_sync_policy("lazy") / GAUSSMART_B200_SYNC=lazy.
+#   "sync"  the reference's behaviour: gsm_forward's synchronous mode (one stream synchronisation per forward).
 _binning_capacity = {}
+_sync_policy = os.environ.get("GAUSSMART_B200_SYNC", "event")
+_HEADROOM = {"event": 1.25, "sync": 1.25, "lazy": 2.0}
+
+
+def set_sync_policy(policy):
+    """'event' | 'lazy' | 'sync' (see above); returns the previous policy."""
+    global _sync_policy
+    if policy not in _HEADROOM:
+        raise ValueError(f"unknown sync policy {policy!r}")
+    prev, _sync_policy = _sync_policy, policy
+    return prev
+
+
+class BinningOverflow(RuntimeError):
+    pass
+
+
+class _StatusSlots:
+    """Pool of gsm_status slots (16 B pinned + one event each), recycled."""
+    def __init__(self):
+        self.free = []
+
+    def take(self):
+        if self.free:
+            return self.free.pop()
+        h = ctypes.c_void_p()
+        _lib.check(_lib.load().gsm_status_create(ctypes.byref(h)), "status_create")
+        return h
+
+    def give(self, h):
+        self.free.append(h)
+
+
+_slots = _StatusSlots()
+_pending = {}  # device index -> list of unresolved PendingForward (lazy policy)
+
+
+class PendingForward:
+    """Status of one asynchronously issued forward: resolves to R = num_rendered."""
+    def __init__(self, slot, key, capacity, prefiltered):
+        self.slot, self.key, self.capacity, self.prefiltered = slot, key, capacity, prefiltered
+        self.value = None
+        self.overflow = False
+
+    def ready(self):
+        return self.value is not None or _lib.load().gsm_status_query(self.slot) == 1
+
+    def resolve(self):
+        if self.value is not None:
+            return self.value
+        R, ov, pf = ctypes.c_longlong(0), ctypes.c_int(0), ctypes.c_int(0)
+        _lib.check(_lib.load().gsm_status_wait(self.slot, ctypes.byref(R), ctypes.byref(ov), ctypes.byref(pf)), "status_wait")
+        _slots.give(self.slot)
+        self.slot = None
+        self.value, self.overflow = int(R.value), bool(ov.value)
+        lst = _pending.get(self.key[0])
+        if lst and self in lst:
+            lst.remove(self)
+        # grow-only high-water mark: the workspace keeps the policy's headroom over the largest R seen
+        want = int(self.value * _HEADROOM[_sync_policy]) + 1024
+        if want > _binning_capacity.get(self.key, 0):
+            _binning_capacity[self.key] = want
+        if pf:
+            raise RuntimeError("gaussmart_b200 forward failed: Point is filtered although prefiltered is set. "
+                               "This shouldn't happen!")
+        return self.value
+
+    def check(self):
+        """resolve() + raise if the frame overflowed the workspace (it was rendered empty)."""
+        self.resolve()
+        if self.overflow:
+            raise BinningOverflow(
+                f"gaussmart_b200: a forward issued under the 'lazy' sync policy produced {self.value} (surfel, tile) "
+                f"instances for a binning workspace of {self.capacity}: that frame was rendered EMPTY. The workspace "
+                "has been enlarged; render the frame again, or use set_sync_policy('event').")
+        return self.value
+
+    def __int__(self):
+        return self.check()
+
+    __index__ = __int__
+
+    def __eq__(self, other):
+        return int(self) == other
+
+    def __hash__(self):
+        return id(self)
+
+    def __repr__(self):
+        return f"PendingForward({self.value if self.value is not None else 'pending'})"
+
+
+def _drain_pending(dev_index, block=False):
+    """Resolve the device's outstanding lazy forwards that have passed their scan (all of them with block=True)."""
+    for pf in list(_pending.get(dev_index, ())):
+        if block or pf.ready():
+            pf.check()
 
 
 class _Workspaces(NamedTuple):
@@ -121,20 +231,45 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
         a.work_counters = _ptr(work_counters)
 
         key = (dev.index, )
+        policy = _sync_policy
+        if policy == "lazy":
+            _drain_pending(dev.index)
         capacity = _binning_capacity.get(key, 0)
+        pending = None
         while True:
             binning = torch.empty((lib.gsm_binning_bytes(capacity, W, H),), dtype=torch.uint8, device=dev)
             a.binning, a.binning_bytes, a.binning_capacity = _ptr(binning), binning.numel(), capacity
+            if policy == "sync" or capacity == 0 or P == 0:
+                # (first forward on a device: nothing to size from yet)
+                a.status = None
+                code = lib.gsm_forward(ctypes.byref(a), stream)
+                if code == _lib.GSM_ERR_BINNING_OVERFLOW:
+                    capacity = int(num_rendered.value * _HEADROOM[policy]) + 1024
+                    _binning_capacity[key] = capacity
+                    continue
+                _lib.check(code, "forward")
+                result = num_rendered.value
+                break
+            slot = _slots.take()
+            a.status = slot
             code = lib.gsm_forward(ctypes.byref(a), stream)
-            if code == _lib.GSM_ERR_BINNING_OVERFLOW:
-                capacity = int(num_rendered.value * 1.25) + 1024
-                _binning_capacity[key] = capacity
+            if code != _lib.GSM_OK:
+                _slots.give(slot)
+                _lib.check(code, "forward")
+            pending = PendingForward(slot, key, capacity, bool(prefiltered))
+            if policy == "lazy":
+                _pending.setdefault(dev.index, []).append(pending)
+                result = pending
+                break
+            result = pending.resolve()       # "event": behind the scan, with the rest of the forward already queued
+            if pending.overflow:             # rendered empty: again, with the enlarged workspace
+                capacity = _binning_capacity[key]
                 continue
-            _lib.check(code, "forward")
             break
     # the capacity the forward ran with travels with the buffer (backward needs it to find the strip masks)
     binning.gsm_capacity = capacity
-    return num_rendered.value, out_color, out_others, radii, geometry, binning, image
+    binning.gsm_handover = not forward_only
+    return result, out_color, out_others, radii, geometry, binning, image
 
 
 def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp, viewmatrix,
@@ -153,6 +288,11 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
     `rgb_out` (optional, [P,3]) selects the factored SH gradient: the kernel writes dL/dRGB there and no
     dL_dsh rows (gsm_backward_args.dL_drgb); `sh_grad_expand` rebuilds them."""
     lib = _lib.load()
+    if isinstance(num_rendered, PendingForward):
+        num_rendered.check()   # lazy policy: the forward's status is looked at here (its scan finished long ago)
+    if getattr(binningBuffer, "gsm_handover", True) is False:
+        raise RuntimeError("gaussmart_b200 backward: the forward was an inference render (forward_only: no "
+                           "forward->backward hand-over was written); its buffers cannot be back-propagated")
     P = means3D.shape[0]
     H, W = grad_out_color.shape[1], grad_out_color.shape[2]
     dev = means3D.device
@@ -164,6 +304,14 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
             raise RuntimeError("split SH storage and the factored SH gradient are not combined")
     grad_out_color = _f32c("dL_dout_color", grad_out_color)
     grad_depth = _f32c("dL_dout_others", grad_depth)
+    # autograd saves the tensors the CALLER passed: a strided view must be packed here as the forward packed it
+    # (rasterize_points.cu:112-130 calls .contiguous() on everything, forward and backward)
+    bg, means3D, colors_precomp = _f32c("background", bg), _f32c("means3D", means3D), _f32c("colors", colors_precomp)
+    scales, rotations, cov3Ds_precomp = _f32c("scales", scales), _f32c("rotations", rotations), _f32c("transMat_precomp", cov3Ds_precomp)
+    viewmatrix, projmatrix, campos = _f32c("viewmatrix", viewmatrix), _f32c("projmatrix", projmatrix), _f32c("campos", campos)
+    sh = _f32c("sh", sh)
+    if split:
+        sh_rest = _f32c("sh_rest", sh_rest)
     with torch.cuda.device(dev):
         f32 = dict(dtype=torch.float32, device=dev)
         out = out or {}

@@ -17,29 +17,33 @@ def _ptr(t):
     return ctypes.c_void_p(t.data_ptr()) if t is not None else None
 
 
-_constants = {}  # keyed by the camera matrices' storage + version: cameras are static during training
+_constants = {}  # (id(world_view_transform), id(full_proj_transform), W, H) -> (the two tensors, their versions, constants)
 
 
 def camera_constants(view):
     """The per-camera constants of depths_to_points (utils/point_utils.py:9-24), formed with the reference's own fp32
     expressions, once per camera (cached; the reference rebuilds them on the GPU every iteration):
-    ray_matrix = intrins.inverse().T @ c2w[:3,:3].T (3x3), ray_origin = c2w[:3,3], view_rotation = V[:3,:3]."""
-    wvt = view.world_view_transform
-    key = (wvt.data_ptr(), wvt._version, view.full_proj_transform.data_ptr(), int(view.image_width), int(view.image_height))
+    ray_matrix = intrins.inverse().T @ c2w[:3,:3].T (3x3), ray_origin = c2w[:3,3], view_rotation = V[:3,:3].
+
+    The cache is keyed on the IDENTITY of the two matrix tensors, and an entry keeps them alive, so neither their id()
+    nor their storage address can be handed to another camera while the entry exists (a data_ptr key could: the caching
+    allocator reuses addresses); an in-place update bumps `_version` and misses."""
+    wvt, fpt = view.world_view_transform, view.full_proj_transform
+    key = (id(wvt), id(fpt), int(view.image_width), int(view.image_height))
     cached = _constants.get(key)
-    if cached is not None:
-        return cached
+    if cached is not None and cached[0] is wvt and cached[1] is fpt and cached[2] == (wvt._version, fpt._version):
+        return cached[3]
     V = wvt.detach().float().cpu()
-    FP = view.full_proj_transform.detach().float().cpu()
+    FP = fpt.detach().float().cpu()
     W, H = int(view.image_width), int(view.image_height)
     c2w = (V.T).inverse()
     ndc2pix = torch.tensor([[W / 2, 0, 0, W / 2], [0, H / 2, 0, H / 2], [0, 0, 0, 1]]).float().T
     intrins = ((c2w.T @ FP) @ ndc2pix)[:3, :3].T
     ray_matrix = intrins.inverse().T @ c2w[:3, :3].T
     out = (tuple(ray_matrix.reshape(-1).tolist()), tuple(c2w[:3, 3].tolist()), tuple(V[:3, :3].reshape(-1).tolist()))
-    if len(_constants) >= 4096:
+    if len(_constants) >= 1024:
         _constants.clear()
-    _constants[key] = out
+    _constants[key] = (wvt, fpt, (wvt._version, fpt._version), out)
     return out
 
 

@@ -73,22 +73,33 @@ def _projection(znear, zfar, fovX, fovY):
     return P
 
 
-def make_camera(W, H, theta=0.0, focal=None, radius=4.0, fovx=None):
-    """Camera on a circle of `radius` around the scene centre looking inward; theta=0 is R=I, T=0."""
-    if fovx is None:
-        focal = 0.9 * W if focal is None else focal
-        fovx = 2.0 * math.atan(W / (2.0 * focal))
-    else:
-        focal = W / (2.0 * math.tan(fovx / 2.0))
-    fovy = 2.0 * math.atan(H / (2.0 * focal))
+def camera_pose(theta=0.0, radius=4.0):
+    """(R, T) as scene/cameras.py:Camera takes them (R: camera-to-world rotation, T: world-to-camera translation, the
+    COLMAP convention of the reference) of a camera on a circle of `radius` around the scene centre looking inward."""
     c = np.array(SCENE_CENTRE)
     C = c + radius * np.array([math.sin(theta), 0.0, -math.cos(theta)])
     z = (c - C) / np.linalg.norm(c - C)
     x = np.cross(np.array([0.0, 1.0, 0.0]), z)
     x /= np.linalg.norm(x)
     y = np.cross(z, x)
-    R = np.stack([x, y, z], axis=1)  # camera-to-world rotation (COLMAP convention of the reference)
+    R = np.stack([x, y, z], axis=1)
     t = -R.T @ C
+    return R, t
+
+
+def camera_fov(W, H, focal=None, fovx=None):
+    if fovx is None:
+        focal = 0.9 * W if focal is None else focal
+        fovx = 2.0 * math.atan(W / (2.0 * focal))
+    else:
+        focal = W / (2.0 * math.tan(fovx / 2.0))
+    return fovx, 2.0 * math.atan(H / (2.0 * focal))
+
+
+def make_camera(W, H, theta=0.0, focal=None, radius=4.0, fovx=None):
+    """Camera on a circle of `radius` around the scene centre looking inward; theta=0 is R=I, T=0."""
+    fovx, fovy = camera_fov(W, H, focal, fovx)
+    R, t = camera_pose(theta, radius)
     wvt = torch.tensor(_world2view2(R, t)).transpose(0, 1).contiguous()
     proj = _projection(0.01, 100.0, fovx, fovy).transpose(0, 1)
     full = (wvt.unsqueeze(0).bmm(proj.unsqueeze(0))).squeeze(0).contiguous()

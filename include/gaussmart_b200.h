@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 6
+#define GSM_ABI_VERSION 7
 
 #define GSM_OK 0
 #define GSM_ERR_INVALID_ARGUMENT 10001
@@ -119,12 +119,31 @@ typedef struct gsm_forward_args {
   int raw_params;                /* 1: scales = _scaling, rotations = _rotation, opacities = _opacity as STORED;
                                     exp / F.normalize / sigmoid (gaussian_model.py:104-113) are applied in-kernel,
                                     evaluated as torch's CUDA kernels evaluate them */
+  void* status;                  /* optional gsm_status handle (gsm_status_create): selects the ASYNCHRONOUS forward */
 } gsm_forward_args;
 
-/* Runs preprocess + scan, waits for R (one stream synchronisation, as rasterizer_impl.cu:282),
- * then binning, sort, ranges and compositing.  On GSM_ERR_BINNING_OVERFLOW nothing after the scan
- * has run; grow the binning workspace to *num_rendered_host and call again. */
+/* SYNCHRONOUS mode (status == NULL; what the reference does, rasterizer_impl.cu:282): runs preprocess + scan, waits
+ * for R (one stream synchronisation), then binning, sort and compositing.  On GSM_ERR_BINNING_OVERFLOW nothing
+ * after the scan has run; grow the binning workspace to *num_rendered_host and call again.
+ *
+ * ASYNCHRONOUS mode (status != NULL): the whole forward is enqueued and the call returns WITHOUT waiting for the
+ * device -- no launch shape depends on R (the scatter is P-sized, sort and compositing are tile-sized).  The binning
+ * workspace must be given (sized for binning_capacity); *num_rendered_host is set to -1.  After the scan the device
+ * writes (R, overflow, prefiltered-violation) into the status slot's pinned host record and the slot's event is
+ * recorded; gsm_status_wait / gsm_status_query read it.  If R > binning_capacity the frame is rendered EMPTY
+ * (scatter, sort, both compositing passes see no instances: background image, zero allmap, zero gradients) and
+ * `overflow` is set: the caller grows the workspace and renders the frame again. */
 int gsm_forward(const gsm_forward_args* args, void* stream);
+
+/* Status slot of an asynchronous forward: 16 bytes of pinned host memory + one cudaEvent.  A slot serves one forward
+ * at a time (create a few and recycle them).  Host-side calls; gsm_status_wait blocks the calling thread until the
+ * forward's SCAN has finished (not the whole forward) and returns R, the overflow flag and the prefiltered-violation
+ * flag ("Point is filtered although prefiltered is set", auxiliary.h:202-206); gsm_status_query returns 1 when that
+ * point has been reached, 0 when not yet, and never blocks. */
+int gsm_status_create(void** status_out);
+int gsm_status_destroy(void* status);
+int gsm_status_query(void* status);
+int gsm_status_wait(void* status, long long* num_rendered, int* overflow, int* prefiltered_violation);
 
 /* ---- backward: replaces CudaRasterizer::Rasterizer::backward (rasterizer.h:60-87,
  *      rasterizer_impl.cu:346-458) as called by RasterizeGaussiansBackwardCUDA

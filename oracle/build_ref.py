@@ -17,6 +17,11 @@ uint32_t without the header under gcc 13.
 Outputs (git-ignored, NOT gpurun-ignored):
   oracle/_ref/diff_surfel_rasterization/_C.so  + the reference's __init__.py (install copy)
   oracle/_ref/simple_knn/_C.so
+  oracle/_ref/gaussmart/...                    install copy of the reference's Python CALLERS of the hot path
+                                               (render(), GaussianModel, Camera, utils/*, arguments): what
+                                               `pip install --target` of the reference would put there.  They are the
+                                               "unchanged callers" tests/test_reference_callers_gpu.py runs against
+                                               both back ends, and the loss / render() code of the bench's reference arm.
 """
 import os, shutil, subprocess, sys, sysconfig
 from concurrent.futures import ThreadPoolExecutor
@@ -58,6 +63,24 @@ def build_one(name, srcdir, sources, extra_nvcc):
     return objs, cmds, link
 
 
+# the reference's callers of the hot path -- copied, never edited
+CALLERS = ["gaussian_renderer/__init__.py", "scene/gaussian_model.py", "scene/cameras.py", "utils/point_utils.py",
+           "utils/sh_utils.py", "utils/general_utils.py", "utils/graphics_utils.py", "utils/loss_utils.py",
+           "utils/system_utils.py", "arguments/__init__.py"]
+
+
+def install_callers():
+    """`scene/` and `utils/` are installed WITHOUT their __init__.py (namespace packages): scene/__init__.py pulls in the
+    dataset readers (PIL / plyfile / COLMAP), which are not callers of the hot path."""
+    dst_root = os.path.join(OUT, "gaussmart")
+    shutil.rmtree(dst_root, ignore_errors=True)
+    for rel in CALLERS:
+        dst = os.path.join(dst_root, rel)
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        shutil.copy(os.path.join(REF, rel), dst)
+    print("[build_ref] installed", len(CALLERS), "caller modules into", dst_root)
+
+
 def main():
     if not os.path.isdir(REF):
         print(f"[build_ref] {REF} not present; keeping whatever is prebuilt in {OUT}")
@@ -93,6 +116,7 @@ def main():
                 os.path.join(OUT, "diff_surfel_rasterization/__init__.py"))
     with open(os.path.join(OUT, "simple_knn/__init__.py"), "w") as f:
         f.write("")
+    install_callers()
     shutil.rmtree(OBJ, ignore_errors=True)
     return 0
 

@@ -9,7 +9,8 @@ import pytest
 import torch
 
 import gaussmart_b200 as gb
-from gaussmart_b200 import debug, synthetic
+from gaussmart_b200 import synthetic
+import workspace_views as debug
 from helpers import assert_grads_match_reference, grad_violations, run_cuda, variant_inputs
 import ref_loader
 

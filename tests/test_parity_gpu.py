@@ -12,7 +12,8 @@ import pytest
 import torch
 
 import gaussmart_b200 as gb
-from gaussmart_b200 import debug, synthetic
+from gaussmart_b200 import synthetic
+import workspace_views as debug
 from helpers import (ORACLE_GRAD_KEYS, assert_grads_match_reference, fwd_close, grad_violations, rel_fro,
                      robust_rel_fro, run_cuda, run_oracle, variant_inputs)
 import ref_loader
@@ -204,6 +205,32 @@ def test_non_contiguous_inputs_and_binning_growth():
     assert not scene2.means3D.is_contiguous()
     b = run_cuda(gb, scene2, cam, 0.0, None, "sh", backward=False)
     assert torch.equal(a["color"], b["color"]) and torch.equal(a["radii"], b["radii"])
+
+
+def test_non_contiguous_inputs_backward():
+    """autograd saves the tensors the caller passed: strided views of every input must give the gradients of their packed
+    copies (the reference calls .contiguous() in RasterizeGaussiansBackwardCUDA, rasterize_points.cu:112-130)."""
+    scene = synthetic.make_scene(3000, 96, 1, 8)
+    scene = scene._replace(scales=scene.scales * 2.0)
+    cam = synthetic.make_camera(96, 80, 0.0)
+    cot = synthetic.make_cotangents(96, 80, 4)
+    a = run_cuda(gb, scene, cam, 0.0, cot, "sh")
+
+    def strided(t):
+        wide = torch.zeros(t.shape[0], *[2 * d for d in t.shape[1:]])
+        idx = (slice(None),) + tuple(slice(None, None, 2) for _ in t.shape[1:])
+        wide[idx] = t
+        v = wide[idx]
+        assert not v.is_contiguous() or v.numel() == v.shape[0]
+        return v
+
+    scene2 = scene._replace(means3D=strided(scene.means3D), scales=strided(scene.scales),
+                            rotations=strided(scene.rotations), shs=strided(scene.shs))
+    b = run_cuda(gb, scene2, cam, 0.0, cot, "sh")
+    assert torch.equal(a["color"], b["color"]) and torch.equal(a["radii"], b["radii"])
+    for k in ("grad_means3D", "grad_shs", "grad_scales", "grad_rotations", "grad_opacities", "grad_means2D"):
+        viol, _ = grad_violations(b[k].cpu(), a[k].cpu(), rel=1e-4, floor=1e-6)
+        assert viol <= 1e-5 * a[k].numel() + 1, (k, viol)
 
 
 @pytest.mark.skipif(not ref_loader.available(), reason="oracle/_ref (reference CUDA build) not present")

@@ -57,6 +57,32 @@ def test_camera_constants_reproduce_the_reference_rays():
     assert camera_constants(cam) is camera_constants(cam)   # cached per camera
 
 
+def test_camera_constants_cache_cannot_serve_another_camera():
+    """the cache used to be keyed on data_ptr() / _version, which the caching allocator hands to the NEXT
+    camera (MiniCam per GUI frame) -- it is keyed on the identity of the matrix tensors now, and keeps them alive."""
+    from gaussmart_b200 import regularizer as gr
+    W, H = 33, 21
+    seen = []
+    for th in (0.1, 0.9, 1.7, 0.1):
+        cam = synthetic.make_camera(W, H, th)         # the previous camera's tensors are garbage by now
+        ray = gr.camera_constants(cam)[0]
+        dirs, _ = ro.pixel_rays(cam, "cpu")
+        M = torch.tensor(ray).view(3, 3)
+        pix = torch.tensor([[0.0, 0.0, 1.0], [W - 1.0, H - 1.0, 1.0]])
+        want = torch.stack([dirs[0], dirs[-1]])
+        assert (pix @ M - want).abs().max() <= 1e-6 * want.abs().max()
+        seen.append(ray)
+    assert seen[0] != seen[1] and seen[0] == seen[3]
+    # an in-place pose update of the SAME tensor (version bump) must miss as well
+    cam = synthetic.make_camera(W, H, 0.4)
+    a = gr.camera_constants(cam)
+    other = synthetic.make_camera(W, H, 1.1)
+    cam.world_view_transform.copy_(other.world_view_transform)
+    cam.full_proj_transform.copy_(other.full_proj_transform)
+    b = gr.camera_constants(cam)
+    assert a is not b and b[2] == gr.camera_constants(other)[2]
+
+
 def test_host_mirrors_refuse_cpu_tensors_and_unsupported_settings():
     """No CPU fallback anywhere on the widened path: the host mirrors raise before touching the library."""
     from gaussmart_b200 import loss as gl, regularizer as gr

@@ -1,9 +1,9 @@
-"""Views into the workspaces left by gsm_forward, for parity tests (sorted keys, tile ranges,
+"""Test helper (not part of the product package): views into the workspaces left by gsm_forward, for parity tests (sorted keys, tile ranges,
 final_T, n_contrib).  Layout offsets come from the library itself."""
 import torch
 
-from . import _lib
-from .rasterizer import _forward_impl
+from gaussmart_b200 import _lib
+from gaussmart_b200.rasterizer import _forward_impl
 
 
 def forward_with_intermediates(settings, means3D, opacities, shs=None, colors_precomp=None, scales=None,
@@ -20,8 +20,7 @@ def forward_with_intermediates(settings, means3D, opacities, shs=None, colors_pr
     W, H = settings.image_width, settings.image_height
     N = W * H
     Nt = ((W + 15) // 16) * ((H + 15) // 16)
-    from .rasterizer import _binning_capacity
-    cap = _binning_capacity.get((dev.index,), 0)
+    cap = binning.gsm_capacity  # the capacity the forward ran with travels with the buffer
     ko = lib.gsm_binning_sorted_keys_offset(cap)
     out = dict(num_rendered=R, color=color, allmap=others, radii=radii)
     if R > 0:

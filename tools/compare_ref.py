@@ -18,7 +18,9 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 import gaussmart_b200 as gb  # noqa: E402
-from gaussmart_b200 import synthetic, debug  # noqa: E402
+from gaussmart_b200 import synthetic  # noqa: E402
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+import workspace_views as debug  # noqa: E402
 import ref_loader  # noqa: E402
 
 

@@ -50,11 +50,15 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--views-per-step", type=int, default=None,
+                    help="views in the step's global batch (default: one per GPU = weak scaling; BASELINE.json configs[4] is "
+                         "--workload C5 --views-per-step 8: a FIXED batch of 8 views shared by the N GPUs = strong scaling)")
     ap.add_argument("--P", type=int, default=None, help="override the surfel count (debug only; flagged in config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-knn", action="store_true")
     ap.add_argument("--no-render", action="store_true", help="skip the render-FPS leg (forward only, workload size and 4K)")
+    ap.add_argument("--no-drop-in", action="store_true", help="skip the leg that runs the reference's unchanged render()")
     return ap.parse_args()
 
 
@@ -153,11 +157,13 @@ class OursArm:
     public autograd API for `e2e`."""
     name = "ours"
 
-    def __init__(self, wl, device, world):
+    def __init__(self, wl, device, world, views_per_step=None):
         import gaussmart_b200 as gb
         from gaussmart_b200 import view_parallel as vp
         from gaussmart_b200.loss import photometric_loss
         self.gb, self.vp, self.wl, self.device, self.world = gb, vp, wl, device, world
+        self.V = views_per_step or world
+        local = (self.V + world - 1) // world
         self.photometric = photometric_loss
         from gaussmart_b200.regularizer import surface_regularizer
         self.regularizer = surface_regularizer
@@ -165,23 +171,25 @@ class OursArm:
         M = wl["params"]["shs"].shape[1]
         self.bucket = vp.GradBucket(wl["P"], M, device, with_stats=True) if world == 1 else None
         # N > 1: factored exchange (all-reduce 40 B/surfel + all-gather dL/dRGB 12 B/surfel/view + local SH expand)
-        self.ex = vp.FactoredExchange(wl["P"], M, device, world, 1, with_stats=True) if world > 1 else None
+        self.ex = vp.FactoredExchange(wl["P"], M, device, world, local, with_stats=True) if world > 1 else None
         self.bg = torch.zeros(3, device=device)
         self.leaves = {k: v.clone().requires_grad_(True) for k, v in wl["params"].items()}
         self.means2D = torch.zeros_like(self.leaves["means3D"], requires_grad=True)
         self.leaves_data = {k: v.detach() for k, v in self.leaves.items()}
 
-    def value_step(self, view):
+    def value_step(self, step):
+        """One step = the fwd+bwd of the step's V views (V = one per GPU by default): views (step*V + i) mod 8."""
         wl = self.wl
         from gaussmart_b200.rasterizer import rasterize_into_bucket
+        views = [(step * self.V + i) % N_VIEWS for i in range(self.V)]
         if self.world == 1:
-            color, radii, allmap, backward = rasterize_into_bucket(wl["params"], wl["cams_d"][view], self.bucket, False,
-                                                                   bg=self.bg)
-            backward(wl["cot_d"][0], wl["cot_d"][1])
+            for j, v in enumerate(views):   # the views of the step accumulate in the bucket
+                color, radii, allmap, backward = rasterize_into_bucket(wl["params"], wl["cams_d"][v], self.bucket, j > 0,
+                                                                       bg=self.bg)
+                backward(wl["cot_d"][0], wl["cot_d"][1])
             return
-        # the step's global batch: rank r renders cams[r]; every rank knows all N cameras of the step
-        base = (view - self.rank) % N_VIEWS
-        cams = [wl["cams_d"][(base + r) % N_VIEWS] for r in range(self.world)]
+        # rank r renders views {r, r+N, ...} of the batch; every rank knows all cameras of the step
+        cams = [wl["cams_d"][v] for v in views]
         self.vp.view_parallel_step_factored(
             wl["params"], cams, self.ex, lambda v, c, a: wl["cot_d"],
             raster_fn=lambda p_, c_, b_, a_, rgb_out=None: rasterize_into_bucket(p_, c_, b_, a_, bg=self.bg, rgb_out=rgb_out,
@@ -261,14 +269,29 @@ class ReferenceArm:
     """The UNMODIFIED reference CUDA build (oracle/_ref) through its own public API and stock code path."""
     name = "reference"
 
-    def __init__(self, wl, device, world):
+    def __init__(self, wl, device, world, views_per_step=None):
         import ref_loader
+        self.V = views_per_step or 1
         self.ref = ref_loader.load_dsr()
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import loss_oracle  # the reference's own torch loss (utils/loss_utils.py restated; pinned by tests/golden/loss_ref_*)
+        import regularizer_oracle  # render()'s allmap post-processing (restated: it sits inside render()) + train.py:131-140
+        import ref_callers
+        self.modules = "restated (oracle/loss_oracle.py, oracle/regularizer_oracle.py)"
         self.photometric = loss_oracle.photometric_loss
-        import regularizer_oracle  # render()'s allmap post-processing + depth_to_normal + train.py:131-140, restated
         self.regularizer = regularizer_oracle.surface_regularizer
+        if ref_callers.available():
+            # the reference's OWN modules (install copy oracle/_ref/gaussmart/utils/{loss_utils,point_utils}.py)
+            C = ref_callers.load("reference")
+            l1_loss, ssim, d2n = C.loss_utils.l1_loss, C.loss_utils.ssim, C.point_utils.depth_to_normal
+            self.photometric = lambda x, gt, lam: (1.0 - lam) * l1_loss(x, gt) + lam * (1.0 - ssim(x, gt))   # train.py:113-114
+
+            def regularizer(allmap, view, depth_ratio, lambda_normal, lambda_dist):
+                n, d, _ = regularizer_oracle.regularizer_terms(allmap, view, depth_ratio, lambda_normal, lambda_dist, normal_fn=d2n)
+                return n + d
+            self.regularizer = regularizer
+            self.modules = ("the reference's own utils/loss_utils.py (l1_loss, ssim) and utils/point_utils.py (depth_to_normal) "
+                            "from the install copy oracle/_ref/gaussmart; render()'s 12 glue lines around them restated")
         self.wl, self.device, self.world = wl, device, 1
         self.bg = torch.zeros(3, device=device)
         self.leaves = {k: v.clone().requires_grad_(True) for k, v in wl["params"].items()}
@@ -309,9 +332,10 @@ class ReferenceArm:
         self.last_radii = radii
         return loss
 
-    def value_step(self, view):
-        color, radii, allmap = self._render(self.wl["cams_d"][view])
-        torch.autograd.backward([color, allmap], [self.wl["cot_d"][0], self.wl["cot_d"][1]])
+    def value_step(self, step):
+        for i in range(self.V):   # the reference is single-GPU: the step's V views one after the other
+            color, radii, allmap = self._render(self.wl["cams_d"][(step * self.V + i) % N_VIEWS])
+            torch.autograd.backward([color, allmap], [self.wl["cot_d"][0], self.wl["cot_d"][1]])
 
     def api_step(self, cam_d, gt, cam_h=None, gt_ready=None):
         color, radii, allmap = self._render(cam_d)
@@ -359,7 +383,32 @@ def peaks():
     except Exception:
         pass
     p["fp32_tflops"] = 148 * 128 * 2 * p["sm_max_mhz"] * 1e6 / 1e12   # SIMT FP32 FMA peak at max clock
+    p["fp32_source"] = "derived: 148 SMs x 128 FP32 lanes x 2 x sm_max_mhz (no tensor-core work on this path)"
     return p
+
+
+def measure_fp32_peak(device):
+    """MEASURED SIMT FP32 FMA rate (gsm_fp32_peak_probe: 64 resident warps per SM, 8 independent register-resident FMA
+    chains per thread), best of 5 launches of ~2 ms, CUDA events: the denominator of the compositing kernels' roofline
+    (MEASURED_PEAKS.json has HBM and tensor-core peaks only)."""
+    import ctypes
+    from gaussmart_b200 import _lib
+    lib = _lib.load()
+    sms = torch.cuda.get_device_properties(device).multi_processor_count
+    out = torch.empty(sms * 4 * 512, device=device)
+    flops = ctypes.c_double(0.0)
+    stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    best = 0.0
+    for rep in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(lib.gsm_fp32_peak_probe(20000, ctypes.c_void_p(out.data_ptr()), out.numel(), ctypes.byref(flops), stream),
+                   "fp32_peak_probe")
+        e1.record()
+        torch.cuda.synchronize()
+        if rep:
+            best = max(best, flops.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best
 
 
 def work_counts(wl, view, device):
@@ -635,6 +684,57 @@ def loss_leg(wl, photometric, reps=20):
             "loss": float(loss.detach()), "grad_checksum": float(grad.double().abs().sum())}
 
 
+def drop_in_leg(args, wl, device, view_of):
+    """What a user of the reference gets by switching the two packages and NOTHING else: the reference's UNCHANGED
+    gaussian_renderer.render() (install copy oracle/_ref/gaussmart, tests/ref_callers.py) on a GaussianModel holding the
+    workload's surfels, the reference's own L1 + SSIM (utils/loss_utils.py) and train.py:131-140's regularisers as torch
+    ops, loss.backward(), loss read-back -- with `diff_surfel_rasterization` resolving to this repo (--impl ours) or to
+    the reference build (--impl reference).  Per step the ground truth goes host -> device and the loss comes back."""
+    import ref_callers
+    if not ref_callers.available():
+        return {"unavailable": "oracle/_ref/gaussmart (install copy of the reference's callers) not present"}
+    from argparse import ArgumentParser
+    C = ref_callers.load("ours" if args.impl == "ours" else "reference")
+    prm = wl["params"]
+    gm = C.GaussianModel(wl["deg"])
+    o_ = prm["opacities"].clamp(1e-6, 1 - 1e-6)
+    mk = lambda t: torch.nn.Parameter(t.clone().contiguous().requires_grad_(True))
+    gm._xyz, gm._features_dc, gm._features_rest = mk(prm["means3D"]), mk(prm["shs"][:, :1]), mk(prm["shs"][:, 1:])
+    gm._opacity, gm._scaling, gm._rotation = mk(torch.log(o_ / (1 - o_))), mk(torch.log(prm["scales"])), mk(prm["rotations"])
+    gm.active_sh_degree = wl["deg"]
+    parser = ArgumentParser()
+    opt, pipe = C.arguments.OptimizationParams(parser), C.arguments.PipelineParams(parser)
+    W, H = wl["W"], wl["H"]
+    cams = [C.MiniCam(W, H, c.FoVy, c.FoVx, 0.01, 100.0, c.world_view_transform, c.full_proj_transform) for c in wl["cams_d"]]
+    background = torch.tensor([0, 0, 0], dtype=torch.float32, device=device)
+    gt_dev = torch.empty(3, H, W, device=device)
+    loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+    l1_loss, ssim = C.loss_utils.l1_loss, C.loss_utils.ssim
+    params = [gm._xyz, gm._features_dc, gm._features_rest, gm._opacity, gm._scaling, gm._rotation]
+
+    def step(s):
+        gt_dev.copy_(wl["gt_host"][s % 2], non_blocking=True)
+        for p_ in params:
+            p_.grad = None
+        render_pkg = C.render(cams[view_of(s)], gm, pipe, background)             # train.py:104
+        image = render_pkg["render"]
+        Ll1 = l1_loss(image, gt_dev)                                              # train.py:113-114
+        loss = (1.0 - opt.lambda_dssim) * Ll1 + opt.lambda_dssim * (1.0 - ssim(image, gt_dev))
+        rend_dist, rend_normal, surf_normal = render_pkg["rend_dist"], render_pkg["rend_normal"], render_pkg["surf_normal"]
+        normal_error = (1 - (rend_normal * surf_normal).sum(dim=0))[None]         # train.py:135-140
+        total_loss = loss + LAMBDA_DIST * (rend_dist).mean() + LAMBDA_NORMAL * (normal_error).mean()
+        total_loss.backward()                                                     # train.py:144
+        loss_host.copy_(total_loss.detach(), non_blocking=False)                  # train.py:149 (.item())
+    ms = timed_loop(step, args.steps, max(3, args.warmup), 1, 0)
+    out = {"value": 1000.0 * args.steps / ms, "unit": UNIT, "ms_per_step": ms / args.steps, "loss": float(loss_host),
+           "h2d_bytes_per_step": int(3 * H * W * 4), "d2h_bytes_per_step": 4,
+           "what": "the reference's unchanged render() + its torch L1/SSIM/regulariser loss + backward; only the two "
+                   "packages diff_surfel_rasterization / simple_knn differ between the arms"}
+    del gm, params
+    torch.cuda.empty_cache()
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 def main():
     args = parse()
@@ -669,10 +769,10 @@ def main():
                 "cpu_baseline": cb,
                 "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
             return 0
-        arm = ReferenceArm(wl, device, world)
+        arm = ReferenceArm(wl, device, world, args.views_per_step)
         ref_kind = "reference CUDA build (oracle/_ref, unmodified sources, sm_100a) on the GPU"
     else:
-        arm = OursArm(wl, device, world)
+        arm = OursArm(wl, device, world, args.views_per_step)
         from gaussmart_b200 import _lib
         _lib.stage_timing_enable(True)
         _lib.stage_timing_read(reset=True)
@@ -685,22 +785,23 @@ def main():
     # sampler runs from before the warm-up (the same load) to the end of the timed region
     sampler.start()
     time.sleep(0.3)
+    V = args.views_per_step or world           # views per step over all GPUs
     for s in range(max(args.warmup, 3)):
-        arm.value_step(view_of(s))
+        arm.value_step(s)
     barrier(world)
     if args.impl == "ours":
         _lib.stage_timing_read(reset=True)   # the stage timers cover the timed region only
-    ms_total = timed_loop(lambda s: arm.value_step(view_of(s)), args.steps, 0, world, rank)
+    ms_total = timed_loop(lambda s: arm.value_step(max(args.warmup, 3) + s), args.steps, 0, world, rank)
     clocks = sampler.stop()
     stages = _lib.stage_timing_read(reset=True) if args.impl == "ours" else {}
     if args.impl == "ours":
         _lib.stage_timing_enable(False)
     ms_per_step = ms_total / args.steps
-    value = world * 1000.0 / ms_per_step
+    value = V * 1000.0 / ms_per_step           # view-iterations per second over all GPUs
 
     # ---- e2e: public API, host buffers
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and V == world:   # (one view per GPU; the fixed-batch strong-scaling runs report `value` only)
         W, H = wl["W"], wl["H"]
         gt_dev = torch.empty(3, H, W, device=device)
         mats_host = [torch.cat([c.world_view_transform.reshape(-1), c.full_proj_transform.reshape(-1),
@@ -737,6 +838,34 @@ def main():
                "ms_per_step": ms_e2e / args.steps,
                "api": "GaussianRasterizationSettings/GaussianRasterizer + train.py's loss (L1+SSIM, normal, distortion; each "
                       "arm's own implementation: fused kernels here, the reference's torch ops there) + loss.backward()"}
+
+    value_api = None
+    if world == 1 and V == 1 and args.impl == "ours":
+        # `value` above runs the bucket path (no autograd; the path the view-parallel step uses); the reference arm's
+        # `value` goes through ITS autograd front end.  The same thing for this arm, for a like-for-like reading:
+        def autograd_step(s):
+            cam_d = wl["cams_d"][view_of(s)]
+            S = arm.gb.GaussianRasterizationSettings(**synthetic_settings(cam_d, wl["deg"], arm.bg))
+            for v_ in arm.leaves.values():
+                v_.grad = None
+            arm.means2D.grad = None
+            L = arm.leaves
+            color, radii, allmap = arm.gb.GaussianRasterizer(S)(
+                means3D=L["means3D"], means2D=arm.means2D, opacities=L["opacities"], shs=L["shs"], scales=L["scales"],
+                rotations=L["rotations"])
+            torch.autograd.backward([color, allmap], [wl["cot_d"][0], wl["cot_d"][1]])
+        from gaussmart_b200.synthetic import settings_kwargs as synthetic_settings
+        ms_api = timed_loop(autograd_step, args.steps, max(3, args.warmup), world, rank)
+        value_api = {"value": 1000.0 * args.steps / ms_api, "unit": UNIT, "ms_per_step": ms_api / args.steps,
+                     "path": "GaussianRasterizer + torch.autograd.backward with resident cotangents (what the reference "
+                             "arm's `value` times); `value` itself is rasterize_into_bucket (no autograd)"}
+
+    drop_in = None
+    if world == 1 and V == 1 and not args.no_drop_in and not args.no_e2e:
+        try:
+            drop_in = drop_in_leg(args, wl, device, view_of)
+        except Exception as ex:  # pragma: no cover
+            drop_in = {"error": repr(ex)[:300]}
 
     render = None
     if not args.no_render:
@@ -787,10 +916,12 @@ def main():
             else:
                 add_densification_stats(dens[0], dens[1], dens[2], radii, m2d.grad)
             opt.step()
+        for s_ in range(3):
+            train_step(s_)
         if args.impl == "ours":
             _lib.stage_timing_enable(True)
-            _lib.stage_timing_read(reset=True)
-        ms_train = timed_loop(train_step, args.steps, 3, world, rank)
+            _lib.stage_timing_read(reset=True)   # after the warm-up: the stage sums cover exactly the timed steps
+        ms_train = timed_loop(lambda s: train_step(3 + s), args.steps, 0, world, rank)
         train_stages = None
         if args.impl == "ours":
             train_stages = {k: v[0] / args.steps for k, v in _lib.stage_timing_read(reset=True).items() if v[1]}
@@ -811,14 +942,24 @@ def main():
         return 0
 
     pk = peaks()
+    if args.impl == "ours":
+        try:
+            pk["fp32_tflops_derived"] = pk["fp32_tflops"]
+            pk["fp32_tflops"] = measure_fp32_peak(device)
+            pk["fp32_source"] = ("measured: gsm_fp32_peak_probe (register-resident FMA chains, 64 warps/SM), best of 5; "
+                                 "derived 148 x 128 x 2 x sm_max_mhz = %.1f TFLOP/s" % pk["fp32_tflops_derived"])
+        except Exception as ex:  # pragma: no cover
+            pk["fp32_source"] += " (probe failed: %s)" % repr(ex)[:80]
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak" if args.views_per_step is None else "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {wl['P']} surfels, {wl['W']}x{wl['H']}, SH degree {wl['deg']}, "
-                               f"fwd+bwd of one view per GPU per step, {N_VIEWS} cameras cycled",
+                               + (f"fwd+bwd of one view per GPU per step, {N_VIEWS} cameras cycled" if args.views_per_step is None
+                                  else f"fwd+bwd of a fixed batch of {V} views per step shared by the GPUs, {N_VIEWS} cameras cycled"),
                    "surfels": wl["P"], "width": wl["W"], "height": wl["H"], "sh_degree": wl["deg"],
-                   "views_per_step": world, "parallelism": f"view-parallel x{world}" if world > 1 else "single GPU",
+                   "views_per_step": V, "parallelism": f"view-parallel x{world}" if world > 1 else "single GPU",
                    "l2": "inputs larger than L2 (surfel parameters %.2f GB >> 126 MB)" %
                          (wl["P"] * 58 * 4 / 1e9),
                    "exchange": ("none (single GPU)" if world == 1 else
@@ -826,6 +967,10 @@ def main():
                    "debug_P_override": args.P is not None},
         "clocks": clocks, "e2e": e2e,
     }
+    if value_api is not None:
+        line["value_public_api"] = value_api
+    if drop_in is not None:
+        line["drop_in"] = drop_in
     if render is not None:
         line["render"] = render
     if train_iter is not None:
@@ -833,6 +978,7 @@ def main():
     if args.impl == "reference":
         line["impl"] = "reference"
         line["gpu_launches"] = None
+        line["reference_modules"] = arm.modules
         line["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
                                 "sample": f"full workload, every step; {ref_kind}. The reference has no CPU "
                                           "implementation of this path, so its own implementation is timed where "
@@ -857,7 +1003,8 @@ def main():
         return 0
 
     # ---- roofline of every stage, dominant kernel first
-    wcs = [work_counts(wl, v, device) for v in sorted({view_of(s) for s in range(args.steps)})][:N_VIEWS]
+    wcs = [work_counts(wl, v, device) for v in sorted({(s * V + i * world + rank) % N_VIEWS for s in range(args.steps)
+                                                      for i in range(max(1, V // world))})][:N_VIEWS]
     wc = {k: sum(w[k] for w in wcs) / len(wcs) for k in wcs[0]}
     model = stage_model(wl, wc, wl["deg"], world)
     rows = []
@@ -875,16 +1022,17 @@ def main():
                      "share_of_step": ms / ms_total})
     rows.sort(key=lambda r: -r["ms"])
     top = dict(rows[0]) if rows else {}
-    traffic = None
+    traffic, traffic_src = None, None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(top.get("kernel"))
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj.get(top.get("kernel"))
+        traffic_src = "ncu --set full dram__bytes_read+write per launch, %s of commit %s" % (tj.get("_source", "profiles/"), tj.get("_commit", "?"))
     except Exception:
         pass
     line["roofline"] = {"kernel": top.get("kernel"), "bound": top.get("bound"), "achieved": top.get("achieved"),
                         "peak": top.get("peak"), "unit": top.get("unit"), "frac": top.get("frac"),
-                        "traffic": traffic, "ms": top.get("ms"),
-                        "peak_source": pk["source"] if top.get("bound") == "hbm" else
-                        "derived: 148 SMs x 128 FP32 lanes x 2 x sm_max_mhz (no tensor-core work on this path)"}
+                        "traffic": traffic, "traffic_source": traffic_src, "ms": top.get("ms"),
+                        "peak_source": pk["source"] if top.get("bound") == "hbm" else pk["fp32_source"]}
     line["stages"] = rows
     line["work"] = wc
     kernels_per_stage = {"preprocess_fwd": 1, "tile_scan": 1, "scatter": 1, "tile_sort": 3,

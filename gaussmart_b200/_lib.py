@@ -28,7 +28,7 @@ EXPORTS = [
     "gsm_sort_pairs32_temp_bytes", "gsm_sort_pairs32", "gsm_sh_grad_expand",
     "gsm_photometric_loss_workspace_bytes", "gsm_photometric_loss", "gsm_adam_step", "gsm_densification_stats",
     "gsm_surface_regularizer_workspace_bytes", "gsm_surface_regularizer",
-    "gsm_status_create", "gsm_status_destroy", "gsm_status_query", "gsm_status_wait",
+    "gsm_status_create", "gsm_status_destroy", "gsm_status_query", "gsm_status_wait", "gsm_fp32_peak_probe",
 ]
 
 
@@ -149,6 +149,8 @@ def load():
     lib.gsm_adam_step.argtypes = [POINTER(AdamTensor), c_int, c_void_p]
     lib.gsm_densification_stats.restype = c_int
     lib.gsm_densification_stats.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
+    lib.gsm_fp32_peak_probe.restype = c_int
+    lib.gsm_fp32_peak_probe.argtypes = [c_int, c_void_p, c_size_t, POINTER(ctypes.c_double), c_void_p]
     lib.gsm_status_create.restype = c_int
     lib.gsm_status_create.argtypes = [POINTER(c_void_p)]
     lib.gsm_status_destroy.restype = c_int

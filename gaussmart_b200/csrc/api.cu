@@ -426,6 +426,38 @@ extern "C" int gsm_sh_grad_expand(int P, int D, int M, int n_views, const float*
   return GSM_OK;
 }
 
+// ---- measured SIMT FP32 peak (bench aid): register-resident FMA chains, 64 warps per SM ------------------------
+namespace gsm {
+__global__ void __launch_bounds__(512) fp32_peak_kernel(float* __restrict__ out, int iters, float b, float c) {
+  float a[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) a[k] = (float)(threadIdx.x + k);
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) a[k] = __fmaf_rn(a[k], b, c);   // 8 independent chains per thread
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; k++) s += a[k];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+}  // namespace gsm
+
+extern "C" int gsm_fp32_peak_probe(int iters, float* out, size_t out_floats, double* flops_out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  int dev = 0, sms = 0;
+  GSM_CUDA(cudaGetDevice(&dev));
+  GSM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = sms * 4, block = 512;
+  if (iters <= 0 || out == nullptr || out_floats < (size_t)grid * block) {
+    set_error("gsm_fp32_peak_probe: needs iters > 0 and out[%d]", grid * block); return GSM_ERR_INVALID_ARGUMENT;
+  }
+  fp32_peak_kernel<<<grid, block, 0, stream>>>(out, iters, 1.0000001f, 1e-9f);
+  GSM_CUDA(cudaGetLastError());
+  if (flops_out) *flops_out = (double)grid * block * (double)iters * 8.0 * 2.0;
+  return GSM_OK;
+}
+
 extern "C" int gsm_mark_visible(int P, const float* means3D, const float* viewmatrix,
                                 const float* projmatrix, uint8_t* present, void* stream_) {
   (void)projmatrix;  // the reference's NDC test is commented out (auxiliary.h:200)

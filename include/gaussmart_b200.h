@@ -50,6 +50,11 @@ const char* gsm_stage_name(int stage);
 int gsm_stage_timing_enable(int on); /* returns the previous setting */
 int gsm_stage_timing_read(double* sum_ms /*[GSM_NUM_STAGES]*/, long long* calls /*[GSM_NUM_STAGES]*/, int reset);
 
+/* Bench aid: the SIMT FP32 FMA rate this GPU sustains (the denominator of the compositing kernels' roofline): launches
+ * 4 CTAs x 512 threads per SM, each thread running `iters` rounds of 8 independent register-resident FMAs; time it with
+ * CUDA events.  out: device scratch of >= 4 * SMs * 512 floats; *flops_out (host) receives the flops of the launch. */
+int gsm_fp32_peak_probe(int iters, float* out, size_t out_floats, double* flops_out, void* stream);
+
 /* ---- workspace sizing (host-only arithmetic, no CUDA calls) ---------------------------- */
 
 /* geometry workspace (must survive until backward): records + tile counts/offsets + scan temp.

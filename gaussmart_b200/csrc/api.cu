@@ -311,16 +311,20 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     }
     bin = aligned_base(a->binning);
     uint2* pairs = (uint2*)(bin + B.pairs);
+    // block masks ride in the top byte of the pairs' values when the surfel index fits 24 bits (debug bit 3 forces the
+    // other path, in which the sort gathers box and slabs per instance, so that tests can cover it at small P)
+    const int packed = (P <= (1 << 24) && !(a->debug & 8)) ? 1 : 0;
     {
       StageMark m(GSM_STAGE_DUPLICATE, stream);
-      launch_scatter(P, (const uint4*)(geom + G.rects), a->radii, tile_cursor, pairs, grid_x, status_dev, stream);
+      launch_scatter(P, (const uint4*)(geom + G.rects), a->radii, tile_cursor, pairs, grid_x, (const short4*)(geom + G.bbox),
+                     (const float4*)(geom + G.cull), (a->debug & 2) ? 1 : 0, packed, status_dev, stream);
     }
     GSM_STAGE("scatter");
     {
       StageMark m(GSM_STAGE_SORT, stream);
       launch_tile_sort(ranges, pairs, (uint64_t*)(bin + B.keys_sorted), (uint32_t*)(bin + B.point_list),
                        (uint8_t*)(bin + B.strip_mask), (const short4*)(geom + G.bbox), (const float4*)(geom + G.cull), grid_x, num_tiles,
-                       (a->debug & 2) ? 1 : 0, status_dev, stream);
+                       (a->debug & 2) ? 1 : 0, packed, status_dev, stream);
     }
     GSM_STAGE("tile sort");
   }

@@ -103,13 +103,61 @@ void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* 
   tile_scan_kernel<<<1, TSCAN_THREADS, 0, stream>>>(tile_count, tile_cursor, ranges, num_tiles, capacity, flags, status);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Block mask of one (surfel, tile) instance: which of the tile's 8 blocks (8x4 pixels) the surfel's conservative
+// contribution region -- box AND diagonal slabs = an octagon, common.cuh -- can reach.  Computed by the scatter, where
+// the surfel's box / slabs are loaded ONCE per surfel as a coalesced stream, and carried through the sort in the top
+// byte of the pair's value (surfel index < 2^24); round 1 gathered box and slabs per INSTANCE at the end of the sort
+// (24 B in 32-B sectors from random surfels: 2.5x the algorithmic DRAM traffic of that kernel).
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t ID_BITS = 24, ID_MASK = (1u << ID_BITS) - 1u;
+
+__device__ __forceinline__ uint32_t instance_block_mask(const short4 bx, const float4 dg, int tx, int ty) {
+  uint32_t mask = 0;
+  const int c0 = max((int)bx.x - tx, 0), c1 = min((int)bx.z - tx, TILE_X - 1);
+  const int r0 = max((int)bx.y - ty, 0), r1 = min((int)bx.w - ty, TILE_Y - 1);
+  if (c0 <= c1 && r0 <= r1) {
+    mask = block_mask(c0, c1, r0, r1);
+    // keep only the blocks that meet the surfel's diagonal slabs (cull record: bounds of x+y and x-y over
+    // its contribution region, slack included): with the box this bounds the region by an octagon
+#if GSM_BLOCK_W == 8
+    // 2 x 4 blocks of 8 x 4 pixels: block (bx, by) sits on the diagonals u = 2bx + by (x+y = s + 4u) and
+    // v = 2bx - by (x-y = d + 4v), so each slab bound is a range of u or v and the four tests
+    //   x1+y1 = s+4u+10 >= dg.x,  x0+y0 = s+4u <= dg.y,  x1-y0 = d+4v+7 >= dg.z,  x0-y1 = d+4v-3 <= dg.w
+    // become four table lookups (one byte per threshold: the blocks on the right side of it) -- no loop over blocks
+    const float s = (float)(tx + ty), d = (float)(tx - ty);
+    const int ulo = (int)fminf(fmaxf(ceilf((dg.x - 10.0f - s) * 0.25f), 0.0f), 6.0f);
+    const int uhi = (int)fminf(fmaxf(floorf((dg.y - s) * 0.25f), -1.0f), 5.0f);
+    const int vlo = (int)fminf(fmaxf(ceilf((dg.z - 7.0f - d) * 0.25f), -3.0f), 3.0f);
+    const int vhi = (int)fminf(fmaxf(floorf((dg.w + 3.0f - d) * 0.25f), -4.0f), 2.0f);
+    mask &= (uint32_t)((0x80a0e8fafeffull >> (8 * ulo)) & (0xff7f5f17050100ull >> (8 * (uhi + 1))) &
+                       (0x20a2bafbfffull >> (8 * (vlo + 3))) & (0xfffdf5d4504000ull >> (8 * (vhi + 4)))) & 0xffu;
+#else
+    uint32_t keep = 0;
+    for (uint32_t rest = mask; rest; rest &= rest - 1u) {
+      const int b = __ffs(rest) - 1;
+      const float x0 = (float)(tx + (b % BLOCKS_X) * BLOCK_W), y0 = (float)(ty + (b / BLOCKS_X) * BLOCK_H);
+      const float x1 = x0 + (float)(BLOCK_W - 1), y1 = y0 + (float)(BLOCK_H - 1);
+      if (x1 + y1 >= dg.x && x0 + y0 <= dg.y && x1 - y0 >= dg.z && x0 - y1 <= dg.w) keep |= 1u << b;
+    }
+    mask = keep;
+#endif
+  }
+  return mask;
+}
+
 // ---------------------------------------------------------------------------------------------
 // 3. scatter (the reference's duplicateWithKeys, rasterizer_impl.cu:70-111): one thread per
 //    surfel; rects of more than 16 tiles are spread over the warp.
 // ---------------------------------------------------------------------------------------------
+// PACKED: P <= 2^24, the pair's value is (block mask << 24 | surfel); otherwise the plain surfel index (the sort's
+// epilogue then gathers box and slabs itself, as in round 1).
+template <bool PACKED>
 __global__ void __launch_bounds__(256)
 scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ radii,
                uint32_t* __restrict__ tile_cursor, uint2* __restrict__ pairs, int grid_x,
+               const short4* __restrict__ bbox, const float4* __restrict__ cull, int no_cull,
                const ForwardStatus* __restrict__ status) {
   if (status->overflow) return;  // R exceeds the pair buffer: nothing may be appended
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -118,6 +166,8 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ r
   if (idx < P) r = __ldg(radii + idx);
   uint32_t depth_bits = 0;
   int minx = 0, miny = 0, w = 0, n = 0;
+  short4 bx = make_short4(0, 0, 0, 0);
+  float4 dg = make_float4(0.f, 0.f, 0.f, 0.f);
   if (r > 0) {
     // tile rect (getRect, auxiliary.h:67-77) and depth bits as left by the forward preprocess
     const uint4 q = __ldg(rects + idx);
@@ -125,24 +175,32 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ r
     w = (int)(q.y & 0xffffu) - minx;
     n = w * ((int)(q.y >> 16) - miny);
     depth_bits = q.z;
+    if (PACKED && !no_cull) { bx = __ldg(bbox + idx); dg = __ldg(cull + idx); }
   }
+  auto value_of = [&](uint32_t surfel, const short4 b, const float4 g, uint32_t tile_x, uint32_t tile_y) -> uint32_t {
+    if (!PACKED) return surfel;
+    const uint32_t m = no_cull ? 0xffu : instance_block_mask(b, g, (int)tile_x * TILE_X, (int)tile_y * TILE_Y);
+    return surfel | (m << ID_BITS);
+  };
   const int BIG = 16;
   if (n > 0 && n <= BIG) {
     // the cursor atomics return a value: four are issued before the first result is consumed, instead of one
     // L2 round trip per instance in sequence
     for (int t0 = 0; t0 < n; t0 += 4) {
-      uint32_t slot[4];
+      uint32_t slot[4], val[4];
 #pragma unroll
       for (int u = 0; u < 4; u++) {
         const int t = t0 + u;
         if (t < n) {
-          const uint32_t tile = (uint32_t)((miny + t / w) * grid_x + minx + t % w);
+          const uint32_t ty = (uint32_t)(miny + t / w), tx = (uint32_t)(minx + t % w);
+          const uint32_t tile = ty * (uint32_t)grid_x + tx;
           slot[u] = atomicAdd(tile_cursor + tile * TILE_SUBS + ((uint32_t)idx & (TILE_SUBS - 1)), 1u);
+          val[u] = value_of((uint32_t)idx, bx, dg, tx, ty);
         }
       }
 #pragma unroll
       for (int u = 0; u < 4; u++)
-        if (t0 + u < n) pairs[slot[u]] = make_uint2(depth_bits, (uint32_t)idx);
+        if (t0 + u < n) pairs[slot[u]] = make_uint2(depth_bits, val[u]);
     }
   }
   unsigned big = __ballot_sync(0xffffffffu, n > BIG);
@@ -155,18 +213,26 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ r
     const int bminy = __shfl_sync(0xffffffffu, miny, src);
     const uint32_t bdepth = __shfl_sync(0xffffffffu, depth_bits, src);
     const uint32_t bidx = (uint32_t)(idx - lane + src);
+    short4 bbx = make_short4(0, 0, 0, 0);
+    float4 bdg = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (PACKED && !no_cull) { bbx = __ldg(bbox + bidx); bdg = __ldg(cull + bidx); }   // (same address in every lane: one request)
     for (int t = lane; t < bn; t += 32) {
-      const uint32_t tile = (uint32_t)((bminy + t / bw) * grid_x + bminx + t % bw);
+      const uint32_t ty = (uint32_t)(bminy + t / bw), tx = (uint32_t)(bminx + t % bw);
+      const uint32_t tile = ty * (uint32_t)grid_x + tx;
       const uint32_t slot = atomicAdd(tile_cursor + tile * TILE_SUBS + (bidx & (TILE_SUBS - 1)), 1u);
-      pairs[slot] = make_uint2(bdepth, bidx);
+      pairs[slot] = make_uint2(bdepth, value_of(bidx, bbx, bdg, tx, ty));
     }
   }
 }
 
 void launch_scatter(int P, const uint4* rects, const int* radii, uint32_t* tile_cursor, uint2* pairs,
-                    int grid_x, const ForwardStatus* status, cudaStream_t stream) {
+                    int grid_x, const short4* bbox, const float4* cull, int no_cull, int packed,
+                    const ForwardStatus* status, cudaStream_t stream) {
   if (P <= 0) return;
-  scatter_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, rects, radii, tile_cursor, pairs, grid_x, status);
+  if (packed)
+    scatter_kernel<true><<<(P + 255) / 256, 256, 0, stream>>>(P, rects, radii, tile_cursor, pairs, grid_x, bbox, cull, no_cull, status);
+  else
+    scatter_kernel<false><<<(P + 255) / 256, 256, 0, stream>>>(P, rects, radii, tile_cursor, pairs, grid_x, bbox, cull, no_cull, status);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -194,6 +260,7 @@ struct TileSortParams {
   int no_cull;
   uint32_t n_lo, n_hi;     // this launch handles segments with n_lo < n <= n_hi
   uint32_t cap;            // pairs per shared-memory buffer (0: global-memory class)
+  int packed;              // the pairs' values carry the block mask in their top byte (scatter_kernel<true>)
   const ForwardStatus* status;
 };
 
@@ -240,7 +307,7 @@ __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* _
         const bool valid = i < wend;
         uint2 e = make_uint2(0u, 0u);
         if (valid) e = A[i];
-        const uint32_t d = valid ? ((((BY_ID ? e.y : e.x) - kmin) >> shift) & dmask) : 0u;
+        const uint32_t d = valid ? ((((BY_ID ? (e.y & ID_MASK) : e.x) - kmin) >> shift) & dmask) : 0u;
         const unsigned peers = digit_peers(d, valid, bits);
         if (valid && lane == __ffs(peers) - 1) whist[warp][d] += __popc(peers);
         ce[k] = e;
@@ -252,7 +319,7 @@ __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* _
     for (uint32_t it = wbeg; it < wend; it += 32) {
       const uint32_t i = it + lane;
       const bool valid = i < wend;
-      const uint32_t d = valid ? ((((BY_ID ? A[i].y : A[i].x) - kmin) >> shift) & dmask) : 0u;
+      const uint32_t d = valid ? ((((BY_ID ? (A[i].y & ID_MASK) : A[i].x) - kmin) >> shift) & dmask) : 0u;
       const unsigned peers = digit_peers(d, valid, bits);
       if (valid && lane == __ffs(peers) - 1) whist[warp][d] += __popc(peers);
       __syncwarp();
@@ -302,7 +369,7 @@ __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* _
         const unsigned peers = cp[k];
         const bool valid = peers != 0u;
         const uint2 e = ce[k];
-        const uint32_t d = (((BY_ID ? e.y : e.x) - kmin) >> shift) & dmask;
+        const uint32_t d = (((BY_ID ? (e.y & ID_MASK) : e.x) - kmin) >> shift) & dmask;
         const int leader = valid ? __ffs(peers) - 1 : lane;
         const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
         uint32_t old = 0;
@@ -320,7 +387,7 @@ __device__ __forceinline__ void radix_pass(const uint2* __restrict__ A, uint2* _
     const bool valid = i < wend;
     uint2 e = make_uint2(0u, 0u);
     if (valid) e = A[i];
-    const uint32_t d = valid ? ((((BY_ID ? e.y : e.x) - kmin) >> shift) & dmask) : 0u;
+    const uint32_t d = valid ? ((((BY_ID ? (e.y & ID_MASK) : e.x) - kmin) >> shift) & dmask) : 0u;
     const unsigned peers = digit_peers(d, valid, bits);
     const int leader = valid ? __ffs(peers) - 1 : lane;
     const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
@@ -384,7 +451,7 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
   for (uint32_t i = t; i + TIE_RUN < n; i += THREADS) long_run |= A[i].x == A[i + TIE_RUN].x;
   if (__syncthreads_or(long_run)) {
     uint32_t imin = 0xffffffffu, imax = 0u;
-    for (uint32_t i = t; i < n; i += THREADS) { const uint32_t k = A[i].y; imin = min(imin, k); imax = max(imax, k); }
+    for (uint32_t i = t; i < n; i += THREADS) { const uint32_t k = A[i].y & ID_MASK; imin = min(imin, k); imax = max(imax, k); }
     imin = __reduce_min_sync(0xffffffffu, imin);
     imax = __reduce_max_sync(0xffffffffu, imax);
     if (lane == 0) { warp_tot[warp] = imax; warp_min[warp] = imin; }
@@ -412,7 +479,7 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
         for (uint32_t a = i + 1; a <= j; a++) {  // insertion sort of the run's <= TIE_RUN surfel indices
           const uint32_t v = A[a].y;
           uint32_t b = a;
-          while (b > i && A[b - 1].y > v) { A[b].y = A[b - 1].y; b--; }
+          while (b > i && (A[b - 1].y & ID_MASK) > (v & ID_MASK)) { A[b].y = A[b - 1].y; b--; }
           A[b].y = v;
         }
       }
@@ -422,50 +489,19 @@ __global__ void __launch_bounds__(THREADS) tile_sort_kernel(const TileSortParams
   const int tx = (int)(tile % (uint32_t)p.grid_x) * TILE_X, ty = (int)(tile / (uint32_t)p.grid_x) * TILE_Y;
   for (uint32_t i = t; i < n; i += THREADS) {
     const uint2 e = A[i];  // (in the global class A may alias keys_sorted[range.x + i]: read before write, same thread)
-    p.point_list[range.x + i] = e.y;
+    const uint32_t surfel = p.packed ? (e.y & ID_MASK) : e.y;
+    p.point_list[range.x + i] = surfel;
     p.keys_sorted[range.x + i] = ((uint64_t)tile << 32) | e.x;
     uint32_t mask = 0xffu;
-    if (!p.no_cull) {
-      const short4 bx = __ldg(p.bbox + e.y);
-      mask = 0;
-      const int c0 = max((int)bx.x - tx, 0), c1 = min((int)bx.z - tx, TILE_X - 1);
-      const int r0 = max((int)bx.y - ty, 0), r1 = min((int)bx.w - ty, TILE_Y - 1);
-      if (c0 <= c1 && r0 <= r1) {
-        mask = block_mask(c0, c1, r0, r1);
-        // keep only the blocks that meet the surfel's diagonal slabs (cull record: bounds of x+y and x-y over
-        // its contribution region, slack included): with the box this bounds the region by an octagon
-        const float4 dg = __ldg(p.cull + e.y);
-#if GSM_BLOCK_W == 8
-        // 2 x 4 blocks of 8 x 4 pixels: block (bx, by) sits on the diagonals u = 2bx + by (x+y = s + 4u) and
-        // v = 2bx - by (x-y = d + 4v), so each slab bound is a range of u or v and the four tests
-        //   x1+y1 = s+4u+10 >= dg.x,  x0+y0 = s+4u <= dg.y,  x1-y0 = d+4v+7 >= dg.z,  x0-y1 = d+4v-3 <= dg.w
-        // become four table lookups (one byte per threshold: the blocks on the right side of it) -- no loop over blocks
-        const float s = (float)(tx + ty), d = (float)(tx - ty);
-        const int ulo = (int)fminf(fmaxf(ceilf((dg.x - 10.0f - s) * 0.25f), 0.0f), 6.0f);
-        const int uhi = (int)fminf(fmaxf(floorf((dg.y - s) * 0.25f), -1.0f), 5.0f);
-        const int vlo = (int)fminf(fmaxf(ceilf((dg.z - 7.0f - d) * 0.25f), -3.0f), 3.0f);
-        const int vhi = (int)fminf(fmaxf(floorf((dg.w + 3.0f - d) * 0.25f), -4.0f), 2.0f);
-        mask &= (uint32_t)((0x80a0e8fafeffull >> (8 * ulo)) & (0xff7f5f17050100ull >> (8 * (uhi + 1))) &
-                           (0x20a2bafbfffull >> (8 * (vlo + 3))) & (0xfffdf5d4504000ull >> (8 * (vhi + 4)))) & 0xffu;
-#else
-        uint32_t keep = 0;
-        for (uint32_t rest = mask; rest; rest &= rest - 1u) {
-          const int b = __ffs(rest) - 1;
-          const float x0 = (float)(tx + (b % BLOCKS_X) * BLOCK_W), y0 = (float)(ty + (b / BLOCKS_X) * BLOCK_H);
-          const float x1 = x0 + (float)(BLOCK_W - 1), y1 = y0 + (float)(BLOCK_H - 1);
-          if (x1 + y1 >= dg.x && x0 + y0 <= dg.y && x1 - y0 >= dg.z && x0 - y1 <= dg.w) keep |= 1u << b;
-        }
-        mask = keep;
-#endif
-      }
-    }
+    if (p.packed) mask = e.y >> ID_BITS;
+    else if (!p.no_cull) mask = instance_block_mask(__ldg(p.bbox + surfel), __ldg(p.cull + surfel), tx, ty);
     p.strip_mask[range.x + i] = (uint8_t)mask;
   }
 }
 
 void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, uint32_t* point_list,
                       uint8_t* strip_mask, const short4* bbox, const float4* cull, int grid_x, int num_tiles,
-                      int no_cull, const ForwardStatus* status, cudaStream_t stream) {
+                      int no_cull, int packed, const ForwardStatus* status, cudaStream_t stream) {
   auto small = tile_sort_kernel<TS_SMALL_THREADS, TS_SMALL_BITS, (TS_CAP_SMALL + TS_SMALL_THREADS - 1) / TS_SMALL_THREADS>;
   auto large = tile_sort_kernel<TS_LARGE_THREADS, TS_LARGE_BITS, (TS_CAP_LARGE + TS_LARGE_THREADS - 1) / TS_LARGE_THREADS>;
   constexpr size_t hist_small = (size_t)(TS_SMALL_THREADS / 32) * (1u << TS_SMALL_BITS) * 4;
@@ -477,7 +513,7 @@ void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, 
   });
   TileSortParams p{};
   p.ranges = ranges; p.pairs = pairs; p.keys_sorted = keys_sorted; p.point_list = point_list;
-  p.strip_mask = strip_mask; p.bbox = bbox; p.cull = cull; p.grid_x = grid_x; p.no_cull = no_cull; p.status = status;
+  p.strip_mask = strip_mask; p.bbox = bbox; p.cull = cull; p.grid_x = grid_x; p.no_cull = no_cull; p.packed = packed; p.status = status;
   p.n_lo = 0; p.n_hi = TS_CAP_SMALL; p.cap = TS_CAP_SMALL;
   small<<<num_tiles, TS_SMALL_THREADS, 2 * TS_CAP_SMALL * sizeof(uint2) + hist_small, stream>>>(p);
   p.n_lo = TS_CAP_SMALL; p.n_hi = TS_CAP_LARGE; p.cap = TS_CAP_LARGE;

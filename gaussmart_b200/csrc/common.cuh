@@ -229,10 +229,12 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
 void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* ranges, int num_tiles,
                       unsigned long long capacity, const uint32_t* flags, ForwardStatus* status, cudaStream_t stream);
 void launch_scatter(int P, const uint4* rects, const int* radii, uint32_t* tile_cursor, uint2* pairs,
-                    int grid_x, const ForwardStatus* status, cudaStream_t stream);
+                    int grid_x, const short4* bbox, const float4* cull, int no_cull, int packed,
+                    const ForwardStatus* status, cudaStream_t stream);
+// packed: the scatter ran with P <= 2^24 and left the block masks in the top byte of the pairs' values
 void launch_tile_sort(const uint2* ranges, uint2* pairs, uint64_t* keys_sorted, uint32_t* point_list,
                       uint8_t* strip_mask, const short4* bbox, const float4* cull, int grid_x, int num_tiles, int no_cull,
-                      const ForwardStatus* status, cudaStream_t stream);
+                      int packed, const ForwardStatus* status, cudaStream_t stream);
 
 struct FwdRenderParams {
   int W, H, grid_x, grid_y;

@@ -94,7 +94,9 @@ typedef struct gsm_forward_args {
                         (every (pixel, list entry) pair is evaluated, as the reference does);
                         bit 2: inference render (render.py, torch.no_grad): no backward will follow, so the
                         compositing kernel skips what it would hand to gsm_backward; calling gsm_backward on
-                        the buffers of such a forward is invalid (undefined gradients) */
+                        the buffers of such a forward is invalid (undefined gradients);
+                        bit 3: test aid: take the binning path of P > 2^24 surfels (block masks gathered by the tile
+                        sort instead of travelling in the top byte of the pair values) at any P */
   const float* background;       /* [3] */
   const float* means3D;          /* [P,3] */
   const float* shs;              /* [P,M,3] or NULL */

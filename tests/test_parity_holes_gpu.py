@@ -100,3 +100,28 @@ def test_small_variants_match_reference_build(name, P, W, H, deg, variant, bg, m
     # scale_modifier != 1: the reference's backward ignores it (backward.cu:487 forces 1.0) and so does ours -- the
     # gradients of a modified render are compared as well
     compare_with_reference_build(scene, cam, variant, bg, name, scale_modifier=mod)
+
+
+# ---------------------------------------------------------------------------------------------------- binning paths
+def test_binning_path_for_more_than_2_24_surfels_equals_the_packed_one():
+    """Up to 2^24 surfels the block masks travel through the tile sort in the top byte of the pair values; beyond, the
+    sort gathers each instance's box and slabs itself.  debug bit 3 selects the second path at any P: identical bits."""
+    import gaussmart_b200 as gb
+    from helpers import run_cuda, variant_inputs
+    import workspace_views
+    W, H = 200, 150
+    scene = synthetic.make_scene(40_000, W, 2, 808)
+    scene = scene._replace(scales=scene.scales * 2.5)
+    cam = synthetic.make_camera(W, H, 0.4)
+    cot = synthetic.make_cotangents(W, H, 3)
+    a = run_cuda(gb, scene, cam, 0.0, cot, "sh")
+    b = run_cuda(gb, scene, cam, 0.0, cot, "sh", debug=8)
+    assert torch.equal(a["radii"], b["radii"]) and torch.equal(a["color"], b["color"]) and torch.equal(a["allmap"], b["allmap"])
+    kw = {k: v.cuda() for k, v in variant_inputs(scene, cam, "sh").items()}
+    ia = workspace_views.forward_with_intermediates(a["settings"], scene.means3D.cuda(), scene.opacities.cuda(), **kw)
+    ib = workspace_views.forward_with_intermediates(b["settings"], scene.means3D.cuda(), scene.opacities.cuda(), **kw)
+    for k in ("keys", "point_list", "ranges", "n_contrib"):
+        assert torch.equal(ia[k], ib[k]), k
+    for k in ("grad_means3D", "grad_shs", "grad_scales", "grad_rotations", "grad_opacities"):
+        d = (a[k] - b[k]).abs().max().item()
+        assert d <= 1e-4 * a[k].abs().max().item() + 1e-12, (k, d)

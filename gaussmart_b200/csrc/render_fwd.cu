@@ -28,6 +28,10 @@ namespace gsm {
 // no __syncthreads anywhere: a warp with a short (heavily culled or early-terminated) list retires
 // at once and the hardware block scheduler backfills, instead of waiting at a per-batch barrier
 // for the slowest strip of the tile.
+// GSM_FWD_WALK: per-pixel walk of pre-tested candidates (see the chunk loop); 0 = one entry at a time for the whole warp
+#ifndef GSM_FWD_WALK
+#define GSM_FWD_WALK 0
+#endif
 #ifndef GSM_FWD_WARPS
 #define GSM_FWD_WARPS 4
 #endif
@@ -124,6 +128,76 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
     // the exact evaluation below (expf, the products, the two divisions: a few ulp).  Negative for o < 1/255.
     if (lane < n_cur) sm.cut[lane] = p.no_cull ? 3.0e38f : FMA(2.0f * __logf(255.0f * q2[lane].w), 1.001f, 1.0e-3f);
     __syncwarp();
+#if GSM_FWD_WALK
+    // Two phases per chunk.  (1) EVERY lane runs the cheap geometric pre-test of its pixel against every staged entry,
+    // at full lane occupancy, and keeps the entries that can reach alpha >= 1/255 as a bit set.  (2) Each lane then
+    // walks ITS OWN candidates in list order through the exact evaluation: the warp's trip count is the busiest
+    // pixel's number of candidates in the chunk (~5 of 32 entries), not the number of entries some pixel of the block
+    // passes (~17 of 32), which is what one-entry-at-a-time costs with 5-6 of 32 lanes active in the expensive part.
+    uint32_t mine = 0;
+    for (int j = 0; j < n_cur; j++) {
+      const float4 a = q0[j], b = q1[j], c = q2[j];
+      const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
+      const float lx = FMA(pyf, c.x, -b.x), ly = FMA(pyf, c.y, -b.y), lz = FMA(pyf, c.z, -b.z);
+      const float ppx = FMA(ky, lz, -MUL(kz, ly));
+      const float ppy = FMA(kz, lx, -MUL(kx, lz));
+      const float ppz = FMA(kx, ly, -MUL(ky, lx));
+      const float dx = SUB(a.w, pxf), dy = SUB(b.w, pyf);
+      const float r2 = FMA(dy, dy, MUL(dx, dx));
+      const float rho2d = ADD(r2, r2);
+      const float cut = sm.cut[j];
+      // (the same conservative pre-test as below: NaNs pass)
+      const bool fail = (ppx * ppx + ppy * ppy) > cut * (ppz * ppz) && rho2d > cut;
+      mine |= (fail ? 0u : 1u) << j;
+    }
+    if (STATS && !done) n_evaluated += (uint32_t)n_cur;
+    if (done) mine = 0u;
+    while (__any_sync(0xffffffffu, mine != 0u)) {
+      if (mine == 0u) continue;
+      const int j = __ffs(mine) - 1;
+      mine &= mine - 1u;
+      contributor = qpos[j];  // position in the tile list, 1-based (forward.cu:350)
+      const float4 a = q0[j], b = q1[j], c = q2[j];
+      const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
+      const float lx = FMA(pyf, c.x, -b.x), ly = FMA(pyf, c.y, -b.y), lz = FMA(pyf, c.z, -b.z);
+      const float ppx = FMA(ky, lz, -MUL(kz, ly));
+      const float ppy = FMA(kz, lx, -MUL(kx, lz));
+      const float ppz = FMA(kx, ly, -MUL(ky, lx));
+      const float dx = SUB(a.w, pxf), dy = SUB(b.w, pyf);
+      const float r2 = FMA(dy, dy, MUL(dx, dx));
+      const float rho2d = ADD(r2, r2);
+      if (ppz == 0.0f) continue;
+      const float sx = __fdiv_rn(ppx, ppz), sy = __fdiv_rn(ppy, ppz);
+      const float rho3d = FMA(sx, sx, MUL(sy, sy));
+      const float rho = fminf(rho3d, rho2d);
+      const float depth = ADD(c.z, FMA(c.x, sx, MUL(c.y, sy)));
+      if (depth < NEAR_N) continue;
+      const float power = MUL(rho, -0.5f);
+      if (power > 0.0f) continue;
+      const float alpha = fminf(MUL(c.w, expf(power)), ALPHA_MAX);
+      if (alpha < ALPHA_MIN) continue;
+      const float test_T = MUL(T, SUB(1.0f, alpha));
+      if (test_T < T_EPS) { done = true; mine = 0u; if (STATS) stopped = true; continue; }
+
+      const float w = MUL(T, alpha);
+      const float A = SUB(1.0f, T);
+      const float m = MUL(ADD(__fdiv_rn(-NEAR_N, depth), 1.0f), far_ratio);
+      const float mm = MUL(m, m);
+      distortion = FMA(w, FMA(-M1, ADD(m, m), FMA(A, mm, M2)), distortion);
+      D = FMA(depth, w, D);
+      M1 = FMA(m, w, M1);
+      M2 = FMA(mm, w, M2);
+      if (T > 0.5f) { median_depth = depth; median_contributor = contributor; }
+      const float4 nrm = q3[j], col = q4[j];
+      N0 = FMA(w, nrm.x, N0); N1 = FMA(w, nrm.y, N1); N2 = FMA(w, nrm.z, N2);
+      C0 = FMA(w, col.x, C0); C1 = FMA(w, col.y, C1); C2 = FMA(w, col.z, C2);
+      T = test_T;
+      last_contributor = contributor;
+      if (HANDOVER) atomicOr(&sm.hit[j], 1u << lane);
+      if (STATS) n_contributing++;
+    }
+    if (__all_sync(0xffffffffu, done)) all_done = true;
+#else
     for (int j = 0; j < n_cur; j++) {
       if (__all_sync(0xffffffffu, done)) { all_done = true; break; }
       if (done) continue;
@@ -178,6 +252,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
       if (HANDOVER) atomicOr(&sm.hit[j], 1u << lane);
       if (STATS) n_contributing++;
     }
+#endif
     // Hand the backward pass what this pass found out.  The backward's activity test of a pair is this kernel's
     // contribution test, bit for bit (pixels that stopped earlier are excluded by their last contributor), so
     //  * an entry that no pixel of this block blended is a no-op there too: this block's bit of the entry's mask

@@ -70,6 +70,7 @@ def test_lazy_policy_reports_overflow_and_renders_empty(scene_cam, restore_polic
     rasterizer.set_sync_policy("lazy")
     run_cuda(gb, scene, cam, 0.0, None, "sh", backward=False)
     key = (torch.cuda.current_device(),)
+    rasterizer._drain_pending(key[0], block=True)            # (resolving a forward raises the high-water mark again)
     rasterizer._binning_capacity[key] = 777
     o = run_cuda(gb, scene, cam, 0.25, None, "sh", backward=False)
     # the overflowed frame is the EMPTY frame (background, zero allmap), never garbage

@@ -36,7 +36,9 @@ def _point_cloud(C, P=P0, seed=4711):
     pts = sc.means3D[z > 0.5][:P].contiguous()
     g = torch.Generator().manual_seed(seed + 1)
     colors = torch.rand(pts.shape[0], 3, generator=g)
-    return C.BasicPointCloud(points=pts.numpy(), colors=colors.numpy(), normals=np.zeros((pts.shape[0], 3), np.float32))
+    # (segments: GauSSmart's per-point SAM segment ids, utils/graphics_utils.py:17-22; all zero = no mask-area augmentation)
+    return C.BasicPointCloud(points=pts.numpy(), colors=colors.numpy(), normals=np.zeros((pts.shape[0], 3), np.float32),
+                             segments=np.zeros(pts.shape[0], np.int64))
 
 
 def _cameras(C, n=N_VIEWS, seed=99):

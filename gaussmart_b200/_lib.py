@@ -17,7 +17,7 @@ GSM_ERR_BINNING_OVERFLOW = 10002
 GSM_ERR_WORKSPACE_TOO_SMALL = 10003
 GSM_SURFEL_RECORD_BYTES = 80
 GSM_GRAD_RECORD_FLOATS = 20
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 EXPORTS = [
     "gsm_last_error", "gsm_abi_version", "gsm_geometry_bytes", "gsm_image_bytes", "gsm_binning_bytes", "gsm_binning_persistent_bytes",
@@ -29,6 +29,7 @@ EXPORTS = [
     "gsm_photometric_loss_workspace_bytes", "gsm_photometric_loss", "gsm_adam_step", "gsm_densification_stats",
     "gsm_surface_regularizer_workspace_bytes", "gsm_surface_regularizer",
     "gsm_status_create", "gsm_status_destroy", "gsm_status_query", "gsm_status_wait", "gsm_fp32_peak_probe",
+    "gsm_densify_workspace_bytes", "gsm_densify_plan", "gsm_densify_apply",
 ]
 
 
@@ -37,6 +38,17 @@ class RegularizerArgs(Structure):
                 ("view_rotation", c_float * 9), ("depth_ratio", c_float), ("lambda_normal", c_float), ("lambda_dist", c_float),
                 ("grad_scale", c_float), ("loss_out", c_void_p), ("dL_dallmap", c_void_p), ("rend_normal", c_void_p),
                 ("surf_normal", c_void_p), ("surf_depth", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
+
+
+class DensifyArgs(Structure):
+    _fields_ = [("P", c_size_t), ("xyz", c_void_p), ("opacity", c_void_p), ("scaling", c_void_p), ("rotation", c_void_p),
+                ("xyz_gradient_accum", c_void_p), ("denom", c_void_p), ("grad_threshold", c_float), ("dense_limit", c_float),
+                ("min_opacity", c_float), ("world_limit", c_float), ("split_inv", c_float), ("has_size_limit", c_int),
+                ("split_count", c_int), ("totals_host", c_void_p)]
+
+
+class DensifyTensor(Structure):
+    _fields_ = [("inp", c_void_p), ("out", c_void_p), ("words", c_int), ("role", c_int)]
 
 
 class AdamTensor(Structure):
@@ -151,6 +163,13 @@ def load():
     lib.gsm_densification_stats.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
     lib.gsm_fp32_peak_probe.restype = c_int
     lib.gsm_fp32_peak_probe.argtypes = [c_int, c_void_p, c_size_t, POINTER(ctypes.c_double), c_void_p]
+    lib.gsm_densify_workspace_bytes.restype = c_size_t
+    lib.gsm_densify_workspace_bytes.argtypes = [c_size_t]
+    lib.gsm_densify_plan.restype = c_int
+    lib.gsm_densify_plan.argtypes = [POINTER(DensifyArgs), c_void_p, c_size_t, c_void_p]
+    lib.gsm_densify_apply.restype = c_int
+    lib.gsm_densify_apply.argtypes = [POINTER(DensifyArgs), c_void_p, POINTER(DensifyTensor), c_int, c_size_t, c_void_p,
+                                      c_void_p, c_void_p, c_void_p]
     lib.gsm_status_create.restype = c_int
     lib.gsm_status_create.argtypes = [POINTER(c_void_p)]
     lib.gsm_status_destroy.restype = c_int

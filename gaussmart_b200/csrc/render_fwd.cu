@@ -28,9 +28,13 @@ namespace gsm {
 // no __syncthreads anywhere: a warp with a short (heavily culled or early-terminated) list retires
 // at once and the hardware block scheduler backfills, instead of waiting at a per-batch barrier
 // for the slowest strip of the tile.
-// GSM_FWD_WALK: per-pixel walk of pre-tested candidates (see the chunk loop); 0 = one entry at a time for the whole warp
+// GSM_FWD_WALK (see the chunk loop): 2 = entry-parallel pre-test + per-pixel walk of the candidates (production);
+// 1 = pixel-parallel pre-test + per-pixel walk; 0 = one entry at a time for the whole warp (round 1).  Measured at C4
+// (5 M surfels, 1237x822), bit-identical images in all three: 1.19 ms (0), 1.00 ms (1), 0.95 ms (2); 3840x2160: 4.17 /
+// 4.24 / 4.04 ms.  GSM_FWD_MIN_CTAS = 8 caps the kernel at 64 registers: without it the build of variant 2 takes 72
+// and runs at 1.7 ms.
 #ifndef GSM_FWD_WALK
-#define GSM_FWD_WALK 0
+#define GSM_FWD_WALK 2
 #endif
 #ifndef GSM_FWD_WARPS
 #define GSM_FWD_WARPS 4
@@ -45,11 +49,15 @@ struct FwdWarpSmem {
   uint32_t queue[FWD_QUEUE];
   uint32_t hit[FWD_CHUNK];         // per staged entry: the pixels of the block that blended it
   float cut[FWD_CHUNK];            // per staged entry: upper bound of rho for alpha >= 1/255 (pre-test below)
+  uint32_t cand[FWD_CHUNK];        // GSM_FWD_WALK == 2: per staged entry, the pixels of the block that pass the pre-test
 };
 
 // HANDOVER: collect what the backward needs (per-entry pixel sets, dead block bits); false for inference renders
+#ifndef GSM_FWD_MIN_CTAS
+#define GSM_FWD_MIN_CTAS 8
+#endif
 template <bool STATS, bool HANDOVER>
-__global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRenderParams p) {
+__global__ void __launch_bounds__(FWD_WARPS * 32, GSM_FWD_MIN_CTAS) render_fwd_kernel(const FwdRenderParams p) {
   __shared__ __align__(16) FwdWarpSmem smem_all[FWD_WARPS];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   FwdWarpSmem& sm = smem_all[warp];
@@ -135,6 +143,50 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
     // pixel's number of candidates in the chunk (~5 of 32 entries), not the number of entries some pixel of the block
     // passes (~17 of 32), which is what one-entry-at-a-time costs with 5-6 of 32 lanes active in the expensive part.
     uint32_t mine = 0;
+#if GSM_FWD_WALK == 2
+    // (1) with LANE = ENTRY: lane j finds the pixels of the block that can reach alpha >= 1/255 for staged entry j:
+    // the same pre-test, with the same expressions (k = px Tw - Tu and l = py Tw - Tv by one FMA each, p = k x l), as
+    // the pixel-parallel form below -- but k is shared by the 4 pixels of a column and l by the 8 pixels of a row, the
+    // record is read once per entry instead of once per (entry, pixel), and nothing diverges: ~19 warp-instructions per
+    // entry instead of 37.  (An expansion of rho3d <= cut into a quadratic per row is cheaper still, ~7, but cancels
+    // catastrophically for needle-thin splats: it failed the needle scene of test_conservative_culling_changes_nothing.)
+    {
+      uint32_t pm = 0u;
+      if (lane < n_cur) {
+        const float4 a = q0[lane], b = q1[lane], c = q2[lane];
+        const float cut = sm.cut[lane];
+        const float bxf = pxf - (float)(lane % BLOCK_W), byf = pyf - (float)(lane / BLOCK_W);   // block origin
+        float lx[BLOCK_H], ly[BLOCK_H], lz[BLOCK_H], dyv[BLOCK_H];
+#pragma unroll
+        for (int r = 0; r < BLOCK_H; r++) {
+          const float y = byf + (float)r;
+          lx[r] = FMA(y, c.x, -b.x); ly[r] = FMA(y, c.y, -b.y); lz[r] = FMA(y, c.z, -b.z);
+          dyv[r] = SUB(b.w, y);
+        }
+#pragma unroll
+        for (int col = 0; col < BLOCK_W; col++) {
+          const float x = bxf + (float)col;
+          const float kx = FMA(x, c.x, -a.x), ky = FMA(x, c.y, -a.y), kz = FMA(x, c.z, -a.z);
+          const float dxv = SUB(a.w, x), dx2 = MUL(dxv, dxv);
+#pragma unroll
+          for (int r = 0; r < BLOCK_H; r++) {
+            const float ppx = FMA(ky, lz[r], -MUL(kz, ly[r]));
+            const float ppy = FMA(kz, lx[r], -MUL(kx, lz[r]));
+            const float ppz = FMA(kx, ly[r], -MUL(ky, lx[r]));
+            const float r2 = FMA(dyv[r], dyv[r], dx2);
+            const float rho2d = ADD(r2, r2);
+            const bool fail = (ppx * ppx + ppy * ppy) > cut * (ppz * ppz) && rho2d > cut;   // (NaNs pass)
+            pm |= (fail ? 0u : 1u) << (r * BLOCK_W + col);
+          }
+        }
+      }
+      sm.cand[lane] = pm;
+      __syncwarp();
+      // (2) transpose: every lane collects the entries ITS pixel passed
+      for (int j = 0; j < n_cur; j++) mine |= ((sm.cand[j] >> lane) & 1u) << j;
+      __syncwarp();
+    }
+#else
     for (int j = 0; j < n_cur; j++) {
       const float4 a = q0[j], b = q1[j], c = q2[j];
       const float kx = FMA(pxf, c.x, -a.x), ky = FMA(pxf, c.y, -a.y), kz = FMA(pxf, c.z, -a.z);
@@ -150,6 +202,7 @@ __global__ void __launch_bounds__(FWD_WARPS * 32) render_fwd_kernel(const FwdRen
       const bool fail = (ppx * ppx + ppy * ppy) > cut * (ppz * ppz) && rho2d > cut;
       mine |= (fail ? 0u : 1u) << j;
     }
+#endif
     if (STATS && !done) n_evaluated += (uint32_t)n_cur;
     if (done) mine = 0u;
     while (__any_sync(0xffffffffu, mine != 0u)) {

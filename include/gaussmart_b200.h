@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 7
+#define GSM_ABI_VERSION 8
 
 #define GSM_OK 0
 #define GSM_ERR_INVALID_ARGUMENT 10001
@@ -261,6 +261,55 @@ int gsm_adam_step(const gsm_adam_tensor* tensors, int n_tensors, void* stream);
  *      max_radii2D [P], xyz_gradient_accum [P,1], denom [P,1] fp32, updated in place.  16-byte aligned arrays. */
 int gsm_densification_stats(const int* radii, const float* viewspace_grad, const unsigned char* update_filter,
                             float* max_radii2D, float* xyz_gradient_accum, float* denom, size_t P, void* stream);
+
+/* ---- densify_and_prune of the training loop (last part).  Replaces GaussianModel.densify_and_prune
+ *      (scene/gaussian_model.py:535-549) with everything it calls: densify_and_clone (:519-533), densify_and_split
+ *      (:492-517), densification_postfix (:468-490), cat_tensors_to_optimizer (:446-466), prune_points /
+ *      _prune_optimizer (:413-444); called from train.py:205-208.  Two calls with one host read between them (the new
+ *      surfel count sizes the new tensors):
+ *        gsm_densify_plan   flags every surfel (clone / split / prune), scans, leaves the four totals
+ *                           (kept originals nA, kept clones nB, kept split parents nS, all split parents n_split)
+ *                           in the workspace and, if totals_host != NULL, copies them there on the stream;
+ *                           P_new = nA + nB + 2 nS; the caller draws normal_draw = N(0,1)[2 n_split, 3] (the same
+ *                           draw torch.normal(mean, std) makes at gaussian_model.py:507, so the random stream matches)
+ *        gsm_densify_apply  builds the source map and gathers EVERY tensor in one launch: rows of surfel order
+ *                           [kept originals | clones | first children | second children].
+ *      Roles: COPY for plain per-surfel rows (also int64 segments as 2 words), MOMENT for Adam's exp_avg / exp_avg_sq
+ *      (kept for originals, zero for clones and children; in == NULL means all zero), XYZ and SCALING for the two
+ *      tensors whose children rows are computed (xyz + R(q) (z * (exp(scaling), 0)); log(exp(scaling) / (0.8 N))).
+ *      All tests are evaluated as the reference's torch statements evaluate them (fp32, sigmoid / exp as torch's
+ *      kernels, Python scalars rounded to fp32).  src_map / zrow: caller-owned u32[P_new] scratch. */
+#define GSM_DENSIFY_ROLE_COPY 0
+#define GSM_DENSIFY_ROLE_MOMENT 1
+#define GSM_DENSIFY_ROLE_XYZ 2
+#define GSM_DENSIFY_ROLE_SCALING 3
+typedef struct gsm_densify_args {
+  size_t P;
+  const float* xyz;                 /* [P,3] */
+  const float* opacity;             /* [P]   raw (pre-sigmoid) */
+  const float* scaling;             /* [P,2] raw (log) */
+  const float* rotation;            /* [P,4] raw */
+  const float* xyz_gradient_accum;  /* [P] */
+  const float* denom;               /* [P] */
+  float grad_threshold;             /* max_grad */
+  float dense_limit;                /* percent_dense * extent */
+  float min_opacity;
+  float world_limit;                /* 0.1 * extent */
+  float split_inv;                  /* fp32(1) / fp32(0.8 * N) */
+  int has_size_limit;               /* max_screen_size is not None */
+  int split_count;                  /* N = 2 */
+  unsigned long long* totals_host;  /* optional HOST u64[4] */
+} gsm_densify_args;
+typedef struct gsm_densify_tensor {
+  const void* in;   /* [P, words] 4-byte words */
+  void* out;        /* [P_new, words], 16-byte aligned */
+  int words;
+  int role;
+} gsm_densify_tensor;
+size_t gsm_densify_workspace_bytes(size_t P);
+int gsm_densify_plan(const gsm_densify_args* args, void* workspace, size_t workspace_bytes, void* stream);
+int gsm_densify_apply(const gsm_densify_args* args, const void* workspace, const gsm_densify_tensor* tensors, int n_tensors,
+                      size_t P_new, uint32_t* src_map, uint32_t* zrow, const float* normal_draw, void* stream);
 
 /* ---- surface regularisers of the training iteration.  Replaces, fused, the allmap
  *      post-processing of render() (gaussian_renderer/__init__.py:117-147: world-space normal, nan_to_num'd median and

@@ -627,6 +627,68 @@ def densification_leg(wl, impl, reps=20):
             "checksum": [float(mr.double().sum()), float(acc.double().sum()), float(den.double().sum())]}
 
 
+def densify_leg(wl, impl, reps=3):
+    """densify_and_prune of the training loop (train.py:205-208; scene/gaussian_model.py:535-549) on a model of the
+    workload's size with an Adam history and densification statistics around the thresholds: the reference's own
+    GaussianModel.densify_and_prune (install copy oracle/_ref/gaussmart) for the reference arm, gaussmart_b200.densify's
+    kernels on the same GaussianModel class for ours.  One call per fresh model (the call changes the surfel count)."""
+    import ref_callers
+    if not ref_callers.available():
+        return {"unavailable": "oracle/_ref/gaussmart (install copy of the reference's callers) not present"}
+    from argparse import ArgumentParser
+    C = ref_callers.load("reference" if impl == "reference" else "ours")
+    P, extent = wl["P"], 4.4
+    names = ("_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation")
+
+    def model(seed):
+        g = torch.Generator(device="cuda").manual_seed(seed)
+        r = lambda *s_: torch.randn(*s_, device="cuda", generator=g)
+        gm = C.GaussianModel(3)
+        gm._xyz, gm._features_dc = torch.nn.Parameter(r(P, 3) * 2.0), torch.nn.Parameter(r(P, 1, 3) * 0.5)
+        gm._features_rest, gm._opacity = torch.nn.Parameter(r(P, 15, 3) * 0.05), torch.nn.Parameter(r(P, 1) * 2.5 - 1.0)
+        gm._scaling = torch.nn.Parameter(r(P, 2) * 0.9 + float(torch.log(torch.tensor(0.01 * extent))))
+        gm._rotation = torch.nn.Parameter(r(P, 4))
+        gm._segments = torch.zeros(P, dtype=torch.long, device="cuda")
+        gm.max_radii2D = torch.zeros(P, device="cuda")
+        gm.spatial_lr_scale = 1.0
+        gm.training_setup(C.arguments.OptimizationParams(ArgumentParser()))
+        for n in names:
+            p_ = getattr(gm, n)
+            p_.grad = torch.full_like(p_, 1e-3)
+        gm.optimizer.step()
+        gm.optimizer.zero_grad(set_to_none=True)
+        seen = torch.rand(P, device="cuda", generator=g) > 0.2
+        gm.denom = (seen.float() * torch.randint(1, 40, (P,), device="cuda", generator=g).float())[:, None].contiguous()
+        gm.xyz_gradient_accum = (gm.denom * torch.rand(P, 1, device="cuda", generator=g) * 4e-4).contiguous()
+        return gm
+
+    if impl == "reference":
+        run = lambda gm: gm.densify_and_prune(0.0002, 0.05, extent, 20)
+    else:
+        from gaussmart_b200.densify import densify_and_prune
+        run = lambda gm: densify_and_prune(gm, 0.0002, 0.05, extent, 20)
+    total, after, chk = 0.0, None, None
+    for rep in range(reps + 1):
+        gm = model(11)
+        torch.manual_seed(99)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        run(gm)
+        e1.record()
+        torch.cuda.synchronize()
+        if rep:   # (the first call warms the allocator)
+            total += e0.elapsed_time(e1)
+        after = gm._xyz.shape[0]
+        chk = [float(gm._scaling.detach().double().sum()), float(gm._features_rest.detach().double().abs().sum())]
+        del gm
+        torch.cuda.empty_cache()
+    moved = 4.0 * after * (58 * 3 + 2) * 2   # every surviving row read and written once: 58 params + 116 moments + segments
+    ms = total / reps
+    return {"ms": ms, "surfels_before": P, "surfels_after": after, "calls": reps, "compulsory_gbs": moved / (ms * 1e-3) / 1e9,
+            "checksum": chk}
+
+
 def regularizer_leg(arm, wl, reps=20):
     """The allmap regularisers of the iteration (render() post-processing + depth_to_normal + train.py:131-140), value +
     gradient w.r.t. allmap, on a rendered allmap of the workload: each arm's own implementation, CUDA events
@@ -999,6 +1061,10 @@ def main():
                 line["densification_stats"] = {"error": repr(ex)[:200]}
             if hasattr(arm, "regularizer"):
                 line["regularizer"] = regularizer_leg(arm, wl)
+            try:
+                line["densify_and_prune"] = densify_leg(wl, "reference")
+            except Exception as ex:  # pragma: no cover
+                line["densify_and_prune"] = {"error": repr(ex)[:200]}
         print(json.dumps(line))
         return 0
 
@@ -1044,6 +1110,10 @@ def main():
         line["adam"] = adam_leg(wl, "ours")
         line["densification_stats"] = densification_leg(wl, "ours")
         line["regularizer"] = regularizer_leg(arm, wl)
+        try:
+            line["densify_and_prune"] = densify_leg(wl, "ours")
+        except Exception as ex:  # pragma: no cover
+            line["densify_and_prune"] = {"error": repr(ex)[:200]}
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(int(wc["E_bwd"]), wl["deg"])
     print(json.dumps(line))

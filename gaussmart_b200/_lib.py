@@ -17,6 +17,7 @@ GSM_ERR_BINNING_OVERFLOW = 10002
 GSM_ERR_WORKSPACE_TOO_SMALL = 10003
 GSM_SURFEL_RECORD_BYTES = 80
 GSM_GRAD_RECORD_FLOATS = 20
+GSM_DENSIFY_ROLE_COPY, GSM_DENSIFY_ROLE_MOMENT, GSM_DENSIFY_ROLE_XYZ, GSM_DENSIFY_ROLE_SCALING = 0, 1, 2, 3
 ABI_VERSION = 8
 
 EXPORTS = [

@@ -171,7 +171,17 @@ class OursArm:
         M = wl["params"]["shs"].shape[1]
         self.bucket = vp.GradBucket(wl["P"], M, device, with_stats=True) if world == 1 else None
         # N > 1: factored exchange (all-reduce 40 B/surfel + all-gather dL/dRGB 12 B/surfel/view + local SH expand)
-        self.ex = vp.FactoredExchange(wl["P"], M, device, world, local, with_stats=True) if world > 1 else None
+        self.ex, self.peer = None, False
+        if world > 1:
+            # the fused exchange over NVLink peer memory (K6 pushes dL/dRGB into every rank's slot, one two-shot kernel
+            # reduces the rest); NCCL collectives (FactoredExchange) where symmetric memory is not available
+            if vp.peer_exchange_available():
+                try:
+                    self.ex, self.peer = vp.PeerExchange(wl["P"], M, device, None, local, with_stats=True), True
+                except Exception as ex_:  # pragma: no cover
+                    print(f"[bench] peer exchange unavailable ({ex_!r}); falling back to NCCL collectives", file=sys.stderr)
+            if self.ex is None:
+                self.ex = vp.FactoredExchange(wl["P"], M, device, world, local, with_stats=True)
         self.bg = torch.zeros(3, device=device)
         self.leaves = {k: v.clone().requires_grad_(True) for k, v in wl["params"].items()}
         self.means2D = torch.zeros_like(self.leaves["means3D"], requires_grad=True)
@@ -190,8 +200,18 @@ class OursArm:
             return
         # rank r renders views {r, r+N, ...} of the batch; every rank knows all cameras of the step
         cams = [wl["cams_d"][v] for v in views]
+        self._step(wl["params"], cams, lambda v, c, a: wl["cot_d"])
+
+    def _step(self, params, cams, cot):
+        from gaussmart_b200.rasterizer import rasterize_into_bucket
+        if self.peer:
+            self.vp.view_parallel_step_peer(
+                params, cams, self.ex, cot,
+                raster_fn=lambda p_, c_, b_, a_, rgb_peers=None: rasterize_into_bucket(p_, c_, b_, a_, bg=self.bg, rgb_peers=rgb_peers,
+                                                                                       fused_stats=True))
+            return
         self.vp.view_parallel_step_factored(
-            wl["params"], cams, self.ex, lambda v, c, a: wl["cot_d"],
+            params, cams, self.ex, cot,
             raster_fn=lambda p_, c_, b_, a_, rgb_out=None: rasterize_into_bucket(p_, c_, b_, a_, bg=self.bg, rgb_out=rgb_out,
                                                                                 fused_stats=True),
             fused_stats=True)
@@ -257,11 +277,7 @@ class OursArm:
             box["loss"] = loss.detach()
             return c.grad, a.grad
 
-        self.vp.view_parallel_step_factored(
-            self.leaves_data, cams_step, self.ex, cot,
-            raster_fn=lambda p_, c_, b_, a_, rgb_out=None: rasterize_into_bucket(p_, c_, b_, a_, bg=self.bg, rgb_out=rgb_out,
-                                                                                fused_stats=True),
-            fused_stats=True)
+        self._step(self.leaves_data, cams_step, cot)
         return box["loss"]
 
 
@@ -1025,7 +1041,10 @@ def main():
                    "l2": "inputs larger than L2 (surfel parameters %.2f GB >> 126 MB)" %
                          (wl["P"] * 58 * 4 / 1e9),
                    "exchange": ("none (single GPU)" if world == 1 else
-                                "factored: all-reduce 40 B/surfel + all-gather dL/dRGB 12 B/surfel/view + local SH expand"),
+                                ("fused over NVLink peer memory: K6 pushes dL/dRGB (12 B/surfel/view) into every rank's slot, one "
+                                 "two-shot kernel reduces 48 B/surfel + max radii, local SH expand alongside"
+                                 if getattr(arm, "peer", False) else
+                                 "factored over NCCL: all-reduce 40 B/surfel + all-gather dL/dRGB 12 B/surfel/view + local SH expand")),
                    "debug_P_override": args.P is not None},
         "clocks": clocks, "e2e": e2e,
     }

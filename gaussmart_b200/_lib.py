@@ -18,7 +18,7 @@ GSM_ERR_WORKSPACE_TOO_SMALL = 10003
 GSM_SURFEL_RECORD_BYTES = 80
 GSM_GRAD_RECORD_FLOATS = 20
 GSM_DENSIFY_ROLE_COPY, GSM_DENSIFY_ROLE_MOMENT, GSM_DENSIFY_ROLE_XYZ, GSM_DENSIFY_ROLE_SCALING = 0, 1, 2, 3
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 EXPORTS = [
     "gsm_last_error", "gsm_abi_version", "gsm_geometry_bytes", "gsm_image_bytes", "gsm_binning_bytes", "gsm_binning_persistent_bytes",
@@ -31,6 +31,7 @@ EXPORTS = [
     "gsm_surface_regularizer_workspace_bytes", "gsm_surface_regularizer",
     "gsm_status_create", "gsm_status_destroy", "gsm_status_query", "gsm_status_wait", "gsm_fp32_peak_probe",
     "gsm_densify_workspace_bytes", "gsm_densify_plan", "gsm_densify_apply",
+    "gsm_sh_grad_expand_strided", "gsm_peer_allreduce",
 ]
 
 
@@ -91,6 +92,7 @@ class BackwardArgs(Structure):
         ("dL_drgb", c_void_p),
         ("densify_grad_norm", c_void_p), ("densify_visible", c_void_p), ("max_radii", c_void_p),
         ("shs_rest", c_void_p), ("dL_dsh_rest", c_void_p), ("opacities", c_void_p), ("raw_params", c_int),
+        ("dL_drgb_peers", c_void_p * 8), ("n_rgb_peers", c_int),
     ]
 
 
@@ -164,6 +166,10 @@ def load():
     lib.gsm_densification_stats.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
     lib.gsm_fp32_peak_probe.restype = c_int
     lib.gsm_fp32_peak_probe.argtypes = [c_int, c_void_p, c_size_t, POINTER(ctypes.c_double), c_void_p]
+    lib.gsm_sh_grad_expand_strided.restype = c_int
+    lib.gsm_sh_grad_expand_strided.argtypes = [c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_void_p]
+    lib.gsm_peer_allreduce.restype = c_int
+    lib.gsm_peer_allreduce.argtypes = [POINTER(c_void_p), c_int, c_int, c_size_t, c_size_t, c_void_p]
     lib.gsm_densify_workspace_bytes.restype = c_size_t
     lib.gsm_densify_workspace_bytes.argtypes = [c_size_t]
     lib.gsm_densify_plan.restype = c_int

@@ -13,7 +13,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libgaussmart_b200.so")
 SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "sort.cu", "render_fwd.cu", "render_bwd.cu",
-           "preprocess_bwd.cu", "knn.cu", "loss.cu", "adam.cu", "regularizer.cu", "densify.cu"]
+           "preprocess_bwd.cu", "knn.cu", "loss.cu", "adam.cu", "regularizer.cu", "densify.cu", "exchange.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 

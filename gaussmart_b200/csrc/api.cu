@@ -405,10 +405,18 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   pp.dL_dmeans2D = a->dL_dmeans2D; pp.dL_dcolors = a->dL_dcolors; pp.dL_dopacity = a->dL_dopacity;
   pp.dL_dmeans3D = a->dL_dmeans3D; pp.dL_dtransMat = a->dL_dtransMat; pp.dL_dsh = a->dL_dsh;
   pp.dL_dscales = a->dL_dscales; pp.dL_drotations = a->dL_drotations; pp.dL_drgb = a->dL_drgb;
+  if (a->n_rgb_peers < 0 || a->n_rgb_peers > GSM_MAX_PEERS) { set_error("gsm_backward: n_rgb_peers out of range"); return GSM_ERR_INVALID_ARGUMENT; }
+  pp.n_rgb_peers = a->shs ? a->n_rgb_peers : 0;
+  for (int k = 0; k < pp.n_rgb_peers; k++) {
+    if (a->dL_drgb_peers[k] == nullptr || (reinterpret_cast<size_t>(a->dL_drgb_peers[k]) & 15) != 0) {
+      set_error("gsm_backward: dL_drgb_peers[%d] must be a 16-byte aligned device pointer", k); return GSM_ERR_INVALID_ARGUMENT;
+    }
+    pp.rgb_peers[k] = a->dL_drgb_peers[k];
+  }
   pp.stat_norm = a->densify_grad_norm; pp.stat_vis = a->densify_visible; pp.max_radii = a->max_radii;
   pp.shs_rest = a->shs ? a->shs_rest : nullptr; pp.dL_dsh_rest = a->dL_dsh_rest; pp.opacities = a->opacities; pp.raw = a->raw_params ? 1 : 0;
   if (pp.raw && pp.opacities == nullptr) { set_error("gsm_backward: raw_params needs the raw opacities"); return GSM_ERR_INVALID_ARGUMENT; }
-  if (pp.shs_rest != nullptr && pp.dL_dsh != nullptr && pp.dL_dsh_rest == nullptr && a->M > 1 && a->dL_drgb == nullptr) {
+  if (pp.shs_rest != nullptr && pp.dL_dsh != nullptr && pp.dL_dsh_rest == nullptr && a->M > 1 && a->dL_drgb == nullptr && a->n_rgb_peers == 0) {
     set_error("gsm_backward: shs_rest given without dL_dsh_rest"); return GSM_ERR_INVALID_ARGUMENT;
   }
   { StageMark m(GSM_STAGE_PREPROCESS_BWD, stream); launch_preprocess_bwd(pp, stream); }
@@ -416,18 +424,24 @@ extern "C" int gsm_backward(const gsm_backward_args* a, void* stream_) {
   return GSM_OK;
 }
 
-extern "C" int gsm_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,
-                                  const float* dL_drgb_all, float* dL_dsh, int accumulate, void* stream_) {
+extern "C" int gsm_sh_grad_expand_strided(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,
+                                          const float* dL_drgb_all, size_t view_stride, float* dL_dsh, int accumulate,
+                                          void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
-  if (P < 0 || n_views < 0 || D < 0 || D > 3 || M < 0 || M > 16 || (D + 1) * (D + 1) > M) {
+  if (P < 0 || n_views < 0 || D < 0 || D > 3 || M < 0 || M > 16 || (D + 1) * (D + 1) > M || view_stride < (size_t)3 * (P > 0 ? P : 0)) {
     set_error("gsm_sh_grad_expand: bad sizes P=%d D=%d M=%d n_views=%d", P, D, M, n_views);
     return GSM_ERR_INVALID_ARGUMENT;
   }
   if (P == 0) return GSM_OK;
   StageMark m(GSM_STAGE_RANGES, stream);
-  launch_sh_grad_expand(P, D, M, n_views, means3D, campos_all, dL_drgb_all, dL_dsh, accumulate, stream);
+  launch_sh_grad_expand(P, D, M, n_views, means3D, campos_all, dL_drgb_all, view_stride, dL_dsh, accumulate, stream);
   GSM_CUDA(cudaGetLastError());
   return GSM_OK;
+}
+extern "C" int gsm_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,
+                                  const float* dL_drgb_all, float* dL_dsh, int accumulate, void* stream_) {
+  return gsm_sh_grad_expand_strided(P, D, M, n_views, means3D, campos_all, dL_drgb_all, (size_t)3 * (P > 0 ? P : 0), dL_dsh,
+                                    accumulate, stream_);
 }
 
 // ---- measured SIMT FP32 peak (bench aid): register-resident FMA chains, 64 warps per SM ------------------------

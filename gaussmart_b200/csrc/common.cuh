@@ -301,6 +301,8 @@ struct BwdPreprocessParams {
   float* dL_dscales;
   float* dL_drotations;
   float* dL_drgb;  // optional [P,3]: factored mode, written INSTEAD of dL_dsh (see sh_grad_expand_kernel)
+  float* rgb_peers[GSM_MAX_PEERS];  // factored mode over NVLink: the [P,3] slot of THIS view in every rank's receive buffer
+  int n_rgb_peers;                  // (peer memory, 16-byte aligned); the rows are pushed there instead of dL_drgb
   float* stat_norm;  // optional [P]: += ||dL_dmeans2D.xy|| of visible surfels
   float* stat_vis;   // optional [P]: += 1 for visible surfels
   int* max_radii;    // optional [P]: max= radii
@@ -311,6 +313,6 @@ struct BwdPreprocessParams {
 };
 void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream);
 void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,
-                           const float* drgb_all, float* dL_dsh, int accumulate, cudaStream_t stream);
+                           const float* drgb_all, size_t view_stride, float* dL_dsh, int accumulate, cudaStream_t stream);
 
 }  // namespace gsm

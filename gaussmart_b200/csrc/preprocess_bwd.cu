@@ -221,7 +221,7 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
   float* my_row = wsm + lane * (3 * p.M + 1);
   // factored mode (view-parallel): dL_dRGB is written instead of the 3M-float dL_dsh row, which the
   // receiver rebuilds as basis(dir) (x) dL_dRGB (sh_grad_expand_kernel); the SH term of dL_dmean3D stays here
-  const bool factored = p.dL_drgb != nullptr;
+  const bool factored = p.dL_drgb != nullptr || p.n_rgb_peers > 0;
   const bool has_sh = p.shs != nullptr && (p.dL_dsh != nullptr || factored);
   // the thread's own operands are requested BEFORE the cooperative row staging, so both streams are in flight together
   float4 g0 = make_float4(0, 0, 0, 0), g1 = g0, g2 = g0, g3 = g0, g4 = g0;
@@ -407,7 +407,24 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
     dmean2D_y = a5 * depth * 0.5f * float(p.H);
   }
 
-  if (has_sh && factored) {
+  if (has_sh && factored && p.n_rgb_peers > 0) {
+    // the all-gather of the factored exchange, fused: the warp's 32 rows (384 contiguous bytes) go to EVERY rank's
+    // receive slot as 24 coalesced 128-bit stores over NVLink (the SH rows in shared memory are spent by now)
+    __syncwarp();
+    wsm[3 * lane] = drgb_masked.x; wsm[3 * lane + 1] = drgb_masked.y; wsm[3 * lane + 2] = drgb_masked.z;
+    __syncwarp();
+    if (rows == 32) {
+      if (lane < 24) {
+        const float4 v = reinterpret_cast<const float4*>(wsm)[lane];
+        for (int k = 0; k < p.n_rgb_peers; k++) reinterpret_cast<float4*>(p.rgb_peers[k] + 3 * (size_t)warp_first)[lane] = v;
+      }
+    } else {
+      for (int e = lane; e < 3 * rows; e += 32) {
+        const float v = wsm[e];
+        for (int k = 0; k < p.n_rgb_peers; k++) p.rgb_peers[k][3 * (size_t)warp_first + e] = v;
+      }
+    }
+  } else if (has_sh && factored) {
     if (valid) store3(p.dL_drgb + 3 * i, drgb_masked);  // per view: never accumulated
   } else if (has_sh) {
     __syncwarp();
@@ -465,7 +482,7 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
 // leave through shared memory as coalesced 128-bit stores (sh_rows_store).
 __global__ void __launch_bounds__(PBWD_THREADS)
 sh_grad_expand_kernel(int P, int D, int M, int n_views, const float* __restrict__ means3D,
-                      const float* __restrict__ campos_all, const float* __restrict__ drgb_all,
+                      const float* __restrict__ campos_all, const float* __restrict__ drgb_all, size_t view_stride,
                       float* __restrict__ dL_dsh, int accumulate) {
   extern __shared__ float sh_smem[];
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -484,7 +501,7 @@ sh_grad_expand_kernel(int P, int D, int M, int n_views, const float* __restrict_
   for (int k = 0; k < 48; k++) acc[k] = 0.f;
   bool any = false;
   for (int v = 0; v < n_views; v++) {
-    const float* g = drgb_all + ((size_t)v * P + i) * 3;
+    const float* g = drgb_all + (size_t)v * view_stride + i * 3;
     const f3 d = mk(__ldg(g), __ldg(g + 1), __ldg(g + 2));
     if (!valid || (d.x == 0.f && d.y == 0.f && d.z == 0.f)) continue;  // culled in this view (or no gradient)
     any = true;
@@ -515,7 +532,7 @@ sh_grad_expand_kernel(int P, int D, int M, int n_views, const float* __restrict_
 }
 
 void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,
-                           const float* drgb_all, float* dL_dsh, int accumulate, cudaStream_t stream) {
+                           const float* drgb_all, size_t view_stride, float* dL_dsh, int accumulate, cudaStream_t stream) {
   if (P <= 0 || M <= 0) return;
   const size_t smem = (size_t)(PBWD_THREADS / 32) * 32 * (3 * M + 1) * sizeof(float);
   static PerDeviceLevel configured;
@@ -523,7 +540,7 @@ void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3
     cudaFuncSetAttribute(sh_grad_expand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   });
   sh_grad_expand_kernel<<<(P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(
-      P, D, M, n_views, means3D, campos_all, drgb_all, dL_dsh, accumulate);
+      P, D, M, n_views, means3D, campos_all, drgb_all, view_stride, dL_dsh, accumulate);
 }
 
 

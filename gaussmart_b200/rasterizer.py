@@ -275,7 +275,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
 def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp, viewmatrix,
                    projmatrix, tanfovx, tanfovy, grad_out_color, grad_depth, sh, sh_degree, campos, geomBuffer,
                    num_rendered, binningBuffer, imgBuffer, debug, out=None, accumulate=False, binning_capacity=None,
-                   rgb_out=None, stats=None, sh_rest=None, raw_opacities=None):
+                   rgb_out=None, stats=None, sh_rest=None, raw_opacities=None, rgb_peers=None):
     """Equivalent of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:136-233).
 
     sh_rest / raw_opacities: the raw-parameter entry (must match the forward): with sh_rest the SH gradient comes back as
@@ -286,7 +286,9 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
     kernel writes into (or adds to, with `accumulate`) -- the view-parallel gradient bucket.
     `stats` (optional) = (grad_norm[P], visible[P], max_radii[P]): densification statistics accumulated by the kernel.
     `rgb_out` (optional, [P,3]) selects the factored SH gradient: the kernel writes dL/dRGB there and no
-    dL_dsh rows (gsm_backward_args.dL_drgb); `sh_grad_expand` rebuilds them."""
+    dL_dsh rows (gsm_backward_args.dL_drgb); `sh_grad_expand` rebuilds them.
+    `rgb_peers` (optional, list of raw device addresses, one per rank of the NVLink domain): the factored SH gradient
+    PUSHED by the kernel into every rank's receive slot over peer memory (gsm_backward_args.dL_drgb_peers)."""
     lib = _lib.load()
     if isinstance(num_rendered, PendingForward):
         num_rendered.check()   # lazy policy: the forward's status is looked at here (its scan finished long ago)
@@ -300,7 +302,7 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
     split = sh_rest is not None and sh_rest.numel() != 0
     if split:
         M = 1 + sh_rest.shape[1]
-        if rgb_out is not None:
+        if rgb_out is not None or rgb_peers:
             raise RuntimeError("split SH storage and the factored SH gradient are not combined")
     grad_out_color = _f32c("dL_dout_color", grad_out_color)
     grad_depth = _f32c("dL_dout_others", grad_depth)
@@ -336,7 +338,7 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
         if rgb_out is not None and (M == 0 or tuple(rgb_out.shape) != (P, 3) or rgb_out.dtype != torch.float32
                                     or not rgb_out.is_contiguous() or rgb_out.device != dev):
             raise RuntimeError("rgb_out must be a contiguous float32 [P,3] tensor on the surfels' device (and shs given)")
-        dL_dsh = _out("shs", (P, 1 if split else M, 3)) if (M != 0 and rgb_out is None) else None
+        dL_dsh = _out("shs", (P, 1 if split else M, 3)) if (M != 0 and rgb_out is None and not rgb_peers) else None
         dL_dsh_rest = _out("shs_rest", (P, M - 1, 3)) if split else None
         dL_dscales = _out("scales", (P, 2)) if scales.numel() != 0 else None
         dL_drotations = _out("rotations", (P, 4)) if rotations.numel() != 0 else None
@@ -361,6 +363,12 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
             a.dL_dscales, a.dL_drotations = _ptr(dL_dscales), _ptr(dL_drotations)
             a.accumulate = int(bool(accumulate))
             a.dL_drgb = _ptr(rgb_out)
+            if rgb_peers:
+                if M == 0 or len(rgb_peers) > 8:
+                    raise RuntimeError("rgb_peers needs shs and at most 8 ranks")
+                a.n_rgb_peers = len(rgb_peers)
+                for k, addr in enumerate(rgb_peers):
+                    a.dL_drgb_peers[k] = int(addr)
             if split:
                 a.shs_rest, a.dL_dsh_rest = _ptr(sh_rest), _ptr(dL_dsh_rest)
             if raw_opacities is not None:
@@ -521,27 +529,35 @@ class _RasterizeGaussians(torch.autograd.Function):
         return grads
 
 
-def sh_grad_expand(means3D, campos_all, rgb_all, dL_dsh, sh_degree, accumulate=False):
+def sh_grad_expand(means3D, campos_all, rgb_all, dL_dsh, sh_degree, accumulate=False, view_stride=None):
     """dL_dsh[P,M,3] (= or +=) sum over views v of basis(normalize(means3D - campos_all[v])) (x) rgb_all[v]
-    (gsm_sh_grad_expand): the receiving side of the factored view-parallel exchange."""
+    (gsm_sh_grad_expand): the receiving side of the factored view-parallel exchange.
+    view_stride: floats between consecutive views in `rgb_all` when it is a flat padded buffer (>= 3 P)."""
     lib = _lib.load()
     P, M = dL_dsh.shape[0], dL_dsh.shape[1]
-    n_views = rgb_all.shape[0]
+    n_views = campos_all.shape[0]
     dev = dL_dsh.device
-    for name, t, shape in (("means3D", means3D, (P, 3)), ("campos_all", campos_all, (n_views, 3)),
-                           ("rgb_all", rgb_all, (n_views, P, 3)), ("dL_dsh", dL_dsh, (P, M, 3))):
+    for name, t, shape in (("means3D", means3D, (P, 3)), ("campos_all", campos_all, (n_views, 3)), ("dL_dsh", dL_dsh, (P, M, 3))):
         _check_cuda(name, t)
         if tuple(t.shape) != shape or t.dtype != torch.float32 or not t.is_contiguous():
             raise RuntimeError(f"{name} must be contiguous float32 {shape}")
+    _check_cuda("rgb_all", rgb_all)
+    if view_stride is None:
+        view_stride = 3 * P
+        if tuple(rgb_all.shape) != (n_views, P, 3):
+            raise RuntimeError(f"rgb_all must be contiguous float32 {(n_views, P, 3)}")
+    if rgb_all.dtype != torch.float32 or not rgb_all.is_contiguous() or view_stride < 3 * P or \
+            rgb_all.numel() < (n_views - 1) * view_stride + 3 * P:
+        raise RuntimeError("rgb_all must be contiguous float32 holding n_views slots of view_stride floats")
     with torch.cuda.device(dev):
         stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-        _lib.check(lib.gsm_sh_grad_expand(P, int(sh_degree), M, n_views, _ptr(means3D), _ptr(campos_all), _ptr(rgb_all),
-                                          _ptr(dL_dsh), int(bool(accumulate)), stream), "sh_grad_expand")
+        _lib.check(lib.gsm_sh_grad_expand_strided(P, int(sh_degree), M, n_views, _ptr(means3D), _ptr(campos_all), _ptr(rgb_all),
+                                                  int(view_stride), _ptr(dL_dsh), int(bool(accumulate)), stream), "sh_grad_expand")
     return dL_dsh
 
 
 def rasterize_into_bucket(params, camera, bucket, accumulate, bg=None, scale_modifier=1.0, rgb_out=None,
-                          sh_degree=None, fused_stats=False):
+                          sh_degree=None, fused_stats=False, rgb_peers=None):
     """Forward + (deferred) backward of one view with the surfel gradients written by the backward
     preprocess kernel straight into `bucket.views` (gaussmart_b200.view_parallel.GradBucket) -- no
     autograd, no pack kernel before the collective.
@@ -572,7 +588,7 @@ def rasterize_into_bucket(params, camera, bucket, accumulate, bg=None, scale_mod
                                camera.world_view_transform.contiguous(), camera.full_proj_transform.contiguous(),
                                camera.tanfovx, camera.tanfovy, dL_dcolor, dL_dallmap, sh.contiguous(), sh_degree,
                                camera.camera_center.contiguous(), geom, R, binning, image, False,
-                               out=bucket.views, accumulate=accumulate, rgb_out=rgb_out,
+                               out=bucket.views, accumulate=accumulate, rgb_out=rgb_out, rgb_peers=rgb_peers,
                                stats=(bucket.stats[0], bucket.stats[1], bucket.max_radii) if fused_stats else None)
         return g[0]
 

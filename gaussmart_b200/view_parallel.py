@@ -261,3 +261,140 @@ def view_parallel_step_factored(params: Dict[str, torch.Tensor], cameras: Sequen
     exchange_factored(ex, group, after_gather=lambda: expand_fn(params["means3D"], ex.campos,
                                                                 ex.rgb_recv.view(-1, ex.P, 3), ex.dL_dsh, sh_degree))
     return results
+
+
+# ------------------------------------------------------------------------------------------------
+# Peer exchange: the factored exchange without NCCL launches, over NVLink peer memory
+# ------------------------------------------------------------------------------------------------
+# Round 1 ran the factored exchange as three NCCL collectives issued after the backward preprocess kernel (K6) had
+# returned: all-gather of dL_dRGB, all-reduce SUM of the other gradients + densification sums, all-reduce MAX of the
+# radii -- fully exposed, 1.6 ms of a 6.0 ms step at 8 GPUs.  Here the buffers live in SYMMETRIC memory
+# (torch.distributed._symmetric_memory: every rank's copy is mapped into every process, NVLink 5 / NVSwitch) and
+#   * K6 itself pushes its dL_dRGB rows into every rank's receive slot while it runs (gsm_backward_args.dL_drgb_peers:
+#     coalesced 128-bit peer stores) -- the all-gather costs no launch and hides inside the kernel;
+#   * the rest is ONE hand-written two-shot kernel (gsm_peer_allreduce, csrc/exchange.cu): rank r reduces shard r of all
+#     ranks' buffers (SUM for the gradient / statistics floats, MAX for the radii, in one pass) and writes it back to
+#     all ranks; it runs on a side stream next to the local SH expand;
+#   * two signal-pad barriers bracket the pair.
+def peer_exchange_available(group=None) -> bool:
+    """True when torch's symmetric memory can serve this process group (NCCL backend, CUDA, one NVLink domain)."""
+    try:
+        import torch.distributed._symmetric_memory as symm_mem  # noqa: F401
+    except Exception:
+        return False
+    return (dist.is_initialized() and dist.get_backend(group) == "nccl" and 1 < dist.get_world_size(group) <= 8
+            and os.environ.get("GSM_VP_EXCHANGE", "peer") != "nccl")
+
+
+class PeerExchange:
+    """Buffers of the peer exchange (same public fields as FactoredExchange: views, stats, max_radii, dL_dsh, campos,
+    gradients()).  Raises if symmetric memory cannot be set up: callers fall back to FactoredExchange."""
+
+    def __init__(self, P: int, M: int, device, group=None, max_local_views: int = 1, with_stats: bool = True):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        self.world_size, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.P, self.M, self.max_local_views = P, M, max_local_views
+        W, L = self.world_size, max_local_views
+        sizes = [(name, (P,) + shape, P * shape[0]) for name, shape in SMALL_SEGMENTS]
+        P_pad = (P + 31) // 32 * 32
+        self.n_sum = sum((cnt + 31) // 32 * 32 for _, _, cnt in sizes) + 2 * P_pad
+        self.n_max = P_pad
+        self.flat = symm_mem.empty(self.n_sum + self.n_max, dtype=torch.float32, device=device)
+        self.flat_hdl = symm_mem.rendezvous(self.flat, self.group)
+        self.flat.zero_()
+        self.views: Dict[str, torch.Tensor] = {}
+        off = 0
+        for name, shape, cnt in sizes:
+            self.views[name] = self.flat[off:off + cnt].view(shape)
+            off += (cnt + 31) // 32 * 32
+        self._stats_off = off
+        self.stats = self.flat[off:off + 2 * P_pad].view(2, P_pad)[:, :P] if with_stats else None
+        self.max_radii = self.flat[self.n_sum:self.n_sum + P].view(torch.int32) if with_stats else None
+        self.slot_stride = (3 * P + 31) // 32 * 32       # floats; every [P,3] slot starts 128-byte aligned
+        self.rgb_recv = symm_mem.empty(W * L * self.slot_stride, dtype=torch.float32, device=device)
+        self.rgb_hdl = symm_mem.rendezvous(self.rgb_recv, self.group)
+        self.rgb_recv.zero_()
+        self.campos = torch.zeros(W * L, 3, dtype=torch.float32, device=device)
+        self.dL_dsh = torch.zeros(P, M, 3, dtype=torch.float32, device=device)
+        self.side = torch.cuda.Stream(device=device)
+        self._flat_ptrs = [int(p) for p in self.flat_hdl.buffer_ptrs]
+        self._rgb_ptrs = [int(p) for p in self.rgb_hdl.buffer_ptrs]
+        torch.cuda.synchronize(device)
+        dist.barrier(self.group)                         # every rank's buffers are zeroed before anyone pushes
+
+    def slot_index(self, rank: int, local_view: int) -> int:
+        return rank * self.max_local_views + local_view
+
+    def rgb_peer_addresses(self, local_view: int) -> List[int]:
+        """Address of this rank's slot `local_view` in every rank's receive buffer."""
+        off = self.slot_index(self.rank, local_view) * self.slot_stride * 4
+        return [p + off for p in self._rgb_ptrs]
+
+    def wire_bytes(self) -> int:
+        return (self.n_sum + self.n_max) * 4 + self.max_local_views * self.P * 12
+
+    def gradients(self) -> Dict[str, torch.Tensor]:
+        g = dict(self.views)
+        g["shs"] = self.dL_dsh
+        return g
+
+
+def view_parallel_step_peer(params: Dict[str, torch.Tensor], cameras: Sequence, ex: PeerExchange, cotangent_fn: Callable,
+                            raster_fn: Optional[Callable] = None, expand_fn: Optional[Callable] = None,
+                            sh_degree: Optional[int] = None, barrier_timeout_ms: int = 60_000) -> List[ViewResult]:
+    """view_parallel_step_factored over peer memory.  After the call ex.gradients(), ex.stats and ex.max_radii hold, on
+    every rank, the sums (max for the radii) over ALL views of `cameras`, bitwise identical on all ranks.
+
+    raster_fn : (params, camera, ex, accumulate, rgb_peers=) -> (color, radii, allmap, backward); the backward must
+                accumulate the densification statistics itself (rasterize_into_bucket(..., fused_stats=True))."""
+    import ctypes
+    from . import _lib
+    if raster_fn is None:
+        from .rasterizer import rasterize_into_bucket
+        raster_fn = lambda p_, c_, b_, a_, rgb_peers=None: rasterize_into_bucket(p_, c_, b_, a_, rgb_peers=rgb_peers,  # noqa: E731
+                                                                                 fused_stats=True)
+    if expand_fn is None:
+        from .rasterizer import sh_grad_expand
+        expand_fn = sh_grad_expand
+    W, rank, L = ex.world_size, ex.rank, ex.max_local_views
+    n_views = len(cameras)
+    if (n_views + W - 1) // W > L:
+        raise ValueError(f"{n_views} views on {W} ranks need max_local_views >= {(n_views + W - 1) // W}")
+    mine = shard_views(n_views, rank, W)
+    results = []
+    # this rank's partial sums start from zero (K6 overwrites the gradient segments with the first view and adds the
+    # statistics); nobody else touches this buffer until the first barrier below
+    if not mine:
+        ex.flat.zero_()
+    else:
+        ex.flat[ex._stats_off:].zero_()
+    for j, v in enumerate(mine):
+        color, radii, allmap, backward = raster_fn(params, cameras[v], ex, j > 0, rgb_peers=ex.rgb_peer_addresses(j))
+        dc, da = cotangent_fn(v, color, allmap)
+        backward(dc, da)
+        results.append(ViewResult(color, radii, allmap))
+    for j in range(len(mine), L):  # unused slots of this rank contribute nothing: zeros pushed to every rank
+        for k in range(W):
+            ex.rgb_hdl.get_buffer(k, (ex.slot_stride,), torch.float32, ex.slot_index(rank, j) * ex.slot_stride).zero_()
+    slots = ex.campos.view(W, L, 3)
+    for v in range(n_views):
+        c = getattr(cameras[v], "camera_center", None)
+        if c is not None:
+            slots[v % W, v // W].copy_(c, non_blocking=True)
+    if sh_degree is None:
+        sh_degree = int(round(params["shs"].shape[1] ** 0.5)) - 1
+    dev = ex.flat.device
+    main = torch.cuda.current_stream(dev)
+    # barrier 1: every rank's K6 has finished -> all receive slots and all partial sums are complete
+    ex.flat_hdl.barrier(channel=0, timeout_ms=barrier_timeout_ms)
+    ex.side.wait_stream(main)
+    with torch.cuda.stream(ex.side):      # the local SH expand runs next to the two-shot reduction
+        expand_fn(params["means3D"], ex.campos, ex.rgb_recv, ex.dL_dsh, sh_degree, view_stride=ex.slot_stride)
+    lib = _lib.load()
+    ptrs = (ctypes.c_void_p * W)(*ex._flat_ptrs)
+    _lib.check(lib.gsm_peer_allreduce(ptrs, W, rank, ex.n_sum, ex.n_max, ctypes.c_void_p(main.cuda_stream)), "peer_allreduce")
+    main.wait_stream(ex.side)
+    # barrier 2: every shard has been written everywhere, every rank is done reading its receive slots
+    ex.flat_hdl.barrier(channel=1, timeout_ms=barrier_timeout_ms)
+    return results

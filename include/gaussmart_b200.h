@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 8
+#define GSM_ABI_VERSION 9
 
 #define GSM_OK 0
 #define GSM_ERR_INVALID_ARGUMENT 10001
@@ -35,6 +35,8 @@ extern "C" {
 /* Floats of one per-surfel gradient accumulation record written by the backward compositing
  * kernel (dTu3 dTv3 dTw3 dmean2D2 dcolor3 dnormal3 dopacity1 = 18, padded to 20). */
 #define GSM_GRAD_RECORD_FLOATS 20
+/* Ranks of one NVLink / NVSwitch domain the view-parallel exchange can address directly. */
+#define GSM_MAX_PEERS 8
 
 const char* gsm_last_error(void);
 int gsm_abi_version(void);
@@ -209,6 +211,14 @@ typedef struct gsm_backward_args {
   float* dL_dsh_rest;
   const float* opacities;
   int raw_params;
+  /* view-parallel exchange FUSED into the backward preprocess (new: the reference is single-GPU): with n_rgb_peers > 0
+     (and shs given) the kernel pushes the clamp-masked dL/dRGB row of every surfel (zeros for culled ones) straight into
+     dL_drgb_peers[k] for every rank k of the NVLink domain -- the [P,3] slot of this (rank, local view) in rank k's
+     receive buffer, peer memory mapped into this process (CUDA IPC / symmetric memory), 16-byte aligned -- as coalesced
+     128-bit stores over NVLink while the kernel runs: the all-gather of the factored exchange without a collective
+     launch.  dL_drgb is then ignored. */
+  float* dL_drgb_peers[GSM_MAX_PEERS];
+  int n_rgb_peers;
 } gsm_backward_args;
 
 size_t gsm_grad_workspace_bytes(int P);
@@ -221,6 +231,19 @@ int gsm_backward(const gsm_backward_args* args, void* stream);
 int gsm_sh_grad_expand(int P, int D, int M, int n_views, const float* means3D /*[P,3]*/,
                        const float* campos_all /*[n_views,3]*/, const float* dL_drgb_all /*[n_views,P,3]*/,
                        float* dL_dsh /*[P,M,3]*/, int accumulate, void* stream);
+/* the same with the views `view_stride` floats apart (>= 3 P; receive buffers pad every [P,3] slot to 16 bytes) */
+int gsm_sh_grad_expand_strided(int P, int D, int M, int n_views, const float* means3D, const float* campos_all,
+                               const float* dL_drgb_all, size_t view_stride, float* dL_dsh, int accumulate, void* stream);
+
+/* ---- the all-reduce of the view-parallel exchange as ONE hand-written kernel over NVLink peer memory (two-shot:
+ *      rank r sums shard r of every rank's buffer and writes the sums back to every rank).  bufs[k]: rank k's copy of
+ *      the SAME buffer (symmetric / IPC-mapped), laid out as n_sum fp32 to be SUMMED followed by n_max int32 to be
+ *      MAXED (the surfel gradients + densification sums, then max_radii); both counts multiples of 4, buffers 16-byte
+ *      aligned.  The caller brackets the call with cross-rank barriers on the stream: every rank's buffer complete before,
+ *      every shard written after.  Summation order is rank 0..n-1 on every rank: the result is bitwise identical
+ *      everywhere. */
+int gsm_peer_allreduce(void* const* bufs /*HOST array [n_ranks] of device pointers*/, int n_ranks, int rank,
+                       size_t n_sum, size_t n_max, void* stream);
 
 /* ---- photometric loss of the training iteration (the rasterizer's caller).  Replaces, fused,
  *      utils/loss_utils.py:16-17 (l1_loss) + :32-62 (ssim, _ssim: 11x11 Gaussian window, sigma 1.5, zero padding,

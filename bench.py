@@ -869,7 +869,17 @@ def main():
     barrier(world)
     if args.impl == "ours":
         _lib.stage_timing_read(reset=True)   # the stage timers cover the timed region only
+    if getattr(arm, "peer", False):
+        arm.ex.probe = []                       # per-step event pairs around the parts of the peer exchange
     ms_total = timed_loop(lambda s: arm.value_step(max(args.warmup, 3) + s), args.steps, 0, world, rank)
+    exchange_probe = None
+    if getattr(arm, "peer", False):
+        acc = {}
+        for step_marks in arm.ex.probe:
+            for name, a_, b_ in step_marks:
+                acc[name] = acc.get(name, 0.0) + a_.elapsed_time(b_)
+        exchange_probe = {k: v / max(1, len(arm.ex.probe)) for k, v in acc.items()}
+        arm.ex.probe = None
     clocks = sampler.stop()
     stages = _lib.stage_timing_read(reset=True) if args.impl == "ours" else {}
     if args.impl == "ours":
@@ -1048,6 +1058,8 @@ def main():
                    "debug_P_override": args.P is not None},
         "clocks": clocks, "e2e": e2e,
     }
+    if exchange_probe is not None:
+        line["exchange_ms_rank0"] = exchange_probe   # cudaEvent pairs on rank 0: barrier waits, two-shot all-reduce, SH expand
     if value_api is not None:
         line["value_public_api"] = value_api
     if drop_in is not None:

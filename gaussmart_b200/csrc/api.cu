@@ -28,7 +28,7 @@ int cuda_fail(cudaError_t e, const char* what) {
 // launching stream around every stage, resolved lazily when read.  Off by default.
 static const char* const kStageNames[GSM_NUM_STAGES] = {
     "preprocess_fwd", "tile_scan", "scatter", "tile_sort", "sh_grad_expand", "render_fwd",
-    "grad_zero", "render_bwd", "preprocess_bwd", "knn", "photometric_loss", "adam", "surface_regularizer"};
+    "grad_zero", "render_bwd", "preprocess_bwd", "knn", "photometric_loss", "adam", "surface_regularizer", "peer_allreduce"};
 
 struct StageTimer {
   std::mutex mu;

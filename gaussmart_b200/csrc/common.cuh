@@ -166,7 +166,7 @@ class PerDeviceLevel {
 enum {
   GSM_STAGE_PREPROCESS_FWD = 0, GSM_STAGE_SCAN, GSM_STAGE_DUPLICATE, GSM_STAGE_SORT, GSM_STAGE_RANGES,
   GSM_STAGE_RENDER_FWD, GSM_STAGE_GRAD_ZERO, GSM_STAGE_RENDER_BWD, GSM_STAGE_PREPROCESS_BWD, GSM_STAGE_KNN,
-  GSM_STAGE_LOSS, GSM_STAGE_ADAM, GSM_STAGE_REGULARIZER
+  GSM_STAGE_LOSS, GSM_STAGE_ADAM, GSM_STAGE_REGULARIZER, GSM_STAGE_PEER_ALLREDUCE
 };
 class StageMark {  // RAII: records a cudaEvent pair around a stage when timing is enabled
  public:

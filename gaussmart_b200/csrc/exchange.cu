@@ -7,6 +7,7 @@
 // three NCCL launches of round 1 (all-reduce SUM, all-reduce SUM, all-reduce MAX) are one kernel.
 // The caller brackets it with cross-rank barriers (symmetric-memory signal pads) on the stream.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace gsm {
 
@@ -18,7 +19,9 @@ __device__ __forceinline__ float4 ld_peer(const float4* a) {  // peer data is wr
   return v;
 }
 
-template <int NR>
+// SYS: system-scope relaxed loads (never served from a stale L1 line); otherwise plain loads -- safe here because every
+// byte this kernel reads was written before the barrier that precedes its launch, and L1 starts a kernel invalidated
+template <int NR, bool SYS>
 __global__ void __launch_bounds__(512) peer_allreduce_kernel(const PeerBufs bufs, int rank, size_t sum_vec, size_t max_vec) {
   // vectors of 16 bytes; [0, sum_vec) fp32 sums, [sum_vec, sum_vec + max_vec) int32 maxima
   const size_t total = sum_vec + max_vec;
@@ -27,7 +30,8 @@ __global__ void __launch_bounds__(512) peer_allreduce_kernel(const PeerBufs bufs
   for (size_t v = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < end; v += (size_t)gridDim.x * blockDim.x) {
     float4 x[NR];
 #pragma unroll
-    for (int k = 0; k < NR; k++) x[k] = ld_peer(reinterpret_cast<const float4*>(bufs.p[k]) + v);   // NR loads in flight
+    for (int k = 0; k < NR; k++)   // NR loads in flight
+      x[k] = SYS ? ld_peer(reinterpret_cast<const float4*>(bufs.p[k]) + v) : reinterpret_cast<const float4*>(bufs.p[k])[v];
     float4 r = x[0];
     if (v < sum_vec) {
 #pragma unroll
@@ -67,15 +71,17 @@ extern "C" int gsm_peer_allreduce(void* const* bufs, int n_ranks, int rank, size
   GSM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const size_t per = (sum_vec + max_vec + n_ranks - 1) / n_ranks;
   const int grid = (int)min((size_t)sms * 2, (per + 511) / 512);
+  StageMark m(GSM_STAGE_PEER_ALLREDUCE, stream);
+  static const bool sys_loads = [] { const char* e = getenv("GSM_PEER_LD"); return e != nullptr && e[0] == 's'; }();
+#define GSM_PEER_CASE(N) \
+  case N: if (sys_loads) peer_allreduce_kernel<N, true><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); \
+          else peer_allreduce_kernel<N, false><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
   switch (n_ranks) {
-    case 2: peer_allreduce_kernel<2><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
-    case 3: peer_allreduce_kernel<3><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
-    case 4: peer_allreduce_kernel<4><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
-    case 5: peer_allreduce_kernel<5><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
-    case 6: peer_allreduce_kernel<6><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
-    case 7: peer_allreduce_kernel<7><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
-    default: peer_allreduce_kernel<8><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
+    GSM_PEER_CASE(2) GSM_PEER_CASE(3) GSM_PEER_CASE(4) GSM_PEER_CASE(5) GSM_PEER_CASE(6) GSM_PEER_CASE(7)
+    default: if (sys_loads) peer_allreduce_kernel<8, true><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec);
+             else peer_allreduce_kernel<8, false><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
   }
+#undef GSM_PEER_CASE
   GSM_CUDA(cudaGetLastError());
   return GSM_OK;
 }

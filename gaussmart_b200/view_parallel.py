@@ -386,15 +386,32 @@ def view_parallel_step_peer(params: Dict[str, torch.Tensor], cameras: Sequence, 
         sh_degree = int(round(params["shs"].shape[1] ** 0.5)) - 1
     dev = ex.flat.device
     main = torch.cuda.current_stream(dev)
+    probe = getattr(ex, "probe", None)   # optional timing probe (bench / tools): list of (name, start event, end event)
+
+    def mark(stream):
+        if probe is None:
+            return None
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(stream)
+        return e
+    t0 = mark(main)
     # barrier 1: every rank's K6 has finished -> all receive slots and all partial sums are complete
     ex.flat_hdl.barrier(channel=0, timeout_ms=barrier_timeout_ms)
+    t1 = mark(main)
     ex.side.wait_stream(main)
     with torch.cuda.stream(ex.side):      # the local SH expand runs next to the two-shot reduction
         expand_fn(params["means3D"], ex.campos, ex.rgb_recv, ex.dL_dsh, sh_degree, view_stride=ex.slot_stride)
+        t_side = mark(ex.side)
     lib = _lib.load()
     ptrs = (ctypes.c_void_p * W)(*ex._flat_ptrs)
     _lib.check(lib.gsm_peer_allreduce(ptrs, W, rank, ex.n_sum, ex.n_max, ctypes.c_void_p(main.cuda_stream)), "peer_allreduce")
+    t2 = mark(main)
     main.wait_stream(ex.side)
+    t3 = mark(main)
     # barrier 2: every shard has been written everywhere, every rank is done reading its receive slots
     ex.flat_hdl.barrier(channel=1, timeout_ms=barrier_timeout_ms)
+    t4 = mark(main)
+    if probe is not None:
+        probe.append((("barrier1", t0, t1), ("allreduce", t1, t2), ("expand_end_after_barrier1", t1, t_side),
+                      ("join", t2, t3), ("barrier2", t3, t4), ("exchange_total", t0, t4)))
     return results

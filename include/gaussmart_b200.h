@@ -46,7 +46,7 @@ int gsm_abi_version(void);
  * cudaEvent pair on the launching stream.  gsm_stage_timing_read synchronises the outstanding
  * events and returns, per stage, the summed device milliseconds and the number of launches.
  * The reference has no equivalent (its only hook is debug's sync-after-stage, auxiliary.h:296-303). */
-#define GSM_NUM_STAGES 13
+#define GSM_NUM_STAGES 14
 int gsm_stage_count(void);
 const char* gsm_stage_name(int stage);
 int gsm_stage_timing_enable(int on); /* returns the previous setting */

@@ -12,6 +12,7 @@
 // order the reference's sm_100a build performs (documented in DESIGN.md, "FP association").
 // Output is one packed 80-byte record per visible surfel instead of the reference's six SoA arrays.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace gsm {
 
@@ -105,6 +106,107 @@ __device__ __forceinline__ float dot3_ref(float a0, float a1, float a2, float b0
 }
 
 constexpr int PFWD_THREADS = 128;
+#ifndef GSM_PFWD_MIN_CTAS
+#define GSM_PFWD_MIN_CTAS 8
+#endif
+
+// ---- SH rows by TMA bulk copy (M a multiple of 4: 12 M bytes is a multiple of 16) ---------------------------------------
+// Every VISIBLE lane fetches its own row with one cp.async.bulk (192 B at M = 16) that completes on the warp's mbarrier,
+// issued as soon as the cull decision is known: the copy runs under the rest of the geometry (contribution box, slabs),
+// and replaces the cooperative staging loop (per float4: one LDG.128, multiply-high row/column indexing, four STS.32 --
+// ~300 instructions per lane at M = 16) by one instruction per row.  Rows sit 208 B apart in shared memory: 16-byte
+// aligned for the copy, and conflict-free for the 128-bit reads of the evaluation (52 floats = 13 x 16 B, odd).
+constexpr int SH_BULK_STRIDE = 52;  // floats per shared-memory row in bulk mode (M <= 16)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n.reg .pred p;\nWAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}"
+      ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+// sh_to_rgb over a 16-byte aligned row read with 128-bit loads: same arithmetic, same order as sh_to_rgb above; the row
+// is fetched degree by degree (3 / 4 / 5 float4s live at a time) so that the evaluation stays inside 64 registers
+__device__ __forceinline__ float3 sh_to_rgb_row4(int D, const float4* row4, float3 dir) {
+  const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
+  float3 r;
+  const float x = dir.x, y = dir.y, z = dir.z;
+  {
+    const float4 v0 = row4[0];
+    r.x = MUL(C0, v0.x); r.y = MUL(C0, v0.y); r.z = MUL(C0, v0.z);
+    if (D > 0) {
+      const float4 v1 = row4[1], v2 = row4[2];
+      const float a[12] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w};   // floats 0..11
+      float t = MUL(y, C1);
+      r.x = FMA(-t, a[3], r.x); r.y = FMA(-t, a[4], r.y); r.z = FMA(-t, a[5], r.z);
+      t = MUL(z, C1);
+      r.x = FMA(t, a[6], r.x); r.y = FMA(t, a[7], r.y); r.z = FMA(t, a[8], r.z);
+      t = MUL(x, C1);
+      r.x = FMA(-t, a[9], r.x); r.y = FMA(-t, a[10], r.y); r.z = FMA(-t, a[11], r.z);
+    }
+  }
+  if (D > 1) {
+    const float xx = MUL(x, x), yy = MUL(y, y), zz = MUL(z, z);
+    const float xy = MUL(x, y), yz = MUL(y, z), xz = MUL(x, z);
+    const float zz2 = ADD(zz, zz);
+    const float xx_yy = SUB(xx, yy);
+    {
+      const float4 v3 = row4[3], v4 = row4[4], v5 = row4[5], v6 = row4[6];
+      const float b[16] = {v3.x, v3.y, v3.z, v3.w, v4.x, v4.y, v4.z, v4.w, v5.x, v5.y, v5.z, v5.w, v6.x, v6.y, v6.z, v6.w};  // floats 12..27
+      const float C20 = 1.0925484305920792f, C21 = -1.0925484305920792f, C22 = 0.31539156525252005f,
+                  C23 = -1.0925484305920792f, C24 = 0.5462742152960396f;
+      float t = MUL(xy, C20);
+      r.x = FMA(t, b[0], r.x); r.y = FMA(t, b[1], r.y); r.z = FMA(t, b[2], r.z);
+      t = MUL(yz, C21);
+      r.x = FMA(t, b[3], r.x); r.y = FMA(t, b[4], r.y); r.z = FMA(t, b[5], r.z);
+      t = MUL(SUB(SUB(zz2, xx), yy), C22);
+      r.x = FMA(t, b[6], r.x); r.y = FMA(t, b[7], r.y); r.z = FMA(t, b[8], r.z);
+      t = MUL(xz, C23);
+      r.x = FMA(t, b[9], r.x); r.y = FMA(t, b[10], r.y); r.z = FMA(t, b[11], r.z);
+      t = MUL(xx_yy, C24);
+      r.x = FMA(t, b[12], r.x); r.y = FMA(t, b[13], r.y); r.z = FMA(t, b[14], r.z);
+    }
+    if (D > 2) {
+      const float4 v6 = row4[6], v7 = row4[7], v8 = row4[8], v9 = row4[9], v10 = row4[10], v11 = row4[11];
+      // floats 27..47: e[i] = float 27 + i
+      const float e[21] = {v6.w, v7.x, v7.y, v7.z, v7.w, v8.x, v8.y, v8.z, v8.w, v9.x, v9.y, v9.z, v9.w,
+                           v10.x, v10.y, v10.z, v10.w, v11.x, v11.y, v11.z, v11.w};
+      const float C30 = -0.5900435899266435f, C31 = 2.890611442640554f, C32 = -0.4570457994644658f,
+                  C33 = 0.3731763325901154f, C34 = -0.4570457994644658f, C35 = 1.445305721320277f,
+                  C36 = -0.5900435899266435f;
+      const float zz4_xx_yy = SUB(FMA(zz, 4.0f, -xx), yy);
+      float t = MUL(MUL(y, C30), FMA(xx, 3.0f, -yy));
+      r.x = FMA(t, e[0], r.x); r.y = FMA(t, e[1], r.y); r.z = FMA(t, e[2], r.z);
+      t = MUL(z, MUL(xy, C31));
+      r.x = FMA(t, e[3], r.x); r.y = FMA(t, e[4], r.y); r.z = FMA(t, e[5], r.z);
+      t = MUL(MUL(y, C32), zz4_xx_yy);
+      r.x = FMA(t, e[6], r.x); r.y = FMA(t, e[7], r.y); r.z = FMA(t, e[8], r.z);
+      t = MUL(MUL(z, C33), FMA(yy, -3.0f, FMA(xx, -3.0f, zz2)));
+      r.x = FMA(t, e[9], r.x); r.y = FMA(t, e[10], r.y); r.z = FMA(t, e[11], r.z);
+      t = MUL(MUL(x, C34), zz4_xx_yy);
+      r.x = FMA(t, e[12], r.x); r.y = FMA(t, e[13], r.y); r.z = FMA(t, e[14], r.z);
+      t = MUL(MUL(z, C35), xx_yy);
+      r.x = FMA(t, e[15], r.x); r.y = FMA(t, e[16], r.y); r.z = FMA(t, e[17], r.z);
+      t = MUL(MUL(x, C36), FMA(yy, -3.0f, xx));
+      r.x = FMA(t, e[18], r.x); r.y = FMA(t, e[19], r.y); r.z = FMA(t, e[20], r.z);
+    }
+  }
+  r.x = ADD(r.x, 0.5f); r.y = ADD(r.y, 0.5f); r.z = ADD(r.z, 0.5f);
+  return r;
+}
 
 // Cooperative, coalesced load of the SH rows of the warp's visible surfels into shared memory
 // (row r at wsm[r * (3M + 1)]: odd stride, conflict-free per-lane reads).
@@ -158,13 +260,19 @@ __device__ __forceinline__ void sh_rows_load(float* wsm, const float* __restrict
 __device__ __forceinline__ double sqrt_up(double x) { return (double)__fsqrt_ru(__double2float_ru(x)); }
 
 // RAW: the raw-parameter entry (in-kernel activations and / or split SH storage); the standard entry compiles without it
-template <bool RAW>
-__global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdPreprocessParams p) {
-  extern __shared__ float sh_smem[];
+// BULK: the SH rows arrive by per-row TMA bulk copies (standard entry, M a multiple of 4; see above)
+template <bool RAW, bool BULK>
+__global__ void __launch_bounds__(PFWD_THREADS, GSM_PFWD_MIN_CTAS) preprocess_fwd_kernel(const FwdPreprocessParams p) {
+  extern __shared__ __align__(16) float sh_smem[];
   const int gidx = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int warp_first = gidx - lane;
   if (warp_first >= p.P) return;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sh_smem + (size_t)(PFWD_THREADS / 32) * 32 * SH_BULK_STRIDE) + warp;
+  if (BULK) {
+    if (lane == 0) mbar_init(bar, 1);
+    __syncwarp();
+  }
   const bool valid = gidx < p.P;
   const int idx = valid ? gidx : p.P - 1;  // out-of-range lanes shadow the last surfel and write nothing
 
@@ -277,6 +385,9 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
       for (int tx = minx; tx < maxx; tx++)
         atomicAdd(p.tile_count + (ty * p.grid_x + tx) * TILE_SUBS + (idx & (TILE_SUBS - 1)), 1u);
 
+    if (BULK)   // this surfel is visible from here on: its SH row is requested now and lands under the box math below
+      bulk_load(sh_smem + ((size_t)warp * 32 + lane) * SH_BULK_STRIDE, p.shs + (size_t)idx * p.M * 3, (uint32_t)(12 * p.M), bar);
+
     // conservative contribution box (common.cuh, CULL_RHO); fp64 so that the cancellation in
     // centre^2 - <f,T^2> cannot shrink it
     opac = opac_in;
@@ -330,7 +441,21 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
   const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
   float3 rgb = make_float3(0.f, 0.f, 0.f);
   int clamp_bits = 0;
-  if (p.colors_precomp == nullptr) {
+  if (BULK) {
+    // every lane of the warp is past its cull decision: arm the barrier with the bytes in flight, then wait for them
+    if (lane == 0) mbar_expect_tx(bar, (uint32_t)(12 * p.M) * (uint32_t)__popc(vis_mask));
+    if (visible) {
+      const float* cp = p.campos;
+      const float dx = SUB(px, cp[0]), dy = SUB(py, cp[1]), dz = SUB(pz, cp[2]);
+      const float len = __fsqrt_rn(FMA(dz, dz, FMA(dx, dx, MUL(dy, dy))));
+      const float3 dir = make_float3(__fdiv_rn(dx, len), __fdiv_rn(dy, len), __fdiv_rn(dz, len));
+      mbar_wait(bar, 0);
+      rgb = sh_to_rgb_row4(p.D, reinterpret_cast<const float4*>(sh_smem + ((size_t)warp * 32 + lane) * SH_BULK_STRIDE), dir);
+      if (rgb.x < 0.0f) { clamp_bits |= 1; rgb.x = 0.0f; }
+      if (rgb.y < 0.0f) { clamp_bits |= 2; rgb.y = 0.0f; }
+      if (rgb.z < 0.0f) { clamp_bits |= 4; rgb.z = 0.0f; }
+    }
+  } else if (p.colors_precomp == nullptr) {
     float* wsm = sh_smem + (size_t)warp * 32 * (3 * p.M + 1);
     if (vis_mask != 0) {
       const int rows = min(32, p.P - warp_first), rs = 3 * p.M + 1;
@@ -375,15 +500,21 @@ __global__ void __launch_bounds__(PFWD_THREADS) preprocess_fwd_kernel(const FwdP
 
 void launch_preprocess_fwd(const FwdPreprocessParams& p, cudaStream_t stream) {
   if (p.P <= 0) return;
-  const size_t smem = (p.colors_precomp == nullptr)
-                          ? (size_t)(PFWD_THREADS / 32) * 32 * (3 * p.M + 1) * sizeof(float) : 0;
+  const bool raw = p.raw || p.shs_rest != nullptr;
+  // per-row TMA bulk copies need 16-byte rows at 16-byte addresses: the concatenated [P,M,3] tensor with M % 4 == 0
+  const bool bulk = !raw && p.colors_precomp == nullptr && p.M > 0 && p.M <= 16 && p.M % 4 == 0 &&
+                    (reinterpret_cast<size_t>(p.shs) & 15) == 0 && getenv("GSM_NO_BULK") == nullptr;
+  const size_t smem = bulk ? (size_t)(PFWD_THREADS / 32) * 32 * SH_BULK_STRIDE * sizeof(float) + (PFWD_THREADS / 32) * 8
+                           : (p.colors_precomp == nullptr ? (size_t)(PFWD_THREADS / 32) * 32 * (3 * p.M + 1) * sizeof(float) : 0);
   static PerDeviceLevel configured;
   if (smem > 48 * 1024) configured.ensure(smem, [&] {
-    cudaFuncSetAttribute(preprocess_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaFuncSetAttribute(preprocess_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(preprocess_fwd_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(preprocess_fwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   });
-  if (p.raw || p.shs_rest != nullptr) preprocess_fwd_kernel<true><<<(p.P + PFWD_THREADS - 1) / PFWD_THREADS, PFWD_THREADS, smem, stream>>>(p);
-  else preprocess_fwd_kernel<false><<<(p.P + PFWD_THREADS - 1) / PFWD_THREADS, PFWD_THREADS, smem, stream>>>(p);
+  const int grid = (p.P + PFWD_THREADS - 1) / PFWD_THREADS;
+  if (bulk) preprocess_fwd_kernel<false, true><<<grid, PFWD_THREADS, smem, stream>>>(p);
+  else if (raw) preprocess_fwd_kernel<true, false><<<grid, PFWD_THREADS, smem, stream>>>(p);
+  else preprocess_fwd_kernel<false, false><<<grid, PFWD_THREADS, smem, stream>>>(p);
 }
 
 // markVisible (rasterizer_impl.cu:54-66): present = view_z > 0.2

@@ -116,27 +116,6 @@ constexpr int PFWD_THREADS = 128;
 // and replaces the cooperative staging loop (per float4: one LDG.128, multiply-high row/column indexing, four STS.32 --
 // ~300 instructions per lane at M = 16) by one instruction per row.  Rows sit 208 B apart in shared memory: 16-byte
 // aligned for the copy, and conflict-free for the 128-bit reads of the evaluation (52 floats = 13 x 16 B, odd).
-constexpr int SH_BULK_STRIDE = 52;  // floats per shared-memory row in bulk mode (M <= 16)
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n.reg .pred p;\nWAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}"
-      ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
 
 // sh_to_rgb over a 16-byte aligned row read with 128-bit loads: same arithmetic, same order as sh_to_rgb above; the row
 // is fetched degree by degree (3 / 4 / 5 float4s live at a time) so that the evaluation stays inside 64 registers

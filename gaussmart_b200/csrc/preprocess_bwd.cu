@@ -8,6 +8,7 @@
 // It reads the compact gradient record written by the backward compositing kernel and writes
 // EVERY public gradient row (zeros for culled surfels), so no output needs a prior memset.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace gsm {
 
@@ -480,6 +481,11 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
 // the view's camera centre, both known on every rank) and 3 floats, so ranks exchange the 3 floats
 // (12 B/surfel/view) instead of the 12M-byte row (192 B at M = 16).  One thread per surfel; the rows
 // leave through shared memory as coalesced 128-bit stores (sh_rows_store).
+// BULK (M % 4 == 0, aligned rows): every lane parks its 48 sums in its own 16-byte aligned shared-memory row with 12
+// 128-bit stores and hands the row to the copy engine (cp.async.bulk / cp.reduce.async.bulk, one instruction per row;
+// rows without a gradient are written from a shared zero row) -- instead of 48 scalar stores and a cooperative copy
+// loop with multiply-high row/column indexing (~300 instructions per lane at M = 16).
+template <bool BULK>
 __global__ void __launch_bounds__(PBWD_THREADS)
 sh_grad_expand_kernel(int P, int D, int M, int n_views, const float* __restrict__ means3D,
                       const float* __restrict__ campos_all, const float* __restrict__ drgb_all, size_t view_stride,
@@ -529,6 +535,31 @@ sh_grad_expand_kernel(int P, int D, int M, int n_views, const float* __restrict_
       }
     }
   }
+  if (BULK) {
+    float* rows_base = sh_smem + (size_t)warp * 32 * SH_BULK_STRIDE;
+    float4* row4 = reinterpret_cast<float4*>(rows_base + lane * SH_BULK_STRIDE);
+    float4* zero4 = reinterpret_cast<float4*>(sh_smem + (size_t)(PBWD_THREADS / 32) * 32 * SH_BULK_STRIDE) + warp * 12;
+    if (!accumulate && lane < 12) zero4[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int n4 = 3 * M / 4;
+    if (any) {
+#pragma unroll
+      for (int k = 0; k < 12; k++)   // (sums beyond the active degree are exact zeros: their coefficients are)
+        if (k < n4) row4[k] = make_float4(acc[4 * k], acc[4 * k + 1], acc[4 * k + 2], acc[4 * k + 3]);
+    }
+    fence_proxy_async();   // (writers fence, then the warp meets, then rows are handed over: the zero row is shared)
+    __syncwarp();
+    if (valid) {
+      float* dst = dL_dsh + i * (size_t)(3 * M);
+      if (any) {
+        if (accumulate) bulk_reduce_add_f32(dst, row4, (uint32_t)(12 * M));
+        else bulk_store(dst, row4, (uint32_t)(12 * M));
+      } else if (!accumulate) {
+        bulk_store(dst, zero4, (uint32_t)(12 * M));
+      }
+    }
+    bulk_commit_and_wait_read();
+    return;
+  }
   const unsigned vis_mask = __ballot_sync(0xffffffffu, any);
   if (any) {
 #pragma unroll
@@ -551,9 +582,16 @@ void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3
   const size_t smem = (size_t)(PBWD_THREADS / 32) * 32 * (3 * M + 1) * sizeof(float);
   static PerDeviceLevel configured;
   if (smem > 48 * 1024) configured.ensure(smem, [&] {
-    cudaFuncSetAttribute(sh_grad_expand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(sh_grad_expand_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   });
-  sh_grad_expand_kernel<<<(P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(
+  const bool bulk = M % 4 == 0 && M <= 16 && (reinterpret_cast<size_t>(dL_dsh) & 15) == 0 && getenv("GSM_NO_BULK") == nullptr;
+  if (bulk) {
+    const size_t bsmem = (size_t)(PBWD_THREADS / 32) * 32 * SH_BULK_STRIDE * sizeof(float) + (PBWD_THREADS / 32) * 192;
+    sh_grad_expand_kernel<true><<<(P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, bsmem, stream>>>(
+        P, D, M, n_views, means3D, campos_all, drgb_all, view_stride, dL_dsh, accumulate);
+    return;
+  }
+  sh_grad_expand_kernel<false><<<(P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(
       P, D, M, n_views, means3D, campos_all, drgb_all, view_stride, dL_dsh, accumulate);
 }
 

@@ -398,15 +398,21 @@ def view_parallel_step_peer(params: Dict[str, torch.Tensor], cameras: Sequence, 
     # barrier 1: every rank's K6 has finished -> all receive slots and all partial sums are complete
     ex.flat_hdl.barrier(channel=0, timeout_ms=barrier_timeout_ms)
     t1 = mark(main)
-    ex.side.wait_stream(main)
-    with torch.cuda.stream(ex.side):      # the local SH expand runs next to the two-shot reduction
-        expand_fn(params["means3D"], ex.campos, ex.rgb_recv, ex.dL_dsh, sh_degree, view_stride=ex.slot_stride)
-        t_side = mark(ex.side)
     lib = _lib.load()
     ptrs = (ctypes.c_void_p * W)(*ex._flat_ptrs)
-    _lib.check(lib.gsm_peer_allreduce(ptrs, W, rank, ex.n_sum, ex.n_max, ctypes.c_void_p(main.cuda_stream)), "peer_allreduce")
-    t2 = mark(main)
-    main.wait_stream(ex.side)
+    if os.environ.get("GSM_VP_OVERLAP", "1") == "1":
+        ex.side.wait_stream(main)
+        with torch.cuda.stream(ex.side):      # the local SH expand runs next to the two-shot reduction
+            expand_fn(params["means3D"], ex.campos, ex.rgb_recv, ex.dL_dsh, sh_degree, view_stride=ex.slot_stride)
+            t_side = mark(ex.side)
+        _lib.check(lib.gsm_peer_allreduce(ptrs, W, rank, ex.n_sum, ex.n_max, ctypes.c_void_p(main.cuda_stream)), "peer_allreduce")
+        t2 = mark(main)
+        main.wait_stream(ex.side)
+    else:  # one after the other on the main stream (the remote shards first: peers wait for them, not for the expand)
+        _lib.check(lib.gsm_peer_allreduce(ptrs, W, rank, ex.n_sum, ex.n_max, ctypes.c_void_p(main.cuda_stream)), "peer_allreduce")
+        t2 = mark(main)
+        expand_fn(params["means3D"], ex.campos, ex.rgb_recv, ex.dL_dsh, sh_degree, view_stride=ex.slot_stride)
+        t_side = mark(main)
     t3 = mark(main)
     # barrier 2: every shard has been written everywhere, every rank is done reading its receive slots
     ex.flat_hdl.barrier(channel=1, timeout_ms=barrier_timeout_ms)

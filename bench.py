@@ -1052,7 +1052,8 @@ def main():
                          (wl["P"] * 58 * 4 / 1e9),
                    "exchange": ("none (single GPU)" if world == 1 else
                                 ("fused over NVLink peer memory: K6 pushes dL/dRGB (12 B/surfel/view) into every rank's slot, one "
-                                 "two-shot kernel reduces 48 B/surfel + max radii, local SH expand alongside"
+                                 "kernel reduces 48 B/surfel + max radii (%s), local SH expand alongside" %
+                                 ("NVLS multimem.ld_reduce / multimem.st" if getattr(arm.ex, "_flat_mc", 0) else "two-shot peer loads / stores")
                                  if getattr(arm, "peer", False) else
                                  "factored over NCCL: all-reduce 40 B/surfel + all-gather dL/dRGB 12 B/surfel/view + local SH expand")),
                    "debug_P_override": args.P is not None},

@@ -50,9 +50,51 @@ __global__ void __launch_bounds__(512) peer_allreduce_kernel(const PeerBufs bufs
   }
 }
 
+// The same reduction through the NVSwitch's multicast address space (NVLS): multimem.ld_reduce has the SWITCH fetch
+// the element from every rank's copy and return their sum (max) in one response, multimem.st has it write the result
+// into every rank's copy -- one request per 16 bytes and direction instead of n_ranks, the additions done in the fabric.
+__global__ void __launch_bounds__(512) peer_allreduce_multimem_kernel(char* mc, int n_ranks, int rank, size_t sum_vec, size_t max_vec) {
+  const size_t total = sum_vec + max_vec;
+  const size_t per = (total + n_ranks - 1) / n_ranks;
+  const size_t begin = per * (size_t)rank, end = min(begin + per, total);
+  for (size_t v = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < end; v += (size_t)gridDim.x * blockDim.x) {
+    char* a = mc + v * 16;
+    if (v < sum_vec) {
+      float x, y, z, w;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x), "=f"(y), "=f"(z), "=f"(w) : "l"(a) : "memory");
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+    } else {
+      int r[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) asm volatile("multimem.ld_reduce.relaxed.sys.global.max.s32 %0, [%1];" : "=r"(r[k]) : "l"(a + 4 * k) : "memory");
+#pragma unroll
+      for (int k = 0; k < 4; k++) asm volatile("multimem.st.relaxed.sys.global.s32 [%0], %1;" ::"l"(a + 4 * k), "r"(r[k]) : "memory");
+    }
+  }
+}
+
 }  // namespace gsm
 
 using namespace gsm;
+
+extern "C" int gsm_peer_allreduce_multimem(void* multicast_buf, int n_ranks, int rank, size_t n_sum, size_t n_max, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (multicast_buf == nullptr || n_ranks < 1 || rank < 0 || rank >= n_ranks || (n_sum & 3) || (n_max & 3) ||
+      (reinterpret_cast<size_t>(multicast_buf) & 15) != 0) {
+    set_error("gsm_peer_allreduce_multimem: bad arguments"); return GSM_ERR_INVALID_ARGUMENT;
+  }
+  const size_t sum_vec = n_sum / 4, max_vec = n_max / 4;
+  if (sum_vec + max_vec == 0 || n_ranks == 1) return GSM_OK;
+  int dev = 0, sms = 0;
+  GSM_CUDA(cudaGetDevice(&dev));
+  GSM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const size_t per = (sum_vec + max_vec + n_ranks - 1) / n_ranks;
+  const int grid = (int)min((size_t)sms * 2, (per + 511) / 512);
+  StageMark m(GSM_STAGE_PEER_ALLREDUCE, stream);
+  peer_allreduce_multimem_kernel<<<grid, 512, 0, stream>>>((char*)multicast_buf, n_ranks, rank, sum_vec, max_vec);
+  GSM_CUDA(cudaGetLastError());
+  return GSM_OK;
+}
 
 extern "C" int gsm_peer_allreduce(void* const* bufs, int n_ranks, int rank, size_t n_sum, size_t n_max, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;

@@ -11,6 +11,7 @@ the raw gradients), visibility counts are summed, radii are max-reduced.
 The data path has exactly one exchange step (the gradient all-reduce); rendering needs none.
 """
 from typing import Callable, Dict, List, NamedTuple, Optional, Sequence
+from torch._C._autograd import DeviceType
 
 import os
 
@@ -319,6 +320,13 @@ class PeerExchange:
         self.dL_dsh = torch.zeros(P, M, 3, dtype=torch.float32, device=device)
         self.side = torch.cuda.Stream(device=device)
         self._flat_ptrs = [int(p) for p in self.flat_hdl.buffer_ptrs]
+        # NVSwitch multicast mapping of the reduced buffer (NVLS), when the fabric offers it
+        self._flat_mc = 0
+        try:
+            if os.environ.get("GSM_VP_REDUCE", "multimem") == "multimem" and self.flat_hdl.has_multicast_support(DeviceType.CUDA, device.index if hasattr(device, "index") else 0):
+                self._flat_mc = int(self.flat_hdl.multicast_ptr or 0)
+        except Exception:
+            self._flat_mc = 0
         self._rgb_ptrs = [int(p) for p in self.rgb_hdl.buffer_ptrs]
         torch.cuda.synchronize(device)
         dist.barrier(self.group)                         # every rank's buffers are zeroed before anyone pushes
@@ -400,16 +408,23 @@ def view_parallel_step_peer(params: Dict[str, torch.Tensor], cameras: Sequence, 
     t1 = mark(main)
     lib = _lib.load()
     ptrs = (ctypes.c_void_p * W)(*ex._flat_ptrs)
+
+    def reduce_on(stream):
+        if ex._flat_mc:   # in-switch reduction (NVLS)
+            _lib.check(lib.gsm_peer_allreduce_multimem(ctypes.c_void_p(ex._flat_mc), W, rank, ex.n_sum, ex.n_max,
+                                                       ctypes.c_void_p(stream.cuda_stream)), "peer_allreduce_multimem")
+        else:
+            _lib.check(lib.gsm_peer_allreduce(ptrs, W, rank, ex.n_sum, ex.n_max, ctypes.c_void_p(stream.cuda_stream)), "peer_allreduce")
     if os.environ.get("GSM_VP_OVERLAP", "1") == "1":
         ex.side.wait_stream(main)
         with torch.cuda.stream(ex.side):      # the local SH expand runs next to the two-shot reduction
             expand_fn(params["means3D"], ex.campos, ex.rgb_recv, ex.dL_dsh, sh_degree, view_stride=ex.slot_stride)
             t_side = mark(ex.side)
-        _lib.check(lib.gsm_peer_allreduce(ptrs, W, rank, ex.n_sum, ex.n_max, ctypes.c_void_p(main.cuda_stream)), "peer_allreduce")
+        reduce_on(main)
         t2 = mark(main)
         main.wait_stream(ex.side)
     else:  # one after the other on the main stream (the remote shards first: peers wait for them, not for the expand)
-        _lib.check(lib.gsm_peer_allreduce(ptrs, W, rank, ex.n_sum, ex.n_max, ctypes.c_void_p(main.cuda_stream)), "peer_allreduce")
+        reduce_on(main)
         t2 = mark(main)
         expand_fn(params["means3D"], ex.campos, ex.rgb_recv, ex.dL_dsh, sh_degree, view_stride=ex.slot_stride)
         t_side = mark(main)

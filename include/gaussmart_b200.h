@@ -244,6 +244,9 @@ int gsm_sh_grad_expand_strided(int P, int D, int M, int n_views, const float* me
  *      everywhere. */
 int gsm_peer_allreduce(void* const* bufs /*HOST array [n_ranks] of device pointers*/, int n_ranks, int rank,
                        size_t n_sum, size_t n_max, void* stream);
+/* the same through the NVSwitch multicast mapping of the buffer (NVLS: multimem.ld_reduce / multimem.st -- the switch
+ * sums the ranks' copies and writes the result back to all of them); multicast_buf = the buffer's multicast address */
+int gsm_peer_allreduce_multimem(void* multicast_buf, int n_ranks, int rank, size_t n_sum, size_t n_max, void* stream);
 
 /* ---- photometric loss of the training iteration (the rasterizer's caller).  Replaces, fused,
  *      utils/loss_utils.py:16-17 (l1_loss) + :32-62 (ssim, _ssim: 11x11 Gaussian window, sigma 1.5, zero padding,

@@ -101,7 +101,7 @@ def main():
         if not same:
             print(f"[rank {rank}] peer exchange: ranks hold different bits {hs}", flush=True)
         ok &= same
-        peer_ok = "ok"
+        peer_ok = "ok (all-reduce: %s)" % ("NVLS multimem" if pex._flat_mc else "two-shot peer loads/stores")
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:

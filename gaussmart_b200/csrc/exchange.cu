@@ -27,26 +27,37 @@ __global__ void __launch_bounds__(512) peer_allreduce_kernel(const PeerBufs bufs
   const size_t total = sum_vec + max_vec;
   const size_t per = (total + NR - 1) / NR;
   const size_t begin = per * (size_t)rank, end = min(begin + per, total);
-  for (size_t v = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < end; v += (size_t)gridDim.x * blockDim.x) {
-    float4 x[NR];
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  constexpr int U = NR <= 2 ? 8 : (NR <= 4 ? 4 : 2);   // U x NR 128-bit peer loads in flight per thread
+  for (size_t v0 = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < end; v0 += stride * U) {
+    float4 x[U][NR];
 #pragma unroll
-    for (int k = 0; k < NR; k++)   // NR loads in flight
-      x[k] = SYS ? ld_peer(reinterpret_cast<const float4*>(bufs.p[k]) + v) : reinterpret_cast<const float4*>(bufs.p[k])[v];
-    float4 r = x[0];
-    if (v < sum_vec) {
+    for (int u = 0; u < U; u++) {
+      const size_t v = min(v0 + stride * u, end - 1);
 #pragma unroll
-      for (int k = 1; k < NR; k++) { r.x += x[k].x; r.y += x[k].y; r.z += x[k].z; r.w += x[k].w; }
-    } else {
-#pragma unroll
-      for (int k = 1; k < NR; k++) {
-        r.x = __int_as_float(max(__float_as_int(r.x), __float_as_int(x[k].x)));
-        r.y = __int_as_float(max(__float_as_int(r.y), __float_as_int(x[k].y)));
-        r.z = __int_as_float(max(__float_as_int(r.z), __float_as_int(x[k].z)));
-        r.w = __int_as_float(max(__float_as_int(r.w), __float_as_int(x[k].w)));
-      }
+      for (int k = 0; k < NR; k++)
+        x[u][k] = SYS ? ld_peer(reinterpret_cast<const float4*>(bufs.p[k]) + v) : reinterpret_cast<const float4*>(bufs.p[k])[v];
     }
 #pragma unroll
-    for (int k = 0; k < NR; k++) reinterpret_cast<float4*>(bufs.p[k])[v] = r;
+    for (int u = 0; u < U; u++) {
+      const size_t v = v0 + stride * u;
+      if (v >= end) continue;
+      float4 r = x[u][0];
+      if (v < sum_vec) {
+#pragma unroll
+        for (int k = 1; k < NR; k++) { r.x += x[u][k].x; r.y += x[u][k].y; r.z += x[u][k].z; r.w += x[u][k].w; }
+      } else {
+#pragma unroll
+        for (int k = 1; k < NR; k++) {
+          r.x = __int_as_float(max(__float_as_int(r.x), __float_as_int(x[u][k].x)));
+          r.y = __int_as_float(max(__float_as_int(r.y), __float_as_int(x[u][k].y)));
+          r.z = __int_as_float(max(__float_as_int(r.z), __float_as_int(x[u][k].z)));
+          r.w = __int_as_float(max(__float_as_int(r.w), __float_as_int(x[u][k].w)));
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < NR; k++) reinterpret_cast<float4*>(bufs.p[k])[v] = r;
+    }
   }
 }
 
@@ -57,18 +68,30 @@ __global__ void __launch_bounds__(512) peer_allreduce_multimem_kernel(char* mc, 
   const size_t total = sum_vec + max_vec;
   const size_t per = (total + n_ranks - 1) / n_ranks;
   const size_t begin = per * (size_t)rank, end = min(begin + per, total);
-  for (size_t v = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < end; v += (size_t)gridDim.x * blockDim.x) {
-    char* a = mc + v * 16;
-    if (v < sum_vec) {
-      float x, y, z, w;
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x), "=f"(y), "=f"(z), "=f"(w) : "l"(a) : "memory");
-      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
-    } else {
-      int r[4];
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  constexpr int U = 8;   // requests in flight per thread: a round trip through the switch is several microseconds
+  for (size_t v0 = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < end; v0 += stride * U) {
+    float4 r[U];
 #pragma unroll
-      for (int k = 0; k < 4; k++) asm volatile("multimem.ld_reduce.relaxed.sys.global.max.s32 %0, [%1];" : "=r"(r[k]) : "l"(a + 4 * k) : "memory");
+    for (int u = 0; u < U; u++) {
+      const size_t v = v0 + stride * u;
+      char* a = mc + v * 16;
+      if (v >= end) continue;
+      if (v < sum_vec) {
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(r[u].x), "=f"(r[u].y), "=f"(r[u].z), "=f"(r[u].w) : "l"(a) : "memory");
+      } else {
+        int q[4];
 #pragma unroll
-      for (int k = 0; k < 4; k++) asm volatile("multimem.st.relaxed.sys.global.s32 [%0], %1;" ::"l"(a + 4 * k), "r"(r[k]) : "memory");
+        for (int k = 0; k < 4; k++) asm volatile("multimem.ld_reduce.relaxed.sys.global.max.s32 %0, [%1];" : "=r"(q[k]) : "l"(a + 4 * k) : "memory");
+        r[u] = make_float4(__int_as_float(q[0]), __int_as_float(q[1]), __int_as_float(q[2]), __int_as_float(q[3]));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const size_t v = v0 + stride * u;
+      if (v >= end) continue;
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc + v * 16), "f"(r[u].x), "f"(r[u].y), "f"(r[u].z), "f"(r[u].w) : "memory");
     }
   }
 }

@@ -21,14 +21,18 @@ __device__ __forceinline__ float4 ld_peer(const float4* a) {  // peer data is wr
 
 // SYS: system-scope relaxed loads (never served from a stale L1 line); otherwise plain loads -- safe here because every
 // byte this kernel reads was written before the barrier that precedes its launch, and L1 starts a kernel invalidated
+// 256 threads, ONE CTA per SM: the kernel is bound by NVLink (~0.7 ms for 260 MB at 8 ranks, NCCL's rate), not by
+// the SMs, and it runs NEXT TO the local SH expand -- a fat launch (2 x 512 threads per SM) took the register file away
+// from the expand, which then ran at less than half its speed.
+constexpr int PEER_THREADS = 256;
 template <int NR, bool SYS>
-__global__ void __launch_bounds__(512) peer_allreduce_kernel(const PeerBufs bufs, int rank, size_t sum_vec, size_t max_vec) {
+__global__ void __launch_bounds__(PEER_THREADS) peer_allreduce_kernel(const PeerBufs bufs, int rank, size_t sum_vec, size_t max_vec) {
   // vectors of 16 bytes; [0, sum_vec) fp32 sums, [sum_vec, sum_vec + max_vec) int32 maxima
   const size_t total = sum_vec + max_vec;
   const size_t per = (total + NR - 1) / NR;
   const size_t begin = per * (size_t)rank, end = min(begin + per, total);
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  constexpr int U = NR <= 2 ? 8 : (NR <= 4 ? 4 : 2);   // U x NR 128-bit peer loads in flight per thread
+  constexpr int U = NR <= 2 ? 8 : (NR <= 4 ? 4 : 3);   // U x NR 128-bit peer loads in flight per thread
   for (size_t v0 = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < end; v0 += stride * U) {
     float4 x[U][NR];
 #pragma unroll
@@ -64,7 +68,7 @@ __global__ void __launch_bounds__(512) peer_allreduce_kernel(const PeerBufs bufs
 // The same reduction through the NVSwitch's multicast address space (NVLS): multimem.ld_reduce has the SWITCH fetch
 // the element from every rank's copy and return their sum (max) in one response, multimem.st has it write the result
 // into every rank's copy -- one request per 16 bytes and direction instead of n_ranks, the additions done in the fabric.
-__global__ void __launch_bounds__(512) peer_allreduce_multimem_kernel(char* mc, int n_ranks, int rank, size_t sum_vec, size_t max_vec) {
+__global__ void __launch_bounds__(PEER_THREADS) peer_allreduce_multimem_kernel(char* mc, int n_ranks, int rank, size_t sum_vec, size_t max_vec) {
   const size_t total = sum_vec + max_vec;
   const size_t per = (total + n_ranks - 1) / n_ranks;
   const size_t begin = per * (size_t)rank, end = min(begin + per, total);
@@ -112,9 +116,9 @@ extern "C" int gsm_peer_allreduce_multimem(void* multicast_buf, int n_ranks, int
   GSM_CUDA(cudaGetDevice(&dev));
   GSM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const size_t per = (sum_vec + max_vec + n_ranks - 1) / n_ranks;
-  const int grid = (int)min((size_t)sms * 2, (per + 511) / 512);
+  const int grid = (int)min((size_t)sms, (per + PEER_THREADS - 1) / PEER_THREADS);
   StageMark m(GSM_STAGE_PEER_ALLREDUCE, stream);
-  peer_allreduce_multimem_kernel<<<grid, 512, 0, stream>>>((char*)multicast_buf, n_ranks, rank, sum_vec, max_vec);
+  peer_allreduce_multimem_kernel<<<grid, PEER_THREADS, 0, stream>>>((char*)multicast_buf, n_ranks, rank, sum_vec, max_vec);
   GSM_CUDA(cudaGetLastError());
   return GSM_OK;
 }
@@ -139,12 +143,12 @@ extern "C" int gsm_peer_allreduce(void* const* bufs, int n_ranks, int rank, size
   StageMark m(GSM_STAGE_PEER_ALLREDUCE, stream);
   static const bool sys_loads = [] { const char* e = getenv("GSM_PEER_LD"); return e != nullptr && e[0] == 's'; }();
 #define GSM_PEER_CASE(N) \
-  case N: if (sys_loads) peer_allreduce_kernel<N, true><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); \
-          else peer_allreduce_kernel<N, false><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
+  case N: if (sys_loads) peer_allreduce_kernel<N, true><<<grid, PEER_THREADS, 0, stream>>>(pb, rank, sum_vec, max_vec); \
+          else peer_allreduce_kernel<N, false><<<grid, PEER_THREADS, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
   switch (n_ranks) {
     GSM_PEER_CASE(2) GSM_PEER_CASE(3) GSM_PEER_CASE(4) GSM_PEER_CASE(5) GSM_PEER_CASE(6) GSM_PEER_CASE(7)
-    default: if (sys_loads) peer_allreduce_kernel<8, true><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec);
-             else peer_allreduce_kernel<8, false><<<grid, 512, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
+    default: if (sys_loads) peer_allreduce_kernel<8, true><<<grid, PEER_THREADS, 0, stream>>>(pb, rank, sum_vec, max_vec);
+             else peer_allreduce_kernel<8, false><<<grid, PEER_THREADS, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
   }
 #undef GSM_PEER_CASE
   GSM_CUDA(cudaGetLastError());

@@ -323,7 +323,7 @@ class PeerExchange:
         # NVSwitch multicast mapping of the reduced buffer (NVLS), when the fabric offers it
         self._flat_mc = 0
         try:
-            if os.environ.get("GSM_VP_REDUCE", "multimem") == "multimem" and self.flat_hdl.has_multicast_support(DeviceType.CUDA, device.index if hasattr(device, "index") else 0):
+            if os.environ.get("GSM_VP_REDUCE", "peer") == "multimem" and self.flat_hdl.has_multicast_support(DeviceType.CUDA, device.index if hasattr(device, "index") else 0):
                 self._flat_mc = int(self.flat_hdl.multicast_ptr or 0)
         except Exception:
             self._flat_mc = 0

@@ -415,13 +415,22 @@ def view_parallel_step_peer(params: Dict[str, torch.Tensor], cameras: Sequence, 
                                                        ctypes.c_void_p(stream.cuda_stream)), "peer_allreduce_multimem")
         else:
             _lib.check(lib.gsm_peer_allreduce(ptrs, W, rank, ex.n_sum, ex.n_max, ctypes.c_void_p(stream.cuda_stream)), "peer_allreduce")
-    if os.environ.get("GSM_VP_OVERLAP", "1") == "1":
+    ov = os.environ.get("GSM_VP_OVERLAP", "1")
+    if ov == "1":
         ex.side.wait_stream(main)
         with torch.cuda.stream(ex.side):      # the local SH expand runs next to the two-shot reduction
             expand_fn(params["means3D"], ex.campos, ex.rgb_recv, ex.dL_dsh, sh_degree, view_stride=ex.slot_stride)
             t_side = mark(ex.side)
         reduce_on(main)
         t2 = mark(main)
+        main.wait_stream(ex.side)
+    elif ov == "2":   # the reduction on the side stream, issued first; the expand on the main stream
+        ex.side.wait_stream(main)
+        with torch.cuda.stream(ex.side):
+            reduce_on(ex.side)
+            t2 = mark(ex.side)
+        expand_fn(params["means3D"], ex.campos, ex.rgb_recv, ex.dL_dsh, sh_degree, view_stride=ex.slot_stride)
+        t_side = mark(main)
         main.wait_stream(ex.side)
     else:  # one after the other on the main stream (the remote shards first: peers wait for them, not for the expand)
         reduce_on(main)

@@ -410,6 +410,10 @@ def view_parallel_step_peer(params: Dict[str, torch.Tensor], cameras: Sequence, 
     ptrs = (ctypes.c_void_p * W)(*ex._flat_ptrs)
 
     def reduce_on(stream):
+        if os.environ.get("GSM_VP_PROBE", "") == "sleep":   # timing probe: a one-CTA spin kernel in place of the reduction
+            with torch.cuda.stream(stream):
+                torch.cuda._sleep(int(0.4e-3 * 1.9e9))
+            return
         if ex._flat_mc:   # in-switch reduction (NVLS)
             _lib.check(lib.gsm_peer_allreduce_multimem(ctypes.c_void_p(ex._flat_mc), W, rank, ex.n_sum, ex.n_max,
                                                        ctypes.c_void_p(stream.cuda_stream)), "peer_allreduce_multimem")

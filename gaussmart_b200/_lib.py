@@ -31,7 +31,7 @@ EXPORTS = [
     "gsm_surface_regularizer_workspace_bytes", "gsm_surface_regularizer",
     "gsm_status_create", "gsm_status_destroy", "gsm_status_query", "gsm_status_wait", "gsm_fp32_peak_probe",
     "gsm_densify_workspace_bytes", "gsm_densify_plan", "gsm_densify_apply",
-    "gsm_sh_grad_expand_strided", "gsm_peer_allreduce", "gsm_peer_allreduce_multimem",
+    "gsm_sh_grad_expand_strided", "gsm_peer_allreduce", "gsm_peer_allreduce_multimem", "gsm_peer_staging_floats", "gsm_peer_scatter", "gsm_peer_sum_broadcast",
 ]
 
 
@@ -170,6 +170,12 @@ def load():
     lib.gsm_sh_grad_expand_strided.argtypes = [c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_void_p]
     lib.gsm_peer_allreduce.restype = c_int
     lib.gsm_peer_allreduce.argtypes = [POINTER(c_void_p), c_int, c_int, c_size_t, c_size_t, c_void_p]
+    lib.gsm_peer_staging_floats.restype = c_size_t
+    lib.gsm_peer_staging_floats.argtypes = [c_int, c_size_t, c_size_t]
+    lib.gsm_peer_scatter.restype = c_int
+    lib.gsm_peer_scatter.argtypes = [c_void_p, POINTER(c_void_p), c_int, c_int, c_size_t, c_size_t, c_void_p]
+    lib.gsm_peer_sum_broadcast.restype = c_int
+    lib.gsm_peer_sum_broadcast.argtypes = [c_void_p, POINTER(c_void_p), c_int, c_int, c_size_t, c_size_t, c_void_p]
     lib.gsm_peer_allreduce_multimem.restype = c_int
     lib.gsm_peer_allreduce_multimem.argtypes = [c_void_p, c_int, c_int, c_size_t, c_size_t, c_void_p]
     lib.gsm_densify_workspace_bytes.restype = c_size_t

@@ -65,6 +65,51 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_allreduce_kernel(const Peer
   }
 }
 
+// ---- the same all-reduce with WRITES only on the wire ("push" form) --------------------------------------------
+// Measured on 8 B200s: a kernel that LOADS from peers moves ~350 GB/s per direction and, while it runs, starves every
+// other kernel's memory traffic (the SH expand next to it made 10 % progress); posted peer STORES fused into a
+// streaming kernel are nearly free (K6 pushes 420 MB of dL/dRGB rows for +0.19 ms).  So:
+//   1. scatter: every rank pushes shard s of its partial buffer into rank s's staging area, slot [own rank];
+//   2. (barrier)  sum + broadcast: rank s sums the n staged copies of its shard -- LOCAL loads, fixed order -- and
+//      pushes the result into every rank's buffer.
+template <int NR>
+__global__ void __launch_bounds__(PEER_THREADS) peer_scatter_kernel(const float4* __restrict__ local, const PeerBufs staging,
+                                                                     int rank, size_t total, size_t per) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < total; v += stride) {
+    const size_t s = v / per;   // owner of this vector
+    reinterpret_cast<float4*>(staging.p[s])[(size_t)rank * per + (v - s * per)] = __ldcs(local + v);
+  }
+}
+
+template <int NR>
+__global__ void __launch_bounds__(PEER_THREADS) peer_sum_broadcast_kernel(const float4* __restrict__ staged, const PeerBufs flats,
+                                                                           int rank, size_t sum_vec, size_t max_vec, size_t per) {
+  const size_t total = sum_vec + max_vec;
+  const size_t begin = per * (size_t)rank, n = begin < total ? min(per, total - begin) : 0;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t o = (size_t)blockIdx.x * blockDim.x + threadIdx.x; o < n; o += stride) {
+    float4 x[NR];
+#pragma unroll
+    for (int k = 0; k < NR; k++) x[k] = staged[(size_t)k * per + o];   // written by rank k before the barrier: plain loads
+    float4 r = x[0];
+    if (begin + o < sum_vec) {
+#pragma unroll
+      for (int k = 1; k < NR; k++) { r.x += x[k].x; r.y += x[k].y; r.z += x[k].z; r.w += x[k].w; }
+    } else {
+#pragma unroll
+      for (int k = 1; k < NR; k++) {
+        r.x = __int_as_float(max(__float_as_int(r.x), __float_as_int(x[k].x)));
+        r.y = __int_as_float(max(__float_as_int(r.y), __float_as_int(x[k].y)));
+        r.z = __int_as_float(max(__float_as_int(r.z), __float_as_int(x[k].z)));
+        r.w = __int_as_float(max(__float_as_int(r.w), __float_as_int(x[k].w)));
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < NR; k++) reinterpret_cast<float4*>(flats.p[k])[begin + o] = r;
+  }
+}
+
 // The same reduction through the NVSwitch's multicast address space (NVLS): multimem.ld_reduce has the SWITCH fetch
 // the element from every rank's copy and return their sum (max) in one response, multimem.st has it write the result
 // into every rank's copy -- one request per 16 bytes and direction instead of n_ranks, the additions done in the fabric.
@@ -151,6 +196,67 @@ extern "C" int gsm_peer_allreduce(void* const* bufs, int n_ranks, int rank, size
              else peer_allreduce_kernel<8, false><<<grid, PEER_THREADS, 0, stream>>>(pb, rank, sum_vec, max_vec); break;
   }
 #undef GSM_PEER_CASE
+  GSM_CUDA(cudaGetLastError());
+  return GSM_OK;
+}
+
+static int check_peers(void* const* bufs, int n_ranks, int rank, size_t n_sum, size_t n_max, const char* what) {
+  if (bufs == nullptr || n_ranks < 1 || n_ranks > GSM_MAX_PEERS || rank < 0 || rank >= n_ranks || (n_sum & 3) || (n_max & 3)) {
+    set_error("%s: bad arguments (1..%d ranks, counts multiples of 4)", what, GSM_MAX_PEERS); return GSM_ERR_INVALID_ARGUMENT;
+  }
+  for (int k = 0; k < n_ranks; k++)
+    if (bufs[k] == nullptr || (reinterpret_cast<size_t>(bufs[k]) & 15) != 0) { set_error("%s: buffer %d null or misaligned", what, k); return GSM_ERR_INVALID_ARGUMENT; }
+  return GSM_OK;
+}
+
+extern "C" size_t gsm_peer_staging_floats(int n_ranks, size_t n_sum, size_t n_max) {
+  const size_t total = (n_sum + n_max) / 4;
+  const size_t per = (total + (size_t)(n_ranks > 0 ? n_ranks : 1) - 1) / (size_t)(n_ranks > 0 ? n_ranks : 1);
+  return per * 4 * (size_t)(n_ranks > 0 ? n_ranks : 1);
+}
+
+extern "C" int gsm_peer_scatter(const void* local_buf, void* const* staging, int n_ranks, int rank, size_t n_sum, size_t n_max,
+                                void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (int rc = check_peers(staging, n_ranks, rank, n_sum, n_max, "gsm_peer_scatter")) return rc;
+  if (local_buf == nullptr || (reinterpret_cast<size_t>(local_buf) & 15) != 0) { set_error("gsm_peer_scatter: local buffer"); return GSM_ERR_INVALID_ARGUMENT; }
+  const size_t total = (n_sum + n_max) / 4;
+  if (total == 0) return GSM_OK;
+  const size_t per = (total + n_ranks - 1) / n_ranks;
+  PeerBufs pb{};
+  for (int k = 0; k < n_ranks; k++) pb.p[k] = staging[k];
+  int dev = 0, sms = 0;
+  GSM_CUDA(cudaGetDevice(&dev));
+  GSM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = (int)min((size_t)sms * 4, (total + PEER_THREADS - 1) / PEER_THREADS);
+  StageMark m(GSM_STAGE_PEER_ALLREDUCE, stream);
+  peer_scatter_kernel<8><<<grid, PEER_THREADS, 0, stream>>>((const float4*)local_buf, pb, rank, total, per);
+  GSM_CUDA(cudaGetLastError());
+  return GSM_OK;
+}
+
+extern "C" int gsm_peer_sum_broadcast(const void* my_staging, void* const* bufs, int n_ranks, int rank, size_t n_sum, size_t n_max,
+                                      void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (int rc = check_peers(bufs, n_ranks, rank, n_sum, n_max, "gsm_peer_sum_broadcast")) return rc;
+  if (my_staging == nullptr || (reinterpret_cast<size_t>(my_staging) & 15) != 0) { set_error("gsm_peer_sum_broadcast: staging buffer"); return GSM_ERR_INVALID_ARGUMENT; }
+  const size_t sum_vec = n_sum / 4, max_vec = n_max / 4, total = sum_vec + max_vec;
+  if (total == 0) return GSM_OK;
+  const size_t per = (total + n_ranks - 1) / n_ranks;
+  PeerBufs pb{};
+  for (int k = 0; k < n_ranks; k++) pb.p[k] = bufs[k];
+  int dev = 0, sms = 0;
+  GSM_CUDA(cudaGetDevice(&dev));
+  GSM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = (int)min((size_t)sms * 2, (per + PEER_THREADS - 1) / PEER_THREADS);
+  StageMark m(GSM_STAGE_PEER_ALLREDUCE, stream);
+  const float4* st = (const float4*)my_staging;
+#define GSM_SB_CASE(N) case N: peer_sum_broadcast_kernel<N><<<grid, PEER_THREADS, 0, stream>>>(st, pb, rank, sum_vec, max_vec, per); break;
+  switch (n_ranks) {
+    GSM_SB_CASE(1) GSM_SB_CASE(2) GSM_SB_CASE(3) GSM_SB_CASE(4) GSM_SB_CASE(5) GSM_SB_CASE(6) GSM_SB_CASE(7)
+    default: peer_sum_broadcast_kernel<8><<<grid, PEER_THREADS, 0, stream>>>(st, pb, rank, sum_vec, max_vec, per); break;
+  }
+#undef GSM_SB_CASE
   GSM_CUDA(cudaGetLastError());
   return GSM_OK;
 }

@@ -312,6 +312,11 @@ class PeerExchange:
         self._stats_off = off
         self.stats = self.flat[off:off + 2 * P_pad].view(2, P_pad)[:, :P] if with_stats else None
         self.max_radii = self.flat[self.n_sum:self.n_sum + P].view(torch.int32) if with_stats else None
+        # staging area of the push-form all-reduce: this rank's shard of every rank's partial buffer
+        from . import _lib
+        self.stage = symm_mem.empty(int(_lib.load().gsm_peer_staging_floats(W, self.n_sum, self.n_max)), dtype=torch.float32, device=device)
+        self.stage_hdl = symm_mem.rendezvous(self.stage, self.group)
+        self._stage_ptrs = [int(p) for p in self.stage_hdl.buffer_ptrs]
         self.slot_stride = (3 * P + 31) // 32 * 32       # floats; every [P,3] slot starts 128-byte aligned
         self.rgb_recv = symm_mem.empty(W * L * self.slot_stride, dtype=torch.float32, device=device)
         self.rgb_hdl = symm_mem.rendezvous(self.rgb_recv, self.group)
@@ -403,18 +408,26 @@ def view_parallel_step_peer(params: Dict[str, torch.Tensor], cameras: Sequence, 
         e.record(stream)
         return e
     t0 = mark(main)
-    # barrier 1: every rank's K6 has finished -> all receive slots and all partial sums are complete
-    ex.flat_hdl.barrier(channel=0, timeout_ms=barrier_timeout_ms)
-    t1 = mark(main)
     lib = _lib.load()
     ptrs = (ctypes.c_void_p * W)(*ex._flat_ptrs)
+    push = os.environ.get("GSM_VP_REDUCE", "push") == "push" and not ex._flat_mc
+    if push:   # shard s of this rank's partial sums -> rank s's staging area (posted stores)
+        sptrs = (ctypes.c_void_p * W)(*ex._stage_ptrs)
+        _lib.check(lib.gsm_peer_scatter(ctypes.c_void_p(ex.flat.data_ptr()), sptrs, W, rank, ex.n_sum, ex.n_max,
+                                        ctypes.c_void_p(main.cuda_stream)), "peer_scatter")
+    # barrier 1: every rank's K6 (and scatter) has finished -> all receive slots and all staged shards are complete
+    ex.flat_hdl.barrier(channel=0, timeout_ms=barrier_timeout_ms)
+    t1 = mark(main)
 
     def reduce_on(stream):
         if os.environ.get("GSM_VP_PROBE", "") == "sleep":   # timing probe: a one-CTA spin kernel in place of the reduction
             with torch.cuda.stream(stream):
                 torch.cuda._sleep(int(0.4e-3 * 1.9e9))
             return
-        if ex._flat_mc:   # in-switch reduction (NVLS)
+        if push:          # local sum of the staged shards, result pushed to every rank
+            _lib.check(lib.gsm_peer_sum_broadcast(ctypes.c_void_p(ex.stage.data_ptr()), ptrs, W, rank, ex.n_sum, ex.n_max,
+                                                  ctypes.c_void_p(stream.cuda_stream)), "peer_sum_broadcast")
+        elif ex._flat_mc:   # in-switch reduction (NVLS)
             _lib.check(lib.gsm_peer_allreduce_multimem(ctypes.c_void_p(ex._flat_mc), W, rank, ex.n_sum, ex.n_max,
                                                        ctypes.c_void_p(stream.cuda_stream)), "peer_allreduce_multimem")
         else:

@@ -244,6 +244,16 @@ int gsm_sh_grad_expand_strided(int P, int D, int M, int n_views, const float* me
  *      everywhere. */
 int gsm_peer_allreduce(void* const* bufs /*HOST array [n_ranks] of device pointers*/, int n_ranks, int rank,
                        size_t n_sum, size_t n_max, void* stream);
+/* The same all-reduce with only WRITES on the wire (the production form: peer loads run at ~1/3 of the rate of posted peer
+ * stores on NVLink 5 and starve concurrent kernels): gsm_peer_scatter pushes shard s of the caller's buffer into rank
+ * s's staging area (slot [rank]; staging areas of gsm_peer_staging_floats(n, n_sum, n_max) floats, symmetric);
+ * after a cross-rank barrier, gsm_peer_sum_broadcast sums the n staged copies of the caller's own shard with LOCAL
+ * loads in rank order and pushes the result into every rank's buffer; a second barrier completes the all-reduce. */
+size_t gsm_peer_staging_floats(int n_ranks, size_t n_sum, size_t n_max);
+int gsm_peer_scatter(const void* local_buf, void* const* staging /*HOST [n_ranks]*/, int n_ranks, int rank, size_t n_sum,
+                     size_t n_max, void* stream);
+int gsm_peer_sum_broadcast(const void* my_staging, void* const* bufs /*HOST [n_ranks]*/, int n_ranks, int rank, size_t n_sum,
+                           size_t n_max, void* stream);
 /* the same through the NVSwitch multicast mapping of the buffer (NVLS: multimem.ld_reduce / multimem.st -- the switch
  * sums the ranks' copies and writes the result back to all of them); multicast_buf = the buffer's multicast address */
 int gsm_peer_allreduce_multimem(void* multicast_buf, int n_ranks, int rank, size_t n_sum, size_t n_max, void* stream);

@@ -275,8 +275,15 @@ def view_parallel_step_factored(params: Dict[str, torch.Tensor], cameras: Sequen
 #     coalesced 128-bit peer stores) -- the all-gather costs no launch and hides inside the kernel;
 #   * the rest is ONE hand-written two-shot kernel (gsm_peer_allreduce, csrc/exchange.cu): rank r reduces shard r of all
 #     ranks' buffers (SUM for the gradient / statistics floats, MAX for the radii, in one pass) and writes it back to
-#     all ranks; it runs on a side stream next to the local SH expand;
+#     all ranks; the local SH expand is issued next to it on a side stream;
 #   * two signal-pad barriers bracket the pair.
+# Measured on 8 B200s (C4, 260 MB reduced + 420 MB of dL/dRGB rows per rank and step; profiles/r02_exchange_probes.md):
+# the pushes cost K6 +0.19 ms; the two-shot kernel takes 0.69 ms (NVLink-bound: NCCL's rate for this size) whatever
+# its launch shape; while it runs the expand next to it makes almost no progress (a spin kernel in its place overlaps
+# perfectly), so the pair costs 1.08 ms against 0.69 + 0.46 one after the other.  Two alternatives are kept behind
+# GSM_VP_REDUCE and were NOT faster: "multimem" (in-switch NVLS reduction: 0.58 ms + 0.33 ms of posted writes landing in
+# the closing barrier) and "push" (scatter into staging + local sum + broadcast, stores only: 0.25 + 0.22 ms at 2 GPUs
+# against 0.39 ms).
 def peer_exchange_available(group=None) -> bool:
     """True when torch's symmetric memory can serve this process group (NCCL backend, CUDA, one NVLink domain)."""
     try:
@@ -410,7 +417,7 @@ def view_parallel_step_peer(params: Dict[str, torch.Tensor], cameras: Sequence, 
     t0 = mark(main)
     lib = _lib.load()
     ptrs = (ctypes.c_void_p * W)(*ex._flat_ptrs)
-    push = os.environ.get("GSM_VP_REDUCE", "push") == "push" and not ex._flat_mc
+    push = os.environ.get("GSM_VP_REDUCE", "peer") == "push" and not ex._flat_mc
     if push:   # shard s of this rank's partial sums -> rank s's staging area (posted stores)
         sptrs = (ctypes.c_void_p * W)(*ex._stage_ptrs)
         _lib.check(lib.gsm_peer_scatter(ctypes.c_void_p(ex.flat.data_ptr()), sptrs, W, rank, ex.n_sum, ex.n_max,

@@ -243,8 +243,14 @@ void launch_scatter(int P, const uint4* rects, const int* radii, uint32_t* tile_
 //    global memory (same code, generic pointers).  Each launch covers all tiles; a CTA whose
 //    segment length is outside the launch's class returns at once.
 // ---------------------------------------------------------------------------------------------
-constexpr uint32_t TS_CAP_SMALL = 4096;    // pairs per shared-memory buffer of the small class (2 x 32 KB + 32 KB histograms: 2 CTAs/SM)
-constexpr uint32_t TS_CAP_LARGE = 9216;    // large class (2 x 72 KB), 1024 threads
+#ifndef GSM_TS_CAP_SMALL
+#define GSM_TS_CAP_SMALL 4096
+#endif
+#ifndef GSM_TS_CAP_LARGE
+#define GSM_TS_CAP_LARGE 9216
+#endif
+constexpr uint32_t TS_CAP_SMALL = GSM_TS_CAP_SMALL;    // pairs per shared-memory buffer of the small class (2 x 32 KB + 32 KB histograms: 2 CTAs/SM)
+constexpr uint32_t TS_CAP_LARGE = GSM_TS_CAP_LARGE;    // large class (2 x 72 KB), 1024 threads
 constexpr int TS_SMALL_THREADS = 512, TS_SMALL_BITS = 9;   // <= 9-bit digits: 26 differing bits -> 3 passes
 constexpr int TS_LARGE_THREADS = 1024, TS_LARGE_BITS = 8;   // (9-bit digits measured slower here: 355 vs 275 us)
 

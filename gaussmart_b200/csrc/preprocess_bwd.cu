@@ -115,6 +115,85 @@ __device__ void sh_backward(int D, int M, float* row, f3 dir_orig, f3 dL_dRGB, f
   dL_dmean_add.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
 }
 
+// sh_backward over a 16-byte aligned shared-memory row accessed with 128-bit loads / stores (TMA bulk mode: the row
+// arrived by cp.async.bulk and leaves the same way).  Same expressions as sh_backward; the coefficients are read degree
+// by degree (at most 6 float4 live), every read precedes the first write.
+__device__ __forceinline__ void sh_backward_row4(int D, int M, float4* row4, f3 dir_orig, f3 dL_dRGB, f3& dL_dmean_add) {
+  const float len = __fsqrt_rn(__fmaf_rn(dir_orig.z, dir_orig.z, __fmaf_rn(dir_orig.x, dir_orig.x, __fmul_rn(dir_orig.y, dir_orig.y))));
+  const float x = __fdiv_rn(dir_orig.x, len), y = __fdiv_rn(dir_orig.y, len), z = __fdiv_rn(dir_orig.z, len);
+  const float C1 = 0.4886025119029199f;
+  f3 dx = mk(0, 0, 0), dy = mk(0, 0, 0), dz = mk(0, 0, 0);
+  int written = 1;
+  if (D > 0) {
+    {
+      const float4 v0 = row4[0], v1 = row4[1], v2 = row4[2];   // floats 0..11: SH(1) = 3..5, SH(2) = 6..8, SH(3) = 9..11
+      const f3 s1 = mk(v0.w, v1.x, v1.y), s2 = mk(v1.z, v1.w, v2.x), s3 = mk(v2.y, v2.z, v2.w);
+      dx = (-C1) * s3;
+      dy = (-C1) * s1;
+      dz = C1 * s2;
+    }
+    written = 4;
+    if (D > 1) {
+      const float C20 = 1.0925484305920792f, C21 = -1.0925484305920792f, C22 = 0.31539156525252005f,
+                  C23 = -1.0925484305920792f, C24 = 0.5462742152960396f;
+      const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+      {
+        const float4 v3 = row4[3], v4 = row4[4], v5 = row4[5], v6 = row4[6];   // floats 12..27: SH(4) = 12..14 ... SH(8) = 24..26
+        const f3 s4 = mk(v3.x, v3.y, v3.z), s5 = mk(v3.w, v4.x, v4.y), s6 = mk(v4.z, v4.w, v5.x), s7 = mk(v5.y, v5.z, v5.w),
+                 s8 = mk(v6.x, v6.y, v6.z);
+        dx = dx + (C20 * y) * s4 + (C22 * 2.f * -x) * s6 + (C23 * z) * s7 + (C24 * 2.f * x) * s8;
+        dy = dy + (C20 * x) * s4 + (C21 * z) * s5 + (C22 * 2.f * -y) * s6 + (C24 * 2.f * -y) * s8;
+        dz = dz + (C21 * y) * s5 + (C22 * 2.f * 2.f * z) * s6 + (C23 * x) * s7;
+      }
+      written = 9;
+      if (D > 2) {
+        const float C30 = -0.5900435899266435f, C31 = 2.890611442640554f, C32 = -0.4570457994644658f,
+                    C33 = 0.3731763325901154f, C34 = -0.4570457994644658f, C35 = 1.445305721320277f,
+                    C36 = -0.5900435899266435f;
+        const float4 v6 = row4[6], v7 = row4[7], v8 = row4[8], v9 = row4[9], v10 = row4[10], v11 = row4[11];  // floats 24..47
+        const f3 s9 = mk(v6.w, v7.x, v7.y), s10 = mk(v7.z, v7.w, v8.x), s11 = mk(v8.y, v8.z, v8.w), s12 = mk(v9.x, v9.y, v9.z),
+                 s13 = mk(v9.w, v10.x, v10.y), s14 = mk(v10.z, v10.w, v11.x), s15 = mk(v11.y, v11.z, v11.w);
+        dx = dx + ((C30 * 3.f * 2.f * xy) * s9 + (C31 * yz) * s10 + (C32 * -2.f * xy) * s11 +
+                   (C33 * -3.f * 2.f * xz) * s12 + (C34 * (-3.f * xx + 4.f * zz - yy)) * s13 +
+                   (C35 * 2.f * xz) * s14 + (C36 * 3.f * (xx - yy)) * s15);
+        dy = dy + ((C30 * 3.f * (xx - yy)) * s9 + (C31 * xz) * s10 + (C32 * (-3.f * yy + 4.f * zz - xx)) * s11 +
+                   (C33 * -3.f * 2.f * yz) * s12 + (C34 * -2.f * xy) * s13 + (C35 * -2.f * yz) * s14 +
+                   (C36 * -3.f * 2.f * xy) * s15);
+        dz = dz + ((C31 * xy) * s10 + (C32 * 4.f * 2.f * yz) * s11 + (C33 * 3.f * (2.f * zz - xx - yy)) * s12 +
+                   (C34 * 4.f * 2.f * xz) * s13 + (C35 * (xx - yy)) * s14);
+        written = 16;
+      }
+    }
+  }
+  // every coefficient has been read: the row becomes dL_dsh = coef (x) dL_dRGB (zeros beyond degree D)
+  {
+    float coef[16];
+    sh_coefficients(D, x, y, z, coef);
+    const float g[3] = {dL_dRGB.x, dL_dRGB.y, dL_dRGB.z};
+    const int n4 = 3 * M / 4;
+#pragma unroll
+    for (int j = 0; j < 12; j++) {
+      if (j < n4) {
+        float o[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          const int idx = 4 * j + e, k = idx / 3, c = idx % 3;
+          o[e] = k < written ? coef[k] * g[c] : 0.0f;
+        }
+        row4[j] = make_float4(o[0], o[1], o[2], o[3]);
+      }
+    }
+  }
+  const f3 dL_ddir = mk(dot(dx, dL_dRGB), dot(dy, dL_dRGB), dot(dz, dL_dRGB));
+  // dnormvdv (auxiliary.h:128-138)
+  const f3 v = dir_orig, dv = dL_ddir;
+  const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+  const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+  dL_dmean_add.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+  dL_dmean_add.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+  dL_dmean_add.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+}
+
 constexpr int PBWD_THREADS = 128;
 
 // SH rows travel through shared memory so that the 12*M-byte-per-surfel streams (shs in, dL_dsh out)
@@ -205,9 +284,12 @@ __device__ __forceinline__ void sh_rows_store(const float* wsm, float* __restric
 #ifndef GSM_PBWD_MIN_CTAS
 #define GSM_PBWD_MIN_CTAS 6
 #endif
-template <bool RAW>  // the raw-parameter entry (activation chain, split SH storage); the standard entry compiles without it
+// RAW: the raw-parameter entry (activation chain, split SH storage); the standard entry compiles without it.
+// BULK: SH rows in (and dL_dsh rows out) by per-row TMA bulk copies (standard entry, M % 4 == 0, aligned tensors): one
+// instruction per row each way instead of the cooperative staging loops, the load in flight under the geometry math.
+template <bool RAW, bool BULK>
 __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bwd_kernel(const BwdPreprocessParams p) {
-  extern __shared__ float sh_smem[];
+  extern __shared__ __align__(16) float sh_smem[];
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int warp_first = idx - lane;
@@ -218,12 +300,22 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
   const bool acc = p.accumulate != 0;  // outputs += (view-parallel accumulation over local views)
   const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
   const int rows = min(32, p.P - warp_first);
-  float* wsm = sh_smem + (size_t)warp * 32 * (3 * p.M + 1);
-  float* my_row = wsm + lane * (3 * p.M + 1);
+  const int row_stride = BULK ? SH_BULK_STRIDE : 3 * p.M + 1;
+  float* wsm = sh_smem + (size_t)warp * 32 * row_stride;
+  float* my_row = wsm + lane * row_stride;
   // factored mode (view-parallel): dL_dRGB is written instead of the 3M-float dL_dsh row, which the
   // receiver rebuilds as basis(dir) (x) dL_dRGB (sh_grad_expand_kernel); the SH term of dL_dmean3D stays here
   const bool factored = p.dL_drgb != nullptr || p.n_rgb_peers > 0;
   const bool has_sh = p.shs != nullptr && (p.dL_dsh != nullptr || factored);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sh_smem + (size_t)(PBWD_THREADS / 32) * 32 * SH_BULK_STRIDE) + warp;
+  float4* zero4 = reinterpret_cast<float4*>(sh_smem + (size_t)(PBWD_THREADS / 32) * 32 * SH_BULK_STRIDE + 2 * (PBWD_THREADS / 32)) + warp * 12;
+  if (BULK) {   // (launched only with has_sh)
+    if (lane == 0) mbar_init(bar, 1);
+    if (lane < 12) zero4[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncwarp();
+    if (visible) bulk_load(my_row, p.shs + i * (size_t)(3 * p.M), (uint32_t)(12 * p.M), bar);
+    if (lane == 0) mbar_expect_tx(bar, (uint32_t)(12 * p.M) * (uint32_t)__popc(vis_mask));
+  }
   // the thread's own operands are requested BEFORE the cooperative row staging, so both streams are in flight together
   float4 g0 = make_float4(0, 0, 0, 0), g1 = g0, g2 = g0, g3 = g0, g4 = g0;
   f3 pos = mk(0, 0, 0);
@@ -232,7 +324,7 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
     g0 = __ldg(g + 0); g1 = __ldg(g + 1); g2 = __ldg(g + 2); g3 = __ldg(g + 3); g4 = __ldg(g + 4);
     pos = mk(__ldg(p.means3D + 3 * i), __ldg(p.means3D + 3 * i + 1), __ldg(p.means3D + 3 * i + 2));
   }
-  if (has_sh) {
+  if (has_sh && !BULK) {
     if (!RAW || p.shs_rest == nullptr) {
       sh_rows_load(wsm, p.shs + (size_t)warp_first * p.M * 3, 3 * p.M, 3 * p.M + 1, 0, rows, vis_mask, lane);
     } else {
@@ -395,7 +487,12 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
       if (clamp_bits & 4) dRGB.z = 0.f;
       const f3 dir_orig = mk(pos.x - p.campos[0], pos.y - p.campos[1], pos.z - p.campos[2]);
       f3 add;
-      sh_backward(p.D, p.M, my_row, dir_orig, dRGB, add);
+      if (BULK) {
+        mbar_wait(bar, 0);
+        sh_backward_row4(p.D, p.M, reinterpret_cast<float4*>(my_row), dir_orig, dRGB, add);
+      } else {
+        sh_backward(p.D, p.M, my_row, dir_orig, dRGB, add);
+      }
       dmean3D = dmean3D + add;
       drgb_masked = dRGB;
     }
@@ -427,6 +524,20 @@ __global__ void __launch_bounds__(PBWD_THREADS, GSM_PBWD_MIN_CTAS) preprocess_bw
     }
   } else if (has_sh && factored) {
     if (valid) store3(p.dL_drgb + 3 * i, drgb_masked);  // per view: never accumulated
+  } else if (has_sh && BULK) {
+    // each lane hands its own row (dL_dsh, or the zero row for a culled surfel) to the copy engine
+    fence_proxy_async();
+    __syncwarp();
+    if (valid) {
+      float* dst = p.dL_dsh + i * (size_t)(3 * p.M);
+      if (visible) {
+        if (acc) bulk_reduce_add_f32(dst, my_row, (uint32_t)(12 * p.M));
+        else bulk_store(dst, my_row, (uint32_t)(12 * p.M));
+      } else if (!acc) {
+        bulk_store(dst, zero4, (uint32_t)(12 * p.M));
+      }
+    }
+    bulk_commit_and_wait_read();
   } else if (has_sh) {
     __syncwarp();
     if (!RAW || p.dL_dsh_rest == nullptr) {
@@ -598,14 +709,23 @@ void launch_sh_grad_expand(int P, int D, int M, int n_views, const float* means3
 
 void launch_preprocess_bwd(const BwdPreprocessParams& p, cudaStream_t stream) {
   if (p.P <= 0) return;
-  const size_t smem = (size_t)(PBWD_THREADS / 32) * 32 * (3 * p.M + 1) * sizeof(float);
+  const bool raw = p.raw || p.shs_rest != nullptr;
+  const bool factored = p.dL_drgb != nullptr || p.n_rgb_peers > 0;
+  const bool has_sh = p.shs != nullptr && (p.dL_dsh != nullptr || factored);
+  // per-row TMA bulk copies: the concatenated [P,M,3] tensors with 16-byte rows at 16-byte addresses
+  const bool bulk = !raw && has_sh && p.M > 0 && p.M <= 16 && p.M % 4 == 0 && (reinterpret_cast<size_t>(p.shs) & 15) == 0 &&
+                    (p.dL_dsh == nullptr || (reinterpret_cast<size_t>(p.dL_dsh) & 15) == 0) && getenv("GSM_NO_BULK") == nullptr;
+  const size_t smem = bulk ? (size_t)(PBWD_THREADS / 32) * 32 * SH_BULK_STRIDE * sizeof(float) + (PBWD_THREADS / 32) * (8 + 192)
+                           : (size_t)(PBWD_THREADS / 32) * 32 * (3 * p.M + 1) * sizeof(float);
   static PerDeviceLevel configured;
   if (smem > 48 * 1024) configured.ensure(smem, [&] {
-    cudaFuncSetAttribute(preprocess_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(preprocess_bwd_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(preprocess_bwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   });
-  if (p.raw || p.shs_rest != nullptr) preprocess_bwd_kernel<true><<<(p.P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(p);
-  else preprocess_bwd_kernel<false><<<(p.P + PBWD_THREADS - 1) / PBWD_THREADS, PBWD_THREADS, smem, stream>>>(p);
+  const int grid = (p.P + PBWD_THREADS - 1) / PBWD_THREADS;
+  if (bulk) preprocess_bwd_kernel<false, true><<<grid, PBWD_THREADS, smem, stream>>>(p);
+  else if (raw) preprocess_bwd_kernel<true, false><<<grid, PBWD_THREADS, smem, stream>>>(p);
+  else preprocess_bwd_kernel<false, false><<<grid, PBWD_THREADS, smem, stream>>>(p);
 }
 
 }  // namespace gsm

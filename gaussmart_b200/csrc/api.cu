@@ -86,7 +86,6 @@ GeometryLayout geometry_layout(int P) {
   L.cull = take(n * 16);
   L.clamp = take(n);
   L.rects = take(n * 16);
-  L.ranks = take(n * 16);
   L.flags = take(16);
   L.total = off + 128;
   return L;
@@ -101,8 +100,8 @@ ImageLayout image_layout(int width, int height) {
   L.final_T = take(N * 3 * 4);
   L.n_contrib = take(N * 2 * 4);
   L.ranges = take(Nt * 8);
-  L.tile_count = take(Nt * 4 * TILE_CTRS);
-  L.tile_cursor = take(Nt * 4 * TILE_CTRS);
+  L.tile_count = take(Nt * 4 * TILE_SUBS);
+  L.tile_cursor = take(Nt * 4 * TILE_SUBS);
   L.num_rendered = take(16);
   L.total = off + 128;
   return L;
@@ -256,7 +255,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
   int R = 0;
   if (P > 0) {
     GSM_CUDA(cudaMemsetAsync(flags, 0, 16, stream));
-    GSM_CUDA(cudaMemsetAsync(tile_count, 0, sizeof(uint32_t) * (size_t)num_tiles * TILE_CTRS, stream));
+    GSM_CUDA(cudaMemsetAsync(tile_count, 0, sizeof(uint32_t) * (size_t)num_tiles * TILE_SUBS, stream));
     FwdPreprocessParams pp{};
     pp.P = P; pp.D = a->D; pp.M = a->M; pp.W = W; pp.H = H; pp.grid_x = grid_x; pp.grid_y = grid_y;
     pp.scale_modifier = a->scale_modifier; pp.prefiltered = a->prefiltered;
@@ -264,7 +263,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     pp.shs = a->shs; pp.transMat_precomp = a->transMat_precomp; pp.colors_precomp = a->colors_precomp;
     pp.shs_rest = a->shs ? a->shs_rest : nullptr; pp.raw = a->raw_params ? 1 : 0;
     pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
-    pp.radii = a->radii; pp.records = records; pp.bbox = (short4*)(geom + G.bbox); pp.cull = (float4*)(geom + G.cull); pp.clamp = (uint8_t*)(geom + G.clamp); pp.rects = (uint4*)(geom + G.rects); pp.ranks = (uint4*)(geom + G.ranks); pp.tile_count = tile_count; pp.flags = flags;
+    pp.radii = a->radii; pp.records = records; pp.bbox = (short4*)(geom + G.bbox); pp.cull = (float4*)(geom + G.cull); pp.clamp = (uint8_t*)(geom + G.clamp); pp.rects = (uint4*)(geom + G.rects); pp.tile_count = tile_count; pp.flags = flags;
     { StageMark m(GSM_STAGE_PREPROCESS_FWD, stream); launch_preprocess_fwd(pp, stream); }
     GSM_STAGE("forward preprocess");
     {
@@ -317,7 +316,7 @@ extern "C" int gsm_forward(const gsm_forward_args* a, void* stream_) {
     const int packed = (P <= (1 << 24) && !(a->debug & 8)) ? 1 : 0;
     {
       StageMark m(GSM_STAGE_DUPLICATE, stream);
-      launch_scatter(P, (const uint4*)(geom + G.rects), (const uint4*)(geom + G.ranks), a->radii, tile_cursor, pairs, grid_x, (const short4*)(geom + G.bbox),
+      launch_scatter(P, (const uint4*)(geom + G.rects), a->radii, tile_cursor, pairs, grid_x, (const short4*)(geom + G.bbox),
                      (const float4*)(geom + G.cull), (a->debug & 2) ? 1 : 0, packed, status_dev, stream);
     }
     GSM_STAGE("scatter");

@@ -33,40 +33,32 @@ namespace gsm {
 // ---------------------------------------------------------------------------------------------
 constexpr int TSCAN_THREADS = 1024;
 
-// tile_count / tile_cursor are [Nt][TILE_CTRS]: two counter sets (common.cuh) of TILE_SUBS sub-counters each,
-// selected by the surfel index, because same-address atomics WITH return serialise in L2 (~27 cycles each): one
-// counter per tile would make the hottest tile the critical path.  A tile's segment holds its sub-segments in
-// counter order: set A (ranked instances) first, then set B (appended through the cursors).
+// tile_count / tile_cursor are [Nt][TILE_SUBS]: a tile's instances are counted and appended through
+// TILE_SUBS sub-cursors selected by the surfel index, because same-address atomics WITH return
+// serialise in L2 (~27 cycles each): one cursor per tile makes the hottest tile the critical path.
 __global__ void __launch_bounds__(TSCAN_THREADS)
 tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_cursor,
                  uint2* __restrict__ ranges, int num_tiles, unsigned long long capacity,
                  const uint32_t* __restrict__ flags, ForwardStatus* __restrict__ status) {
-  // one CTA walks the tiles in chunks of TSCAN_THREADS, one tile (TILE_CTRS counters = 64 B) per thread and chunk; the
-  // next chunk's counters are requested before the current chunk is scanned
+  // one CTA walks the tiles in chunks of TSCAN_THREADS, one tile (TILE_SUBS counters = 32 B) per thread and chunk, so
+  // every access is coalesced; the next chunk's counters are requested before the current chunk is scanned
   __shared__ unsigned long long warp_sums[2][TSCAN_THREADS / 32];
-  static_assert(TILE_CTRS == 16, "a tile's counters are read as four uint4");
+  static_assert(TILE_SUBS == 8, "a tile's counters are read as two uint4");
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const uint4* cnt4 = reinterpret_cast<const uint4*>(tile_count);
   uint4* cur4 = reinterpret_cast<uint4*>(tile_cursor);
   const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
   unsigned long long carry = 0;
-  uint4 n[4] = {zero, zero, zero, zero};
-  if (t < num_tiles) {
-#pragma unroll
-    for (int q = 0; q < 4; q++) n[q] = __ldg(cnt4 + 4 * (size_t)t + q);
-  }
+  uint4 n0 = zero, n1 = zero;
+  if (t < num_tiles) { n0 = __ldg(cnt4 + 2 * (size_t)t); n1 = __ldg(cnt4 + 2 * (size_t)t + 1); }
   int buf = 0;
   for (int base = 0; base < num_tiles; base += TSCAN_THREADS, buf ^= 1) {
     const int i = base + t;
-    uint4 c[4];
-#pragma unroll
-    for (int q = 0; q < 4; q++) c[q] = n[q];
+    const uint4 c0 = n0, c1 = n1;
     const int nxt = i + TSCAN_THREADS;
-#pragma unroll
-    for (int q = 0; q < 4; q++) n[q] = (nxt < num_tiles) ? __ldg(cnt4 + 4 * (size_t)nxt + q) : zero;
-    unsigned long long local = 0;
-#pragma unroll
-    for (int q = 0; q < 4; q++) local += (unsigned long long)c[q].x + c[q].y + c[q].z + c[q].w;
+    n0 = zero; n1 = zero;
+    if (nxt < num_tiles) { n0 = __ldg(cnt4 + 2 * (size_t)nxt); n1 = __ldg(cnt4 + 2 * (size_t)nxt + 1); }
+    const unsigned long long local = (unsigned long long)c0.x + c0.y + c0.z + c0.w + c1.x + c1.y + c1.z + c1.w;
     unsigned long long inc = local;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -84,13 +76,13 @@ tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__
     if (i < num_tiles) {
       unsigned long long run = carry + warp_off + inc - local;
       const unsigned long long first = run;
-#pragma unroll
-      for (int q = 0; q < 4; q++) {
-        uint4 o;  // absolute slot of each sub-segment's first / next pair
-        o.x = (uint32_t)run; run += c[q].x; o.y = (uint32_t)run; run += c[q].y;
-        o.z = (uint32_t)run; run += c[q].z; o.w = (uint32_t)run; run += c[q].w;
-        cur4[4 * (size_t)i + q] = o;
-      }
+      uint4 o;  // absolute slot of each sub-segment's next pair
+      o.x = (uint32_t)run; run += c0.x; o.y = (uint32_t)run; run += c0.y;
+      o.z = (uint32_t)run; run += c0.z; o.w = (uint32_t)run; run += c0.w;
+      cur4[2 * (size_t)i] = o;
+      o.x = (uint32_t)run; run += c1.x; o.y = (uint32_t)run; run += c1.y;
+      o.z = (uint32_t)run; run += c1.z; o.w = (uint32_t)run; run += c1.w;
+      cur4[2 * (size_t)i + 1] = o;
       ranges[i] = run > first ? make_uint2((uint32_t)first, (uint32_t)run) : make_uint2(0u, 0u);
     }
     carry += total;
@@ -163,7 +155,7 @@ __device__ __forceinline__ uint32_t instance_block_mask(const short4 bx, const f
 // epilogue then gathers box and slabs itself, as in round 1).
 template <bool PACKED>
 __global__ void __launch_bounds__(256)
-scatter_kernel(int P, const uint4* __restrict__ rects, const uint4* __restrict__ ranks, const int* __restrict__ radii,
+scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ radii,
                uint32_t* __restrict__ tile_cursor, uint2* __restrict__ pairs, int grid_x,
                const short4* __restrict__ bbox, const float4* __restrict__ cull, int no_cull,
                const ForwardStatus* __restrict__ status) {
@@ -191,25 +183,7 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const uint4* __restrict__
     return surfel | (m << ID_BITS);
   };
   const int BIG = 16;
-  if (n > 0 && n <= RANKED_TILES) {
-    // the forward preprocess kept this surfel's rank in each of its (tile, sub-counter) segments: slot = scanned base +
-    // rank, no atomic (the set-A entries of tile_cursor are never modified)
-    const uint4 rk4 = __ldg(ranks + idx);
-    const uint32_t rk[RANKED_TILES] = {rk4.x, rk4.y, rk4.z, rk4.w};
-    uint32_t slot[RANKED_TILES], val[RANKED_TILES];
-#pragma unroll
-    for (int t = 0; t < RANKED_TILES; t++) {
-      if (t < n) {
-        const uint32_t ty = (uint32_t)(miny + t / w), tx = (uint32_t)(minx + t % w);
-        const uint32_t tile = ty * (uint32_t)grid_x + tx;
-        slot[t] = __ldg(tile_cursor + tile * TILE_CTRS + ((uint32_t)idx & (TILE_SUBS - 1))) + rk[t];
-        val[t] = value_of((uint32_t)idx, bx, dg, tx, ty);
-      }
-    }
-#pragma unroll
-    for (int t = 0; t < RANKED_TILES; t++)
-      if (t < n) pairs[slot[t]] = make_uint2(depth_bits, val[t]);
-  } else if (n > 0 && n <= BIG) {
+  if (n > 0 && n <= BIG) {
     // the cursor atomics return a value: four are issued before the first result is consumed, instead of one
     // L2 round trip per instance in sequence
     for (int t0 = 0; t0 < n; t0 += 4) {
@@ -220,7 +194,7 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const uint4* __restrict__
         if (t < n) {
           const uint32_t ty = (uint32_t)(miny + t / w), tx = (uint32_t)(minx + t % w);
           const uint32_t tile = ty * (uint32_t)grid_x + tx;
-          slot[u] = atomicAdd(tile_cursor + tile * TILE_CTRS + TILE_SUBS + ((uint32_t)idx & (TILE_SUBS - 1)), 1u);
+          slot[u] = atomicAdd(tile_cursor + tile * TILE_SUBS + ((uint32_t)idx & (TILE_SUBS - 1)), 1u);
           val[u] = value_of((uint32_t)idx, bx, dg, tx, ty);
         }
       }
@@ -245,20 +219,20 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const uint4* __restrict__
     for (int t = lane; t < bn; t += 32) {
       const uint32_t ty = (uint32_t)(bminy + t / bw), tx = (uint32_t)(bminx + t % bw);
       const uint32_t tile = ty * (uint32_t)grid_x + tx;
-      const uint32_t slot = atomicAdd(tile_cursor + tile * TILE_CTRS + TILE_SUBS + (bidx & (TILE_SUBS - 1)), 1u);
+      const uint32_t slot = atomicAdd(tile_cursor + tile * TILE_SUBS + (bidx & (TILE_SUBS - 1)), 1u);
       pairs[slot] = make_uint2(bdepth, value_of(bidx, bbx, bdg, tx, ty));
     }
   }
 }
 
-void launch_scatter(int P, const uint4* rects, const uint4* ranks, const int* radii, uint32_t* tile_cursor, uint2* pairs,
+void launch_scatter(int P, const uint4* rects, const int* radii, uint32_t* tile_cursor, uint2* pairs,
                     int grid_x, const short4* bbox, const float4* cull, int no_cull, int packed,
                     const ForwardStatus* status, cudaStream_t stream) {
   if (P <= 0) return;
   if (packed)
-    scatter_kernel<true><<<(P + 255) / 256, 256, 0, stream>>>(P, rects, ranks, radii, tile_cursor, pairs, grid_x, bbox, cull, no_cull, status);
+    scatter_kernel<true><<<(P + 255) / 256, 256, 0, stream>>>(P, rects, radii, tile_cursor, pairs, grid_x, bbox, cull, no_cull, status);
   else
-    scatter_kernel<false><<<(P + 255) / 256, 256, 0, stream>>>(P, rects, ranks, radii, tile_cursor, pairs, grid_x, bbox, cull, no_cull, status);
+    scatter_kernel<false><<<(P + 255) / 256, 256, 0, stream>>>(P, rects, radii, tile_cursor, pairs, grid_x, bbox, cull, no_cull, status);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -37,11 +37,6 @@ __host__ __device__ inline uint32_t block_mask(int c0, int c1, int r0, int r1) {
 }
 // Sub-cursors per tile for counting / appending instances (binning.cu), power of two.
 constexpr int TILE_SUBS = 8;
-// Two counter sets per tile: set A counts the instances of surfels that touch at most RANKED_TILES tiles -- the forward
-// preprocess takes the RETURNING atomic there and keeps the rank, so the scatter places those instances (85 % at C4)
-// with plain loads of the scanned bases --, set B the instances of larger surfels, appended through atomic cursors.
-constexpr int TILE_CTRS = 2 * TILE_SUBS;
-constexpr int RANKED_TILES = 4;
 
 // Compile-time constants of the reference (auxiliary.h:37-40).
 constexpr float NEAR_N = 0.2f;
@@ -95,7 +90,6 @@ struct GeometryLayout {
   size_t cull;           // float4[P]  diagonal slabs of the contribution region ("cull record")
   size_t clamp;          // u8[P]      bit c set when colour channel c was clamped at 0 (read by the backward preprocess)
   size_t rects;          // uint4[P]   (minx | miny<<16, maxx | maxy<<16, depth bits, 0): tile rect for the scatter
-  size_t ranks;          // uint4[P]   rank of the surfel's t-th instance inside its (tile, sub-counter) segment (<= 4 tiles)
   size_t flags;          // u32[4]: [0] prefiltered-violation flag
   size_t total;
 };
@@ -113,8 +107,8 @@ struct ImageLayout {
   size_t final_T;    // f32[3*N]  (T, M1, M2)
   size_t n_contrib;  // u32[2*N]  (last contributor, median contributor)
   size_t ranges;     // uint2[Nt]
-  size_t tile_count;   // u32[Nt][TILE_CTRS]  instances per tile, counter set and sub-counter (counted by the forward preprocess)
-  size_t tile_cursor;  // u32[Nt][TILE_CTRS]  scanned bases (set A) / append cursors (set B) of the scatter
+  size_t tile_count;   // u32[Nt][TILE_SUBS]  instances per tile and sub-cursor (counted by the forward preprocess)
+  size_t tile_cursor;  // u32[Nt][TILE_SUBS]  append cursors of the scatter
   size_t num_rendered; // ForwardStatus (R first)
   size_t total;
 };
@@ -267,8 +261,7 @@ struct FwdPreprocessParams {
   float4* cull;
   uint8_t* clamp;
   uint4* rects;
-  uint4* ranks;
-  uint32_t* tile_count;  // u32[Nt][TILE_CTRS], zeroed by the caller: += 1 per (surfel, tile) instance
+  uint32_t* tile_count;  // u32[Nt], zeroed by the caller: += 1 per (surfel, tile) instance
   uint32_t* flags;
 };
 void launch_preprocess_fwd(const FwdPreprocessParams& p, cudaStream_t stream);
@@ -277,7 +270,7 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
 
 void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* ranges, int num_tiles,
                       unsigned long long capacity, const uint32_t* flags, ForwardStatus* status, cudaStream_t stream);
-void launch_scatter(int P, const uint4* rects, const uint4* ranks, const int* radii, uint32_t* tile_cursor, uint2* pairs,
+void launch_scatter(int P, const uint4* rects, const int* radii, uint32_t* tile_cursor, uint2* pairs,
                     int grid_x, const short4* bbox, const float4* cull, int no_cull, int packed,
                     const ForwardStatus* status, cudaStream_t stream);
 // packed: the scatter ran with P <= 2^24 and left the block masks in the top byte of the pairs' values

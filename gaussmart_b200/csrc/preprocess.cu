@@ -260,7 +260,6 @@ __global__ void __launch_bounds__(PFWD_THREADS, GSM_PFWD_MIN_CTAS) preprocess_fw
   float Tu0 = 0, Tu1 = 0, Tu2 = 0, Tv0 = 0, Tv1 = 0, Tv2 = 0, Tw0 = 0, Tw1 = 0, Tw2 = 0;
   float nx = 0, ny = 0, nz = 0, cx = 0, cy = 0, opac = 0;
   uint32_t rect_min = 0, rect_max = 0;
-  uint4 ranks_out = make_uint4(0u, 0u, 0u, 0u);
   short4 box = make_short4(-32768, -32768, 32767, 32767);
   float4 diag = make_float4(-INFINITY, INFINITY, -INFINITY, INFINITY);  // unbounded diagonal slabs
 
@@ -360,22 +359,10 @@ __global__ void __launch_bounds__(PFWD_THREADS, GSM_PFWD_MIN_CTAS) preprocess_fw
     if (area == 0) break;
     rect_min = (uint32_t)minx | ((uint32_t)miny << 16);
     rect_max = (uint32_t)maxx | ((uint32_t)maxy << 16);
-    // per-tile instance counts (binning.cu step 1).  Up to RANKED_TILES tiles: the atomic's return value is the
-    // instance's rank inside its (tile, sub-counter) segment -- kept for the scatter, which then needs no atomic; the
-    // four round trips to L2 run under the box math and the SH evaluation below.  More tiles: one red per instance.
-    if (area <= (uint32_t)RANKED_TILES) {
-      const int w = maxx - minx;
-      uint32_t rk[RANKED_TILES] = {0u, 0u, 0u, 0u};
-#pragma unroll
-      for (int t = 0; t < RANKED_TILES; t++)
-        if (t < (int)area)
-          rk[t] = atomicAdd(p.tile_count + ((miny + t / w) * p.grid_x + minx + t % w) * TILE_CTRS + (idx & (TILE_SUBS - 1)), 1u);
-      ranks_out = make_uint4(rk[0], rk[1], rk[2], rk[3]);
-    } else {
-      for (int ty = miny; ty < maxy; ty++)
-        for (int tx = minx; tx < maxx; tx++)
-          atomicAdd(p.tile_count + (ty * p.grid_x + tx) * TILE_CTRS + TILE_SUBS + (idx & (TILE_SUBS - 1)), 1u);
-    }
+    // per-tile instance counts (binning.cu step 1): one red.global.add per (surfel, tile) instance
+    for (int ty = miny; ty < maxy; ty++)
+      for (int tx = minx; tx < maxx; tx++)
+        atomicAdd(p.tile_count + (ty * p.grid_x + tx) * TILE_SUBS + (idx & (TILE_SUBS - 1)), 1u);
 
     if (BULK)   // this surfel is visible from here on: its SH row is requested now and lands under the box math below
       bulk_load(sh_smem + ((size_t)warp * 32 + lane) * SH_BULK_STRIDE, p.shs + (size_t)idx * p.M * 3, (uint32_t)(12 * p.M), bar);
@@ -480,7 +467,6 @@ __global__ void __launch_bounds__(PFWD_THREADS, GSM_PFWD_MIN_CTAS) preprocess_fw
     p.clamp[idx] = (uint8_t)clamp_bits;
     p.cull[idx] = diag;
     p.rects[idx] = make_uint4(rect_min, rect_max, __float_as_uint(vz), 0u);
-    p.ranks[idx] = ranks_out;
     float4* rec = p.records + (size_t)idx * REC_F4;
     rec[0] = make_float4(Tu0, Tu1, Tu2, cx);
     rec[1] = make_float4(Tv0, Tv1, Tv2, cy);

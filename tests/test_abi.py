@@ -56,7 +56,7 @@ def test_workspace_sizes(P):
     lib = _lib.load()
     g = lib.gsm_geometry_bytes(P)
     assert g >= P * _lib.GSM_SURFEL_RECORD_BYTES + 8 * P
-    assert g < P * 144 + (1 << 20)   # record 80 + box 8 + slabs 16 + clamp 1 + tile rect 16 + instance ranks 16
+    assert g < P * 128 + (1 << 20)
     assert lib.gsm_grad_workspace_bytes(P) >= P * _lib.GSM_GRAD_RECORD_FLOATS * 4
     assert lib.gsm_knn_workspace_bytes(P) > 0
 

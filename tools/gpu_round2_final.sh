@@ -4,8 +4,10 @@
 TAG=${1:-r02_final}
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.max.sm,clocks.sm,power.limit --format=csv > gpurun_out/${TAG}_smi.txt 2>&1
+if [ "$2" != "skip-tests" ]; then
 timeout 1500 python -m pytest tests -m gpu -q -p no:cacheprovider > gpurun_out/${TAG}_pytest.log 2>&1
 echo "pytest exit $?: $(tail -1 gpurun_out/${TAG}_pytest.log)"
+fi
 timeout 900 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err
 echo "ref bench exit $?"
 timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err
@@ -24,4 +26,7 @@ timeout 900 ncu --set full --clock-control none --import-source on \
 timeout 900 ncu --set full --clock-control none \
   -k regex:'knn_|sort32_|morton|minmax|tree|sh_grad_expand|densify_|tile_scan' --launch-count 40 -o gpurun_out/${TAG}_aux -f \
   python tools/aux_kernels.py > gpurun_out/${TAG}_ncu_aux.log 2>&1
+# gpurun brings back at most 64 MiB: the auxiliary capture is summarised on the box and its report dropped
+python tools/ncu_summary.py gpurun_out/${TAG}_aux.ncu-rep gpurun_out/${TAG}_aux_ncu.txt "ncu --set full --clock-control none, python tools/aux_kernels.py (distCUDA2 on 5 M points, SH expand 8 views, 4K tile scan, densify_and_prune 2 M): per launch" > /dev/null 2>&1
+rm -f gpurun_out/${TAG}_aux.ncu-rep
 ls -la gpurun_out/ | grep ${TAG}

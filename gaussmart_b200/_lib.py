@@ -32,6 +32,7 @@ EXPORTS = [
     "gsm_status_create", "gsm_status_destroy", "gsm_status_query", "gsm_status_wait", "gsm_fp32_peak_probe",
     "gsm_densify_workspace_bytes", "gsm_densify_plan", "gsm_densify_apply",
     "gsm_sh_grad_expand_strided", "gsm_peer_allreduce", "gsm_peer_allreduce_multimem", "gsm_peer_staging_floats", "gsm_peer_scatter", "gsm_peer_sum_broadcast",
+    "gsm_photometric_loss_static_max_elements", "gsm_photometric_loss_static",
 ]
 
 
@@ -156,6 +157,11 @@ def load():
     lib.gsm_photometric_loss.restype = c_int
     lib.gsm_photometric_loss.argtypes = [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_void_p, c_void_p,
                                          c_void_p, c_size_t, c_void_p]
+    lib.gsm_photometric_loss_static_max_elements.restype = c_size_t
+    lib.gsm_photometric_loss_static_max_elements.argtypes = []
+    lib.gsm_photometric_loss_static.restype = c_int
+    lib.gsm_photometric_loss_static.argtypes = [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_void_p, c_void_p,
+                                                c_void_p]
     lib.gsm_surface_regularizer_workspace_bytes.restype = c_size_t
     lib.gsm_surface_regularizer_workspace_bytes.argtypes = [c_int, c_int]
     lib.gsm_surface_regularizer.restype = c_int

@@ -243,3 +243,75 @@ extern "C" int gsm_photometric_loss(const float* image, const float* gt, int C, 
   GSM_CUDA(cudaGetLastError());
   return GSM_OK;
 }
+
+// ---- allocation-free variant ------------------------------------------------------------------------------------
+// gsm_photometric_loss_static: the same two kernels with their scratch (double[2] sums + the three partial maps) in a
+// file-scope device array instead of a caller-owned workspace, for callers that cannot allocate (CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Limit: C*H*W <= GSM_PHOTOMETRIC_LOSS_STATIC_MAX_ELEMENTS (4 Mi pixel-channels: 48 MiB + 256 B
+// of device memory held by every GPU that loads this module, until exit).  The array is shared by every call on a
+// device and keeps the previous call's contents: the sums are cleared at the start of each call (stream-ordered); the
+// maps are fully overwritten by kernel 1 before kernel 2 reads them.  Calls that overlap on one GPU (two streams, two
+// host threads) RACE on it -- callers serialise them.
+namespace gsm {
+
+constexpr size_t LOSS_STATIC_MAX = (size_t)GSM_PHOTOMETRIC_LOSS_STATIC_MAX_ELEMENTS;
+constexpr size_t LOSS_STATIC_BYTES = 256 + 3 * LOSS_STATIC_MAX * sizeof(float);
+static __device__ __align__(256) unsigned char g_loss_static_scratch[LOSS_STATIC_BYTES];
+
+// In host code `g_loss_static_scratch` is only a handle of the symbol, not a device address: the address of each
+// device's copy is asked for once per device, with that device current.
+constexpr int LOSS_STATIC_MAX_DEVICES = 64;
+static std::mutex g_loss_static_mu;
+static unsigned char* g_loss_static_ptr[LOSS_STATIC_MAX_DEVICES] = {};
+
+static int loss_static_setup(unsigned char** out) {
+  int dev = -1;
+  GSM_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= LOSS_STATIC_MAX_DEVICES) {
+    set_error("gsm_photometric_loss_static: device ordinal %d outside [0, %d)", dev, LOSS_STATIC_MAX_DEVICES);
+    return GSM_ERR_INVALID_ARGUMENT;
+  }
+  std::lock_guard<std::mutex> lk(g_loss_static_mu);
+  if (g_loss_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    GSM_CUDA(cudaGetSymbolAddress(&p, g_loss_static_scratch));  // current device's copy of the array
+    if (p == nullptr || ((uintptr_t)p & 255) != 0) { set_error("gsm_photometric_loss_static: bad scratch address %p", p); return (int)cudaErrorInvalidSymbol; }
+    upload_window();                                            // c_gauss is a per-device symbol as well
+    GSM_CUDA(cudaGetLastError());
+    g_loss_static_ptr[dev] = (unsigned char*)p;
+  }
+  *out = g_loss_static_ptr[dev];
+  return GSM_OK;
+}
+
+}  // namespace gsm
+
+extern "C" size_t gsm_photometric_loss_static_max_elements(void) { return LOSS_STATIC_MAX; }
+
+extern "C" int gsm_photometric_loss_static(const float* image, const float* gt, int C, int H, int W, float lambda_dssim,
+                                           float grad_scale, float* loss_out, float* dL_dimage, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (C <= 0 || H <= 0 || W <= 0) { set_error("gsm_photometric_loss_static: bad sizes C=%d H=%d W=%d", C, H, W); return GSM_ERR_INVALID_ARGUMENT; }
+  if (image == nullptr || gt == nullptr || dL_dimage == nullptr) { set_error("gsm_photometric_loss_static: null image / gt / gradient"); return GSM_ERR_INVALID_ARGUMENT; }
+  const size_t n = (size_t)C * H * W;
+  if (n > LOSS_STATIC_MAX) {
+    set_error("gsm_photometric_loss_static: C*H*W = %zu exceeds the static scratch limit of %zu pixel-channels "
+              "(GSM_PHOTOMETRIC_LOSS_STATIC_MAX_ELEMENTS); use gsm_photometric_loss with a caller-owned workspace", n, LOSS_STATIC_MAX);
+    return GSM_ERR_WORKSPACE_TOO_SMALL;
+  }
+  unsigned char* ws = nullptr;
+  const int rc = loss_static_setup(&ws);
+  if (rc != GSM_OK) return rc;
+  double* sums = (double*)ws;
+  float* ma = (float*)(ws + 256);
+  float* mb = ma + n;
+  float* mc = mb + n;
+  GSM_CUDA(cudaMemsetAsync(sums, 0, 16, stream));   // the only part that must start at zero
+  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
+  ssim_forward_kernel<<<grid, LOSS_THREADS, 0, stream>>>(image, gt, H, W, ma, mb, mc, sums);
+  ssim_backward_kernel<<<grid, LOSS_THREADS, 0, stream>>>(image, gt, C, H, W, ma, mb, mc, sums, lambda_dssim, grad_scale,
+                                                          loss_out, dL_dimage);
+  GSM_CUDA(cudaGetLastError());
+  return GSM_OK;
+}

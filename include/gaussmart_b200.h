@@ -269,6 +269,21 @@ size_t gsm_photometric_loss_workspace_bytes(int C, int H, int W);
 int gsm_photometric_loss(const float* image, const float* gt, int C, int H, int W, float lambda_dssim,
                          float grad_scale, float* loss_out, float* dL_dimage, void* workspace,
                          size_t workspace_bytes, void* stream);
+/* ---- allocation-free variant of gsm_photometric_loss.  NO counterpart in the reference: added
+ *      for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ *      harnesses that forbid it).  Same inputs, outputs and numerics as gsm_photometric_loss, but the scratch (the SSIM
+ *      sums and the three partial maps) lives in a file-scope `static __device__` array inside the library, sized for
+ *      C*H*W <= GSM_PHOTOMETRIC_LOSS_STATIC_MAX_ELEMENTS: 48 MiB + 256 B of device memory on every GPU that loads the
+ *      library, held until exit.  Larger images are refused with GSM_ERR_WORKSPACE_TOO_SMALL (gsm_last_error() names
+ *      the limit).  The call performs no cudaMalloc / cudaFree and calls no allocating library routine; its one-time
+ *      set-up per device (cudaGetSymbolAddress of the array, upload of the 11 window weights) happens on the first
+ *      call on that device, so make that call outside a graph capture.  The array is shared by every call on a device
+ *      and keeps the last call's contents (what must start at zero is cleared in stream order): calls that overlap on
+ *      one GPU -- different streams or host threads -- RACE on it and must be serialised by the caller. */
+#define GSM_PHOTOMETRIC_LOSS_STATIC_MAX_ELEMENTS 4194304 /* = 4 Mi pixel-channels, e.g. 3 x 1365 x 1024 */
+size_t gsm_photometric_loss_static_max_elements(void);
+int gsm_photometric_loss_static(const float* image, const float* gt, int C, int H, int W, float lambda_dssim,
+                                float grad_scale, float* loss_out, float* dL_dimage, void* stream);
 
 /* ---- optimizer step of the training iteration.  Replaces, fused into ONE launch over all parameter
  *      tensors, `gaussians.optimizer.step()` (train.py:212) of torch.optim.Adam(l, lr=0.0, eps=1e-15)

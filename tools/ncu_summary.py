@@ -44,7 +44,7 @@ def main():
         # stamped with the commit the capture was taken from (commit BEFORE the GPU visit): bench.py reports it next to
         # roofline.traffic, so a figure from an older build is visible as such
         head = subprocess.run(['git', 'rev-parse', '--short', 'HEAD'], capture_output=True, text=True).stdout.strip()
-        tj['_commit'] = head
+        tj['_commit'] = head or os.environ.get('GSM_COMMIT', '')   # (no .git on the GPU box: the visit script passes it)
         tj['_source'] = os.path.basename(out)
         json.dump(tj, open(os.path.join(os.path.dirname(out), 'traffic.json'), 'w'), indent=1)
     print('wrote', out)

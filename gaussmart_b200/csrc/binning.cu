@@ -25,6 +25,9 @@
 //      and writes point_list, keys_sorted and the strip mask of every instance.
 // HBM traffic: 8 B written + 8 B read + 13 B written per instance (29 B vs 152 B).
 #include "common.cuh"
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
 
 namespace gsm {
 
@@ -32,32 +35,76 @@ namespace gsm {
 // 2. exclusive scan of the per-tile instance counts -> ranges, total R; resets the cursors
 // ---------------------------------------------------------------------------------------------
 constexpr int TSCAN_THREADS = 1024;
+constexpr int TSCAN_CLUSTER = 8;   // CTAs of one thread-block cluster share the tiles; totals cross through DSMEM
 
 // tile_count / tile_cursor are [Nt][TILE_SUBS]: a tile's instances are counted and appended through
 // TILE_SUBS sub-cursors selected by the surfel index, because same-address atomics WITH return
 // serialise in L2 (~27 cycles each): one cursor per tile makes the hottest tile the critical path.
-__global__ void __launch_bounds__(TSCAN_THREADS)
+//
+// One cluster of TSCAN_CLUSTER CTAs (round 1 and 2a: one CTA, 0.10 ms of a 3840x2160 frame's 32,400 tiles).  Every CTA
+// owns a contiguous range of whole chunks: it sums its range, the CTAs exchange the sums through distributed shared
+// memory (no global scratch, nothing to zero between frames), then each scans its range from its own offset.
+__global__ void __cluster_dims__(TSCAN_CLUSTER, 1, 1) __launch_bounds__(TSCAN_THREADS)
 tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_cursor,
                  uint2* __restrict__ ranges, int num_tiles, unsigned long long capacity,
                  const uint32_t* __restrict__ flags, ForwardStatus* __restrict__ status) {
-  // one CTA walks the tiles in chunks of TSCAN_THREADS, one tile (TILE_SUBS counters = 32 B) per thread and chunk, so
+  // a CTA walks its tiles in chunks of TSCAN_THREADS, one tile (TILE_SUBS counters = 32 B) per thread and chunk, so
   // every access is coalesced; the next chunk's counters are requested before the current chunk is scanned
   __shared__ unsigned long long warp_sums[2][TSCAN_THREADS / 32];
+  __shared__ unsigned long long cta_total;      // read by the other CTAs of the cluster
+  __shared__ unsigned long long cta_offset[2];  // sum over the lower ranks, sum over all ranks
   static_assert(TILE_SUBS == 8, "a tile's counters are read as two uint4");
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const uint4* cnt4 = reinterpret_cast<const uint4*>(tile_count);
   uint4* cur4 = reinterpret_cast<uint4*>(tile_cursor);
   const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
-  unsigned long long carry = 0;
+  const int chunks = (num_tiles + TSCAN_THREADS - 1) / TSCAN_THREADS;
+  const int per = ((chunks + TSCAN_CLUSTER - 1) / TSCAN_CLUSTER) * TSCAN_THREADS;
+  const int begin = min(rank * per, num_tiles), end = min(begin + per, num_tiles);
+
+  // ---- pass 1: the range's total
+  unsigned long long mine = 0;
+  for (int i = begin + t; i < end; i += TSCAN_THREADS) {
+    const uint4 c0 = __ldg(cnt4 + 2 * (size_t)i), c1 = __ldg(cnt4 + 2 * (size_t)i + 1);
+    mine += (unsigned long long)c0.x + c0.y + c0.z + c0.w + c1.x + c1.y + c1.z + c1.w;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+  if (lane == 0) warp_sums[0][warp] = mine;
+  __syncthreads();
+  if (warp == 0) {
+    unsigned long long v = warp_sums[0][lane];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) cta_total = v;
+  }
+  cluster.sync();
+  if (warp == 0) {
+    unsigned long long v = 0;
+    if (lane < TSCAN_CLUSTER) v = *cluster.map_shared_rank(&cta_total, lane);
+    unsigned long long below = lane < rank ? v : 0ull, all = v;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      below += __shfl_xor_sync(0xffffffffu, below, o);
+      all += __shfl_xor_sync(0xffffffffu, all, o);
+    }
+    if (lane == 0) { cta_offset[0] = below; cta_offset[1] = all; }
+  }
+  cluster.sync();  // (also: no CTA leaves while another still reads its cta_total)
+
+  // ---- pass 2: scan of the range (the counters come from L2 this time)
+  unsigned long long carry = cta_offset[0];
   uint4 n0 = zero, n1 = zero;
-  if (t < num_tiles) { n0 = __ldg(cnt4 + 2 * (size_t)t); n1 = __ldg(cnt4 + 2 * (size_t)t + 1); }
+  if (begin + t < end) { n0 = __ldg(cnt4 + 2 * (size_t)(begin + t)); n1 = __ldg(cnt4 + 2 * (size_t)(begin + t) + 1); }
   int buf = 0;
-  for (int base = 0; base < num_tiles; base += TSCAN_THREADS, buf ^= 1) {
+  for (int base = begin; base < end; base += TSCAN_THREADS, buf ^= 1) {
     const int i = base + t;
     const uint4 c0 = n0, c1 = n1;
     const int nxt = i + TSCAN_THREADS;
     n0 = zero; n1 = zero;
-    if (nxt < num_tiles) { n0 = __ldg(cnt4 + 2 * (size_t)nxt); n1 = __ldg(cnt4 + 2 * (size_t)nxt + 1); }
+    if (nxt < end) { n0 = __ldg(cnt4 + 2 * (size_t)nxt); n1 = __ldg(cnt4 + 2 * (size_t)nxt + 1); }
     const unsigned long long local = (unsigned long long)c0.x + c0.y + c0.z + c0.w + c1.x + c1.y + c1.z + c1.w;
     unsigned long long inc = local;
 #pragma unroll
@@ -73,7 +120,7 @@ tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__
       if (w < warp) warp_off += s;
       total += s;
     }
-    if (i < num_tiles) {
+    if (i < end) {
       unsigned long long run = carry + warp_off + inc - local;
       const unsigned long long first = run;
       uint4 o;  // absolute slot of each sub-segment's next pair
@@ -87,12 +134,13 @@ tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__
     }
     carry += total;
   }
-  if (t == 0) {
+  if (rank == 0 && t == 0) {
     // R, and whether it fits the binning workspace the host sized from its high-water mark: if not, every kernel
     // behind this one treats the frame as empty (see ForwardStatus) and the host renders it again with a larger one
+    const unsigned long long R = cta_offset[1];
     ForwardStatus st;
-    st.num_rendered = carry;
-    st.overflow = carry > capacity ? 1u : 0u;
+    st.num_rendered = R;
+    st.overflow = R > capacity ? 1u : 0u;
     st.prefiltered_violation = flags[0];
     *status = st;
   }
@@ -100,9 +148,8 @@ tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__
 
 void launch_tile_scan(const uint32_t* tile_count, uint32_t* tile_cursor, uint2* ranges, int num_tiles,
                       unsigned long long capacity, const uint32_t* flags, ForwardStatus* status, cudaStream_t stream) {
-  tile_scan_kernel<<<1, TSCAN_THREADS, 0, stream>>>(tile_count, tile_cursor, ranges, num_tiles, capacity, flags, status);
+  tile_scan_kernel<<<TSCAN_CLUSTER, TSCAN_THREADS, 0, stream>>>(tile_count, tile_cursor, ranges, num_tiles, capacity, flags, status);
 }
-
 
 // ---------------------------------------------------------------------------------------------
 // Block mask of one (surfel, tile) instance: which of the tile's 8 blocks (8x4 pixels) the surfel's conservative
@@ -148,26 +195,33 @@ __device__ __forceinline__ uint32_t instance_block_mask(const short4 bx, const f
 }
 
 // ---------------------------------------------------------------------------------------------
-// 3. scatter (the reference's duplicateWithKeys, rasterizer_impl.cu:70-111): one thread per
-//    surfel; rects of more than 16 tiles are spread over the warp.
+// 3. scatter (the reference's duplicateWithKeys, rasterizer_impl.cu:70-111).  One thread LOADS one surfel, but the
+//    (surfel, tile) instances of a warp's 32 surfels are flattened over its lanes: an inclusive scan of the tile
+//    counts, then lane l takes instances l, l + 32, ... of the warp's list, finds the owning surfel by a 5-step search
+//    over the scanned counts (shuffles) and reads that surfel's rect / box / slabs from shared memory.  (One thread per
+//    surfel with a loop over its tiles ran at 9 of 32 lanes: most surfels touch 1-4 tiles, a few up to 16.)
+//    Rects of more than 16 tiles are spread over the warp one surfel at a time, as before.
 // ---------------------------------------------------------------------------------------------
 // PACKED: P <= 2^24, the pair's value is (block mask << 24 | surfel); otherwise the plain surfel index (the sort's
 // epilogue then gathers box and slabs itself, as in round 1).
+constexpr int SCATTER_THREADS = 256;
 template <bool PACKED>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(SCATTER_THREADS)
 scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ radii,
                uint32_t* __restrict__ tile_cursor, uint2* __restrict__ pairs, int grid_x,
                const short4* __restrict__ bbox, const float4* __restrict__ cull, int no_cull,
                const ForwardStatus* __restrict__ status) {
   if (status->overflow) return;  // R exceeds the pair buffer: nothing may be appended
+  __shared__ uint4 s_rect[SCATTER_THREADS];   // minx | miny << 16, width, ceil(2^16 / width), depth bits
+  __shared__ short4 s_box[PACKED ? SCATTER_THREADS : 1];
+  __shared__ float4 s_slab[PACKED ? SCATTER_THREADS : 1];
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
+  const int wbase = threadIdx.x - lane;
   int r = 0;
   if (idx < P) r = __ldg(radii + idx);
   uint32_t depth_bits = 0;
   int minx = 0, miny = 0, w = 0, n = 0;
-  short4 bx = make_short4(0, 0, 0, 0);
-  float4 dg = make_float4(0.f, 0.f, 0.f, 0.f);
   if (r > 0) {
     // tile rect (getRect, auxiliary.h:67-77) and depth bits as left by the forward preprocess
     const uint4 q = __ldg(rects + idx);
@@ -175,7 +229,6 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ r
     w = (int)(q.y & 0xffffu) - minx;
     n = w * ((int)(q.y >> 16) - miny);
     depth_bits = q.z;
-    if (PACKED && !no_cull) { bx = __ldg(bbox + idx); dg = __ldg(cull + idx); }
   }
   auto value_of = [&](uint32_t surfel, const short4 b, const float4 g, uint32_t tile_x, uint32_t tile_y) -> uint32_t {
     if (!PACKED) return surfel;
@@ -183,25 +236,54 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ r
     return surfel | (m << ID_BITS);
   };
   const int BIG = 16;
-  if (n > 0 && n <= BIG) {
-    // the cursor atomics return a value: four are issued before the first result is consumed, instead of one
-    // L2 round trip per instance in sequence
-    for (int t0 = 0; t0 < n; t0 += 4) {
-      uint32_t slot[4], val[4];
+  const int n_small = (n > 0 && n <= BIG) ? n : 0;
+  int incl = n_small;
 #pragma unroll
-      for (int u = 0; u < 4; u++) {
-        const int t = t0 + u;
-        if (t < n) {
-          const uint32_t ty = (uint32_t)(miny + t / w), tx = (uint32_t)(minx + t % w);
-          const uint32_t tile = ty * (uint32_t)grid_x + tx;
-          slot[u] = atomicAdd(tile_cursor + tile * TILE_SUBS + ((uint32_t)idx & (TILE_SUBS - 1)), 1u);
-          val[u] = value_of((uint32_t)idx, bx, dg, tx, ty);
-        }
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  const int total = __shfl_sync(0xffffffffu, incl, 31);
+  if (n_small) {
+    // t / w for t < 16, w <= 16 as (t * ceil(2^16 / w)) >> 16: exact (error term t * (m w - 2^16) < 2^16)
+    s_rect[threadIdx.x] = make_uint4((uint32_t)minx | ((uint32_t)miny << 16), (uint32_t)w,
+                                     (65535u / (uint32_t)w) + 1u, depth_bits);
+    if (PACKED && !no_cull) { s_box[threadIdx.x] = __ldg(bbox + idx); s_slab[threadIdx.x] = __ldg(cull + idx); }
+  }
+  __syncwarp();
+  // two instances per lane and round: both cursor atomics (they return a value) are issued before either result is used
+  for (int j0 = 0; j0 < total; j0 += 64) {
+    uint32_t slot[2], val[2], dep[2];
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+      const int j = j0 + 32 * u + lane;
+      int s = 0;  // owner: the first lane whose inclusive count exceeds j
+#pragma unroll
+      for (int step = 16; step; step >>= 1) {
+        const int v = __shfl_sync(0xffffffffu, incl, s + step - 1);
+        if (v <= j) s += step;
       }
-#pragma unroll
-      for (int u = 0; u < 4; u++)
-        if (t0 + u < n) pairs[slot[u]] = make_uint2(depth_bits, val[u]);
+      s = min(s, 31);
+      const int first = __shfl_sync(0xffffffffu, incl - n_small, s);
+      slot[u] = 0xffffffffu;
+      if (j < total) {
+        const uint4 q = s_rect[wbase + s];
+        const uint32_t t = (uint32_t)(j - first);
+        const uint32_t row = (t * q.z) >> 16;
+        const uint32_t tx = (q.x & 0xffffu) + (t - row * q.y), ty = (q.x >> 16) + row;
+        const uint32_t surfel = (uint32_t)(idx - lane + s);
+        const uint32_t tile = ty * (uint32_t)grid_x + tx;
+        slot[u] = atomicAdd(tile_cursor + tile * TILE_SUBS + (surfel & (TILE_SUBS - 1)), 1u);
+        short4 b = make_short4(0, 0, 0, 0);
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (PACKED && !no_cull) { b = s_box[wbase + s]; g = s_slab[wbase + s]; }
+        val[u] = value_of(surfel, b, g, tx, ty);
+        dep[u] = q.w;
+      }
     }
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+      if (slot[u] != 0xffffffffu) pairs[slot[u]] = make_uint2(dep[u], val[u]);
   }
   unsigned big = __ballot_sync(0xffffffffu, n > BIG);
   while (big) {

@@ -202,6 +202,20 @@ __device__ __forceinline__ ActivatedRotation activate_rotation(float4 r) {
 // per-lane 128-bit accesses (52 floats = 13 x 16 B, odd).
 constexpr int SH_BULK_STRIDE = 52;  // floats per shared-memory row in bulk mode (M <= 16)
 #ifdef __CUDACC__
+// Transpose of the 32 x 32 bit matrix held one row per lane: on return, bit k of lane i is what bit i of lane k was.
+// Five block-swap stages (16, 8, 4, 2, 1) of one shuffle each: ~30 warp-instructions, where the loop
+// `for j: mine |= ((row[j] >> lane) & 1) << j` over shared memory costs ~130.  All 32 lanes must call it.
+__device__ __forceinline__ uint32_t warp_transpose_bits(uint32_t x, int lane) {
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    const int j = 16 >> k;
+    const uint32_t m = k == 0 ? 0x0000ffffu : k == 1 ? 0x00ff00ffu : k == 2 ? 0x0f0f0f0fu : k == 3 ? 0x33333333u : 0x55555555u;
+    const uint32_t y = __shfl_xor_sync(0xffffffffu, x, j);
+    x = (lane & j) ? (((y >> j) & m) | (x & ~m)) : ((x & m) | ((y & m) << j));
+  }
+  return x;
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");

@@ -261,8 +261,7 @@ __global__ void __launch_bounds__(BWD_WARPS * 32, GSM_BWD_MIN_CTAS) render_bwd_k
 
     // ---- the chunk's pixel masks: lane j holds entry j's, every lane collects the entries of ITS pixel ----
     const uint32_t emask = lane < n_cur ? sm.pmask[s][lane] : 0u;   // pixels that blended entry `lane`
-    uint32_t mine = 0;                                              // entries of the chunk that my pixel blended
-    for (int j = 0; j < n_cur; j++) mine |= ((sm.pmask[s][j] >> lane) & 1u) << j;
+    const uint32_t mine = warp_transpose_bits(emask, lane);         // entries of the chunk that my pixel blended
     // slots: entry j takes ceil(popc/8) quarter-warp slots; exclusive prefix over the entries
     const int cnt = __popc(emask), nq = (cnt + SLOT_W - 1) / SLOT_W;
     int incl = nq;

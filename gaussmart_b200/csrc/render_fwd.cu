@@ -49,7 +49,6 @@ struct FwdWarpSmem {
   uint32_t queue[FWD_QUEUE];
   uint32_t hit[FWD_CHUNK];         // per staged entry: the pixels of the block that blended it
   float cut[FWD_CHUNK];            // per staged entry: upper bound of rho for alpha >= 1/255 (pre-test below)
-  uint32_t cand[FWD_CHUNK];        // GSM_FWD_WALK == 2: per staged entry, the pixels of the block that pass the pre-test
 };
 
 // HANDOVER: collect what the backward needs (per-entry pixel sets, dead block bits); false for inference renders
@@ -180,11 +179,8 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, GSM_FWD_MIN_CTAS) render_fwd_k
           }
         }
       }
-      sm.cand[lane] = pm;
-      __syncwarp();
-      // (2) transpose: every lane collects the entries ITS pixel passed
-      for (int j = 0; j < n_cur; j++) mine |= ((sm.cand[j] >> lane) & 1u) << j;
-      __syncwarp();
+      // (2) transpose (five shuffles): every lane collects the entries ITS pixel passed
+      mine = warp_transpose_bits(pm, lane);
     }
 #else
     for (int j = 0; j < n_cur; j++) {

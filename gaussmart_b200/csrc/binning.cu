@@ -204,7 +204,11 @@ __device__ __forceinline__ uint32_t instance_block_mask(const short4 bx, const f
 // ---------------------------------------------------------------------------------------------
 // PACKED: P <= 2^24, the pair's value is (block mask << 24 | surfel); otherwise the plain surfel index (the sort's
 // epilogue then gathers box and slabs itself, as in round 1).
+#ifndef GSM_SCATTER_UNROLL
+#define GSM_SCATTER_UNROLL 2
+#endif
 constexpr int SCATTER_THREADS = 256;
+constexpr int SCATTER_U = GSM_SCATTER_UNROLL;   // instances per lane and round (returning atomics in flight)
 template <bool PACKED>
 __global__ void __launch_bounds__(SCATTER_THREADS)
 scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ radii,
@@ -252,10 +256,10 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ r
   }
   __syncwarp();
   // two instances per lane and round: both cursor atomics (they return a value) are issued before either result is used
-  for (int j0 = 0; j0 < total; j0 += 64) {
-    uint32_t slot[2], val[2], dep[2];
+  for (int j0 = 0; j0 < total; j0 += 32 * SCATTER_U) {
+    uint32_t slot[SCATTER_U], val[SCATTER_U], dep[SCATTER_U];
 #pragma unroll
-    for (int u = 0; u < 2; u++) {
+    for (int u = 0; u < SCATTER_U; u++) {
       const int j = j0 + 32 * u + lane;
       int s = 0;  // owner: the first lane whose inclusive count exceeds j
 #pragma unroll
@@ -282,7 +286,7 @@ scatter_kernel(int P, const uint4* __restrict__ rects, const int* __restrict__ r
       }
     }
 #pragma unroll
-    for (int u = 0; u < 2; u++)
+    for (int u = 0; u < SCATTER_U; u++)
       if (slot[u] != 0xffffffffu) pairs[slot[u]] = make_uint2(dep[u], val[u]);
   }
   unsigned big = __ballot_sync(0xffffffffu, n > BIG);

@@ -76,14 +76,15 @@ class ClockSampler:
         self.path = None
 
     def start(self):
-        # 100 ms between polls (the profiling recipe uses 200): every NVML poll of power and event reasons briefly holds
-        # up work submission on the sampled GPU; at 20 ms the device-resident loop measured 0.07-0.15 ms per step slower
-        # than the same loop without a sampler, with outliers of several ms in a 20-step region
+        # 200 ms between polls, as in the profiling recipe: every NVML poll of power and event reasons holds up work
+        # submission on the sampled GPU for a few ms.  At 20 ms the device-resident loop measured 0.07-0.15 ms per step
+        # slower than the same loop without a sampler (outliers of several ms in a 20-step region); at 100 ms a 20-step
+        # region still carried 2-4 ms of stall in total
         try:
             f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
             self.path = f.name
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=f,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=f,
                                          stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None

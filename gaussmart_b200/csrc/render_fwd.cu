@@ -41,7 +41,7 @@ namespace gsm {
 #endif
 constexpr int FWD_WARPS = GSM_FWD_WARPS;
 constexpr int FWD_CHUNK = 32;   // entries blended per stage
-constexpr int FWD_QUEUE = 128;  // position queue (power of two, >= FWD_CHUNK + 32)
+constexpr int FWD_QUEUE = 256;  // position queue (power of two, >= FWD_CHUNK - 1 + 128: a scan round queues up to 128)
 
 struct FwdWarpSmem {
   float4 q[2][REC_F4][FWD_CHUNK];  // [stage][field][entry]  5 KB
@@ -89,13 +89,29 @@ __global__ void __launch_bounds__(FWD_WARPS * 32, GSM_FWD_MIN_CTAS) render_fwd_k
   uint32_t scan = 0;           // next list offset (0-based within the tile list) to scan
   uint32_t qhead = 0, qcount = 0;
   auto fill = [&]() {          // scan strip masks until a full chunk is queued or the list ends
+    // 128 entries per round: every lane reads one aligned 32-bit word of the byte-per-entry masks (a quarter of the
+    // dependent loads of a byte per lane; this loop held 12 % of the kernel's stall samples), four ballots keep the
+    // list order.  (Plain loads: other blocks' warps clear THEIR bits of the same words meanwhile.)
+    const uint32_t lt = (1u << lane) - 1u;
     while (qcount < FWD_CHUNK && scan < total) {
-      const uint32_t o = scan + lane;
-      const bool hit = o < total && (p.strip_mask[range.x + o] & strip_bit);  // (plain load: other blocks' warps clear THEIR bits)
-      const unsigned m = __ballot_sync(0xffffffffu, hit);
-      if (hit) sm.queue[(qhead + qcount + __popc(m & ((1u << lane) - 1u))) & (FWD_QUEUE - 1)] = o + 1u;
-      qcount += __popc(m);
-      scan += 32;
+      const uint32_t first = range.x + scan;          // absolute position of the next entry to scan
+      const uint32_t wpos = (first & ~3u) + 4u * (uint32_t)lane;
+      uint32_t wv = 0u;
+      if (wpos < range.y) wv = *reinterpret_cast<const volatile uint32_t*>(p.strip_mask + wpos);
+      bool hit[4];
+      unsigned m[4];
+#pragma unroll
+      for (int b = 0; b < 4; b++) {
+        const uint32_t pos = wpos + (uint32_t)b;
+        hit[b] = pos >= first && pos < range.y && ((wv >> (8 * b)) & strip_bit);
+        m[b] = __ballot_sync(0xffffffffu, hit[b]);
+      }
+      uint32_t at = qhead + qcount + __popc(m[0] & lt) + __popc(m[1] & lt) + __popc(m[2] & lt) + __popc(m[3] & lt);
+#pragma unroll
+      for (int b = 0; b < 4; b++)
+        if (hit[b]) sm.queue[(at++) & (FWD_QUEUE - 1)] = wpos + (uint32_t)b - range.x + 1u;
+      qcount += __popc(m[0]) + __popc(m[1]) + __popc(m[2]) + __popc(m[3]);
+      scan = (first & ~3u) + 128u - range.x;
     }
     __syncwarp();
   };

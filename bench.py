@@ -23,6 +23,7 @@ Nothing here reads /root/reference at run time.
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -864,12 +865,26 @@ def main():
     # ---- value: device-resident
     sampler = ClockSampler(local_rank)
     # nvidia-smi takes ~0.2 s to start sampling and the timed region is only ~0.1 s at the default 20 steps: the
-    # sampler runs from before the warm-up (the same load) to the end of the timed region
+    # sampler runs from before the warm-up (the same load, kept on for ~0.6 s) to the end of the timed region
     sampler.start()
-    time.sleep(0.3)
     V = args.views_per_step or world           # views per step over all GPUs
     for s in range(max(args.warmup, 3)):
         arm.value_step(s)
+    barrier(world)
+    # keep the same load on for ~0.6 s more (untimed): with 200 ms between polls at least two samples fall under load
+    # before the timed region starts, and the median clock is a clock under load.  Same step count on every rank.
+    t_w = time.time()
+    for s in range(3):
+        arm.value_step(s)
+    torch.cuda.synchronize()
+    step_s = torch.tensor([(time.time() - t_w) / 3.0], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(step_s, op=dist.ReduceOp.MAX)
+    n_load = int(min(400, max(0, math.ceil(0.6 / max(step_s.item(), 1e-4)))))
+    for s in range(n_load):
+        arm.value_step(s)
+        if s % 8 == 7:
+            torch.cuda.synchronize()
     barrier(world)
     if args.impl == "ours":
         _lib.stage_timing_read(reset=True)   # the stage timers cover the timed region only

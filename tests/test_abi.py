@@ -92,3 +92,19 @@ def test_stage_names():
     lib = _lib.load()
     names = [lib.gsm_stage_name(i).decode() for i in range(lib.gsm_stage_count())]
     assert names[0] == "preprocess_fwd" and "render_bwd" in names and "tile_sort" in names
+
+
+def test_static_scratch_loss_validates_its_arguments_before_any_cuda_call():
+    """gsm_photometric_loss_static checks sizes and pointers first: these calls never reach the device."""
+    lib = _lib.load()
+    limit = lib.gsm_photometric_loss_static_max_elements()
+    src = open(HEADER).read()
+    assert limit == int(re.search(r"#define GSM_PHOTOMETRIC_LOSS_STATIC_MAX_ELEMENTS (\d+)", src).group(1))
+    dummy = ctypes.create_string_buffer(64)
+    ptr = ctypes.cast(dummy, ctypes.c_void_p)
+    too_big = limit // (3 * 2048) + 1
+    assert lib.gsm_photometric_loss_static(ptr, ptr, 3, too_big, 2048, 0.2, 1.0, None, ptr, None) == _lib.GSM_ERR_WORKSPACE_TOO_SMALL
+    assert str(limit) in lib.gsm_last_error().decode()
+    assert lib.gsm_photometric_loss_static(ptr, ptr, 0, 8, 8, 0.2, 1.0, None, ptr, None) == _lib.GSM_ERR_INVALID_ARGUMENT
+    assert lib.gsm_photometric_loss_static(None, ptr, 3, 8, 8, 0.2, 1.0, None, ptr, None) == _lib.GSM_ERR_INVALID_ARGUMENT
+    assert lib.gsm_photometric_loss_static(ptr, ptr, 3, 8, 8, 0.2, 1.0, None, None, None) == _lib.GSM_ERR_INVALID_ARGUMENT
